@@ -1,0 +1,283 @@
+/* nrb200.h — C ABI of libnrb200.so, the B200-native neural-render hot path.
+ *
+ * This is the drop-in boundary for the per-frame path of Alehandreus/neural-renderer.
+ * The reference has no C ABI: its boundary is the C++ class RendererNeural
+ * (reference src/cuda_renderer_neural.h:84-124) fed by Scene/Mesh objects
+ * (src/scene.h:44-71, src/mesh.h:45-78).  Every entry point below cites the reference
+ * member it replaces; the source-compatible C++ class that forwards to these calls lives
+ * in neural-renderer_b200/cpp/ (see INTEGRATION.md).
+ *
+ * Conventions: plain pointers and sizes only, no C++/torch types.  Every function that can
+ * fail returns 0 on success and a negative nrb_status otherwise; nrb_last_error() returns a
+ * thread-local description.  Host arrays passed to nrb_update_* are borrowed for the call
+ * only.  There is no CPU fallback: if no CUDA device (sm_100) is usable nrb_create fails.
+ */
+#ifndef NRB200_H
+#define NRB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NRB_ABI_VERSION 1
+
+typedef enum nrb_status {
+    NRB_OK = 0,
+    NRB_ERR_INVALID = -1,   /* bad argument */
+    NRB_ERR_CUDA = -2,      /* CUDA runtime failure (message in nrb_last_error) */
+    NRB_ERR_STATE = -3,     /* call not valid in the current state (e.g. no weights) */
+    NRB_ERR_SIZE = -4       /* byte-size mismatch (weights file) */
+} nrb_status;
+
+/* ---- POD mirrors of the reference's host structs (layouts are part of the contract) ---- */
+
+/* = BvhNode, reference src/bvh_data.h:5-13 (44 bytes). */
+typedef struct nrb_bvh_node {
+    float bounds_min[3];
+    float bounds_max[3];
+    int32_t left, right;    /* inner: child indices (right == left + 1 in reference builds) */
+    int32_t first, count;   /* leaf: triangle range in the leaf-ordered index buffer */
+    int32_t is_leaf;
+} nrb_bvh_node;
+
+/* = MaterialParam / MaterialParamVec3 / Material, reference src/material.h:9-117 (12/20/180 B). */
+typedef struct nrb_material_param {
+    float value;
+    uint32_t texture_id;
+    uint8_t channel;
+    uint8_t textured;
+    uint8_t pad_[2];
+} nrb_material_param;
+
+typedef struct nrb_material_param3 {
+    float value[3];
+    uint32_t texture_id;
+    uint8_t textured;
+    uint8_t pad_[3];
+} nrb_material_param3;
+
+typedef struct nrb_material {
+    nrb_material_param3 base_color;
+    nrb_material_param metallic, roughness, specular, specular_tint, anisotropy;
+    nrb_material_param sheen, sheen_tint;
+    nrb_material_param clearcoat, clearcoat_gloss;
+    nrb_material_param3 normal;
+    nrb_material_param3 base_emission;
+    float emission_scale;
+    float ior;
+    float specular_transmission;
+} nrb_material;
+
+/* = MeshTexture / TextureDeviceView, reference src/mesh.h:23-37 (8-bit texels, host pointer). */
+typedef struct nrb_texture {
+    const unsigned char* pixels;
+    int32_t width, height, channels;
+    int32_t srgb;
+} nrb_texture;
+
+/* What Mesh holds after Mesh::buildBvh (reference src/mesh.h:80-172, src/mesh_bvh.cpp:27-162):
+ * indices are already in BVH leaf order; nodes are the flattened BvhNode[].  Replaces
+ * Mesh::uploadToDevice / Mesh::deviceView (src/mesh.cu:91-261). */
+typedef struct nrb_mesh_desc {
+    const float* vertices;          /* 3 * num_vertices */
+    const float* normals;           /* 3 * num_vertices or NULL */
+    const float* texcoords;         /* 2 * num_vertices or NULL */
+    const uint32_t* indices;        /* 3 * num_triangles, leaf order */
+    int32_t num_triangles;
+    int32_t num_vertices;
+    const nrb_bvh_node* nodes;
+    int32_t num_nodes;
+    const nrb_material* materials;  /* or NULL */
+    const uint32_t* material_map;   /* first triangle of each primitive, or NULL */
+    const int32_t* material_ids;    /* material id of each primitive, or NULL */
+    int32_t num_primitives;
+    int32_t num_materials;
+    const nrb_texture* textures;
+    int32_t num_textures;
+    int32_t texture_nearest;
+    int32_t has_mesh_materials;
+    float bounds_min[3];            /* Mesh::boundsMin()/boundsMax(), src/mesh_bvh.cpp:147-161 */
+    float bounds_max[3];
+} nrb_mesh_desc;
+
+/* Mesh slots of Scene (reference src/scene.h:46-56). */
+typedef enum nrb_mesh_slot {
+    NRB_MESH_ORIGINAL = 0,
+    NRB_MESH_INNER_SHELL = 1,
+    NRB_MESH_OUTER_SHELL = 2,
+    NRB_MESH_ADDITIONAL = 3,
+    NRB_MESH_SLOT_COUNT = 4
+} nrb_mesh_slot;
+
+/* = NeuralNetworkConfig, reference src/config_loader.h:46-50, plus the network shape that the
+ * reference hard-codes in the RendererNeural ctor (src/cuda_renderer_neural.cu:1647-1688).
+ * Zero in any shape field selects the reference value given in the comment. */
+typedef struct nrb_nn_config {
+    int32_t log2_hashmap_size;      /* 14 */
+    int32_t base_resolution;        /* 16 */
+    int32_t n_points;               /* 3 (entry, exit, mid) */
+    int32_t n_levels;               /* 8 */
+    int32_t n_features_per_level;   /* 4 */
+    float per_level_scale;          /* 2.0 */
+    int32_t sh_degree;              /* 4; negative = no direction encoding (inputs are points only) */
+    int32_t mlp_width;              /* 128 */
+    int32_t n_hidden_layers;        /* 4 */
+} nrb_nn_config;
+
+/* TraceMode, reference src/mesh_traversal.cuh:107-111. */
+typedef enum nrb_trace_mode {
+    NRB_TRACE_ANY = 0,
+    NRB_TRACE_FORWARD_ONLY = 1,
+    NRB_TRACE_BACKWARD_ONLY = 2
+} nrb_trace_mode;
+
+/* = PreliminaryHitInfo, reference src/hit_info.h:7-13.  t == 1e30f means no hit. */
+typedef struct nrb_hit {
+    float t, u, v;
+    uint32_t prim;
+} nrb_hit;
+
+typedef struct nrb_renderer nrb_renderer;
+
+/* ---- lifecycle ---------------------------------------------------------------------- */
+
+/* RendererNeural::RendererNeural(Scene&, const NeuralNetworkConfig*)
+ * (src/cuda_renderer_neural.cu:1632-1718).  cfg may be NULL (reference defaults).
+ * device < 0 selects the current CUDA device. */
+int nrb_create(const nrb_nn_config* cfg, int device, nrb_renderer** out);
+/* RendererNeural::~RendererNeural (src/cuda_renderer_neural.cu:1720-1734). */
+void nrb_destroy(nrb_renderer* r);
+const char* nrb_last_error(void);
+int nrb_abi_version(void);
+
+/* ---- scene hand-off ------------------------------------------------------------------ */
+
+/* Mesh::uploadToDevice + Mesh::deviceView (src/mesh.cu:91-261) for one Scene slot; also
+ * builds the re-laid-out traversal structure.  desc == NULL or num_triangles == 0 clears
+ * the slot (an empty view, as MeshDeviceView{}). */
+int nrb_update_mesh(nrb_renderer* r, int slot, const nrb_mesh_desc* desc);
+/* EnvironmentMap::uploadToDevice + deviceView (src/scene.cu:318-342, src/scene.h:10-16).
+ * rgb = fp32 triplets, row-major, w*h of them; NULL selects the sky gradient branch
+ * (src/cuda_renderer_neural.cu:166-170). */
+int nrb_update_env(nrb_renderer* r, const float* rgb, int width, int height, float strength);
+/* Scene::globalMaterial() (src/scene.h:61-62). */
+int nrb_set_global_material(nrb_renderer* r, const nrb_material* m);
+
+/* ---- weights ------------------------------------------------------------------------- */
+
+/* RendererNeural::loadWeightsFromFile (src/cuda_renderer_neural.cu:1752-1808): raw little-
+ * endian fp16, (mlp + one hash grid) params; swap_order != 0 means [hg | mlp] (the
+ * reference default, cuda_renderer_neural.h:235), else [mlp | hg].  The single grid is
+ * shared by all point encoders (the reference tiles it n_points times). */
+int nrb_load_weights(nrb_renderer* r, const void* fp16, size_t bytes, int swap_order);
+int nrb_load_weights_file(nrb_renderer* r, const char* path, int swap_order);
+/* RendererNeural::paramsBytes(): bytes of the reference's [mlp | hg x n_points] block. */
+size_t nrb_params_bytes(const nrb_renderer* r);
+/* Bytes loadWeightsFromFile expects. */
+size_t nrb_weights_file_bytes(const nrb_renderer* r);
+
+/* ---- per-frame state ------------------------------------------------------------------ */
+
+/* RendererNeural::resize (src/cuda_renderer_neural.cu:1736-1746). */
+int nrb_resize(nrb_renderer* r, int width, int height);
+/* RendererNeural::setCameraBasis (RenderBasis, src/renderer.h:5-10). */
+int nrb_set_camera_basis(nrb_renderer* r, const float forward[3], const float right[3],
+                         const float up[3], float fov_y);
+
+/* The setters of cuda_renderer_neural.h:94-114. */
+typedef enum nrb_option {
+    NRB_OPT_USE_NEURAL_QUERY = 0,     /* setUseNeuralQuery */
+    NRB_OPT_SAMPLES_PER_PIXEL = 1,    /* setSamplesPerPixel */
+    NRB_OPT_BOUNCE_COUNT = 2,         /* setBounceCount */
+    NRB_OPT_LAMBERT_VIEW = 3,         /* setLambertView */
+    NRB_OPT_CLASSIC_MESH_INDEX = 4,   /* setClassicMeshIndex */
+    NRB_OPT_USE_ADDITIONAL_MESH = 5,  /* setUseAdditionalMesh */
+    NRB_OPT_USE_CONSTANT_NEURAL_COLOR = 6, /* setConstantNeuralColor(use, .) */
+    NRB_OPT_USE_DIRECT_ENV_COLOR = 7, /* setDirectEnvColor(use, .) */
+    NRB_OPT_CAPTURE = 8,              /* (new) keep per-element debug buffers for nrb_read_buffer */
+    NRB_OPT_USE_HARDWARE_RT = 9       /* setUseHardwareRT: accepted, ignored (no OptiX path) */
+} nrb_option;
+int nrb_set_option(nrb_renderer* r, int option, int value);
+int nrb_get_option(const nrb_renderer* r, int option);
+/* setEnvmapRotation (degrees). */
+int nrb_set_envmap_rotation(nrb_renderer* r, float degrees);
+/* colour arguments of setConstantNeuralColor / setDirectEnvColor. */
+int nrb_set_constant_neural_color(nrb_renderer* r, const float rgb[3]);
+int nrb_set_direct_env_color(nrb_renderer* r, const float rgb[3]);
+/* resetSamples(). */
+int nrb_reset_samples(nrb_renderer* r);
+/* (new, multi-GPU) this renderer owns the image rows whose band index
+ * (row / band_rows) is congruent to rank modulo world; pixel indices and RNG streams stay
+ * global, so the union over ranks equals the 1-GPU image bit for bit.  world == 1 = all. */
+int nrb_set_tile(nrb_renderer* r, int band_rows, int rank, int world);
+
+/* ---- the frame ------------------------------------------------------------------------ */
+
+/* RendererNeural::render(const Vec3& camPos) (src/cuda_renderer_neural.cu:2085-2755).
+ * Returns after the work has been enqueued and joined to the legacy default stream, so a
+ * following cudaMemcpy from nrb_device_pixels() is ordered after the frame (the reference's
+ * callers rely on this, evaluate.cu:266). */
+int nrb_render(nrb_renderer* r, const float cam_pos[3]);
+/* RendererNeural::devicePixels(): uchar4 RGBA, row-major, width*height (device pointer). */
+void* nrb_device_pixels(const nrb_renderer* r);
+/* Convenience for host callers: blocking copy of devicePixels into rgba (4*width*height B). */
+int nrb_read_pixels(nrb_renderer* r, void* rgba, size_t bytes);
+int nrb_width(const nrb_renderer* r);
+int nrb_height(const nrb_renderer* r);
+uint32_t nrb_accum_sample_count(const nrb_renderer* r);
+
+/* KernelTimings / lastFrameTimings (src/cuda_renderer_neural.h:17-66): ms per the 13
+ * reference buckets, rayCount, neuralRayCalls; always compiled in here. */
+#define NRB_TIMING_BUCKETS 13
+int nrb_get_timings(nrb_renderer* r, double ms[NRB_TIMING_BUCKETS], int* ray_count,
+                    uint64_t* neural_ray_calls);
+/* (new) counters of the last frame: [0] kernels launched, [1] rays traced (segments),
+ * [2] neural queries, [3] path vertices shaded. */
+int nrb_get_counters(nrb_renderer* r, uint64_t out[4]);
+
+/* (new, parity/debug) copy one of the renderer's per-element buffers to the host, in the
+ * reference's layout (src/cuda_renderer_neural.h:160-214).  Needs NRB_OPT_CAPTURE = 1
+ * before the frame.  Names: "hit_positions", "hit_normals", "hit_colors",
+ * "hit_material_params" (3 floats/element), "hit_flags" (int32/element), "hit_distances"
+ * (float/element), "path_radiance" (3 floats/element), "accum" (3 floats/pixel). */
+int nrb_read_buffer(nrb_renderer* r, const char* name, void* dst, size_t bytes);
+
+/* ---- batch entry points (the kernels behind the frame, on caller-supplied arrays) -------
+ * *_host variants take host pointers and copy both ways inside the call; the others take
+ * device pointers and enqueue on the renderer's stream (call nrb_sync to wait). */
+
+/* traceMeshWithMode (src/mesh_traversal.cuh:118-222) for n rays against one slot's mesh:
+ * closest hit with the reference's facing rules; out[i] = {t,u,v,prim} or t = 1e30f. */
+int nrb_trace_rays(nrb_renderer* r, int slot, int mode, const float* d_origins,
+                   const float* d_directions, size_t n, nrb_hit* d_out);
+int nrb_trace_rays_host(nrb_renderer* r, int slot, int mode, const float* origins,
+                        const float* directions, size_t n, nrb_hit* out);
+
+/* network_->inference_mixed_precision (src/cuda_renderer_neural.cu:2031; tiny-cuda-nn
+ * object.h:166-209): inputs fp32 [n][input_dims] (ray-major, = column-major
+ * [input_dims x n]), outputs fp16 [n][16].  n need not be a multiple of 256. */
+int nrb_neural_query(nrb_renderer* r, const float* d_inputs, size_t n, void* d_outputs_fp16);
+int nrb_neural_query_host(nrb_renderer* r, const float* inputs, size_t n, void* outputs_fp16);
+int nrb_input_dims(const nrb_renderer* r);
+int nrb_output_dims(const nrb_renderer* r);
+
+int nrb_sync(nrb_renderer* r);
+/* The renderer's stream as a cudaStream_t (so callers can record events on it). */
+void* nrb_stream(const nrb_renderer* r);
+
+/* ---- host-side helper ------------------------------------------------------------------
+ * (new) SAH BVH build producing the reference's BvhNode[] / leaf-ordered index format
+ * (what Mesh::buildBvh yields, src/mesh_bvh.cpp:27-162), for callers that do not link
+ * the reference's ext/bvh builder.  indices is permuted in place; nodes must hold
+ * 2*num_triangles entries; *num_nodes receives the count; prim_ids (optional,
+ * num_triangles) receives the source triangle of each output triangle. */
+int nrb_build_bvh(const float* vertices, int num_vertices, uint32_t* indices, int num_triangles,
+                  nrb_bvh_node* nodes, int* num_nodes, uint32_t* prim_ids);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NRB200_H */

@@ -1,0 +1,335 @@
+"""Host-side mirror of the reference's renderer interface over the C ABI.
+
+``RendererNeural`` has the reference class's public surface (src/cuda_renderer_neural.h:84-124):
+same method names (snake_case), argument meaning and error behaviour; ``Scene`` / ``MeshData`` stand
+in for src/scene.h:44-71 and what ``Mesh`` holds after ``buildBvh`` (src/mesh.h:80-172).
+The class is library-agnostic (it takes a ``Lib``): the product binds ``nrb_`` of libnrb200.so; tests
+bind the CPU oracle's ``orc_`` entry points to the very same wrapper.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import List, Optional
+
+import numpy as np
+
+from . import _capi as K
+
+
+@dataclass
+class MeshData:
+    """A mesh as ``Mesh`` holds it after ``Mesh::buildBvh`` (leaf-ordered indices + flattened nodes)."""
+    vertices: np.ndarray                      # [V,3] f32
+    indices: np.ndarray                       # [T,3] u32, BVH leaf order
+    nodes: np.ndarray                         # [N] BVH_NODE_DTYPE
+    normals: Optional[np.ndarray] = None      # [V,3] f32
+    texcoords: Optional[np.ndarray] = None    # [V,2] f32
+    bounds_min: Optional[np.ndarray] = None
+    bounds_max: Optional[np.ndarray] = None
+    materials: List[K.Material] = field(default_factory=list)
+    material_map: Optional[np.ndarray] = None  # [P] u32
+    material_ids: Optional[np.ndarray] = None  # [P] i32
+    textures: list = field(default_factory=list)  # list of (pixels u8 [h,w,c], srgb)
+    texture_nearest: bool = False
+    has_mesh_materials: bool = False
+
+    def __post_init__(self):
+        self.vertices = np.ascontiguousarray(self.vertices, np.float32)
+        self.indices = np.ascontiguousarray(self.indices, np.uint32)
+        if self.bounds_min is None:  # src/mesh_bvh.cpp:147-161
+            self.bounds_min = self.vertices.min(0)
+            self.bounds_max = self.vertices.max(0)
+
+    @property
+    def num_triangles(self):
+        return len(self.indices)
+
+    def desc(self):
+        """-> (MeshDesc, keepalive) for nrb_update_mesh."""
+        keep = []
+        d = K.MeshDesc()
+
+        def arr(a, dt):
+            if a is None:
+                return None
+            a = np.ascontiguousarray(a, dt)
+            keep.append(a)
+            return a.ctypes.data
+
+        d.vertices = arr(self.vertices, np.float32)
+        d.normals = arr(self.normals, np.float32)
+        d.texcoords = arr(self.texcoords, np.float32)
+        d.indices = arr(self.indices, np.uint32)
+        d.num_triangles = len(self.indices)
+        d.num_vertices = len(self.vertices)
+        d.nodes = arr(self.nodes, K.BVH_NODE_DTYPE)
+        d.num_nodes = len(self.nodes)
+        if self.materials:
+            mats = (K.Material * len(self.materials))(*self.materials)
+            keep.append(mats)
+            d.materials = C.cast(mats, C.c_void_p)
+            d.num_materials = len(self.materials)
+        if self.material_map is not None:
+            d.material_map = arr(self.material_map, np.uint32)
+            d.material_ids = arr(self.material_ids, np.int32)
+            d.num_primitives = len(self.material_map)
+        if self.textures:
+            tex = (K.Texture * len(self.textures))()
+            for i, (px, srgb) in enumerate(self.textures):
+                px = np.ascontiguousarray(px, np.uint8)
+                keep.append(px)
+                tex[i].pixels = px.ctypes.data
+                tex[i].height, tex[i].width, tex[i].channels = px.shape
+                tex[i].srgb = int(srgb)
+            keep.append(tex)
+            d.textures = C.cast(tex, C.c_void_p)
+            d.num_textures = len(self.textures)
+        d.texture_nearest = int(self.texture_nearest)
+        d.has_mesh_materials = int(self.has_mesh_materials)
+        d.bounds_min[:] = [float(x) for x in self.bounds_min]
+        d.bounds_max[:] = [float(x) for x in self.bounds_max]
+        return d, keep
+
+
+@dataclass
+class Scene:
+    """src/scene.h:44-71: four mesh slots, environment, global material."""
+    original_mesh: Optional[MeshData] = None
+    inner_shell: Optional[MeshData] = None
+    outer_shell: Optional[MeshData] = None
+    additional_mesh: Optional[MeshData] = None
+    env_pixels: Optional[np.ndarray] = None   # [H,W,3] f32 or None (sky gradient)
+    env_strength: float = 1.0
+    global_material: K.Material = field(default_factory=K.Material.default)
+
+
+@dataclass
+class RenderBasis:
+    """src/renderer.h:5-10."""
+    forward: np.ndarray
+    right: np.ndarray
+    up: np.ndarray
+    fov_y: float
+
+
+def compute_camera_basis(yaw_deg: float, pitch_deg: float, fov_y: float) -> RenderBasis:
+    """computeCameraBasis of the evaluate driver (reference src/evaluate.cu:91-116); yaw/pitch in degrees."""
+    k = np.float32(3.14159265358979323846 / 180.0)
+    yr, pr = np.float32(yaw_deg) * k, np.float32(pitch_deg) * k
+    fwd = np.array([np.cos(pr) * np.cos(yr), np.sin(pr), np.cos(pr) * np.sin(yr)], np.float32)
+    fwd = fwd / np.float32(np.sqrt(np.dot(fwd, fwd)))
+    right = np.cross(fwd, np.array([0.0, 1.0, 0.0], np.float32)).astype(np.float32)
+    rlen = np.float32(np.sqrt(np.dot(right, right)))
+    right = np.array([1.0, 0.0, 0.0], np.float32) if rlen < 1e-4 else right / rlen
+    up = np.cross(right, fwd).astype(np.float32)
+    up = up / np.float32(np.sqrt(np.dot(up, up)))
+    return RenderBasis(fwd, right, up, float(fov_y))
+
+
+def look_at_basis(eye, target, fov_y: float) -> RenderBasis:
+    fwd = np.asarray(target, np.float64) - np.asarray(eye, np.float64)
+    fwd /= np.linalg.norm(fwd)
+    right = np.cross(fwd, [0.0, 1.0, 0.0])
+    right /= np.linalg.norm(right)
+    up = np.cross(right, fwd)
+    return RenderBasis(fwd.astype(np.float32), right.astype(np.float32), up.astype(np.float32), float(fov_y))
+
+
+def _f3(v):
+    return (C.c_float * 3)(*[float(x) for x in v])
+
+
+class RendererNeural:
+    """class RendererNeural (reference src/cuda_renderer_neural.h:84-124) over the C ABI."""
+
+    def __init__(self, scene: Scene, nn_config: Optional[K.NNConfig] = None, lib: Optional[K.Lib] = None,
+                 device: int = -1):
+        self.lib = lib or K.product_lib()
+        self._h = C.c_void_p()
+        self.lib.check(self.lib.fn("create")(C.byref(nn_config) if nn_config is not None else None, device,
+                                             C.byref(self._h)), "create")
+        self.scene = scene
+        self._spp, self._bounces = 1, 0
+        self._use_neural = False
+        self.upload_scene()
+
+    # -- scene hand-off (Mesh::uploadToDevice / EnvironmentMap::uploadToDevice in the reference) ----
+    def upload_scene(self):
+        s = self.scene
+        for slot, m in ((K.SLOT_ORIGINAL, s.original_mesh), (K.SLOT_INNER, s.inner_shell),
+                        (K.SLOT_OUTER, s.outer_shell), (K.SLOT_ADDITIONAL, s.additional_mesh)):
+            if m is None:
+                self.lib.check(self.lib.fn("update_mesh")(self._h, slot, None), "update_mesh")
+            else:
+                d, keep = m.desc()
+                self.lib.check(self.lib.fn("update_mesh")(self._h, slot, C.byref(d)), "update_mesh")
+                del keep
+        if s.env_pixels is not None:
+            e = np.ascontiguousarray(s.env_pixels, np.float32)
+            self.lib.check(self.lib.fn("update_env")(self._h, e.ctypes.data, e.shape[1], e.shape[0],
+                                                     s.env_strength), "update_env")
+        else:
+            self.lib.check(self.lib.fn("update_env")(self._h, None, 0, 0, s.env_strength), "update_env")
+        self.lib.check(self.lib.fn("set_global_material")(self._h, C.byref(s.global_material)), "set_global_material")
+
+    def close(self):
+        if self._h:
+            self.lib.fn("destroy")(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- reference public methods --------------------------------------------------------------------
+    def resize(self, width: int, height: int):
+        self.lib.check(self.lib.fn("resize")(self._h, width, height), "resize")
+
+    def set_camera_basis(self, b: RenderBasis):
+        self.lib.check(self.lib.fn("set_camera_basis")(self._h, _f3(b.forward), _f3(b.right), _f3(b.up),
+                                                       float(b.fov_y)), "set_camera_basis")
+
+    def render(self, cam_pos):
+        self.lib.check(self.lib.fn("render")(self._h, _f3(cam_pos)), "render")
+
+    def device_pixels(self) -> int:
+        return self.lib.fn("device_pixels")(self._h)
+
+    def load_weights_from_file(self, path: str, swap_param_order: bool = True) -> bool:
+        """bool loadWeightsFromFile(path): False (and a message) on open/size mismatch, like the reference."""
+        rc = self.lib.fn("load_weights_file")(self._h, path.encode(), int(swap_param_order))
+        if rc != 0:
+            import sys
+            print(self.lib.fn("last_error")().decode(), file=sys.stderr)
+        return rc == 0
+
+    def load_weights(self, fp16: np.ndarray, swap_param_order: bool = True):
+        a = np.ascontiguousarray(fp16).view(np.uint16)
+        self.lib.check(self.lib.fn("load_weights")(self._h, a.ctypes.data, a.nbytes, int(swap_param_order)),
+                       "load_weights")
+
+    def _opt(self, o, v):
+        self.lib.check(self.lib.fn("set_option")(self._h, o, int(v)), "set_option")
+
+    def set_use_neural_query(self, v: bool):
+        self._use_neural = bool(v)
+        self._opt(K.OPT_USE_NEURAL_QUERY, v)
+
+    def use_neural_query(self) -> bool:
+        return self._use_neural
+
+    def set_samples_per_pixel(self, n: int):
+        self._spp = n
+        self._opt(K.OPT_SAMPLES_PER_PIXEL, n)
+
+    def set_bounce_count(self, n: int):
+        self._bounces = n
+        self._opt(K.OPT_BOUNCE_COUNT, n)
+
+    def set_lambert_view(self, v: bool):
+        self._opt(K.OPT_LAMBERT_VIEW, v)
+
+    def set_classic_mesh_index(self, i: int):
+        self._opt(K.OPT_CLASSIC_MESH_INDEX, i)
+
+    def set_use_additional_mesh(self, v: bool):
+        self._opt(K.OPT_USE_ADDITIONAL_MESH, v)
+
+    def set_use_hardware_rt(self, v: bool):
+        self._opt(K.OPT_USE_HARDWARE_RT, v)
+
+    def set_envmap_rotation(self, degrees: float):
+        self.lib.check(self.lib.fn("set_envmap_rotation")(self._h, float(degrees)), "set_envmap_rotation")
+
+    def set_constant_neural_color(self, use: bool, color):
+        self._opt(K.OPT_USE_CONSTANT_NEURAL_COLOR, use)
+        self.lib.check(self.lib.fn("set_constant_neural_color")(self._h, _f3(color)), "set_constant_neural_color")
+
+    def set_direct_env_color(self, use: bool, color):
+        self._opt(K.OPT_USE_DIRECT_ENV_COLOR, use)
+        self.lib.check(self.lib.fn("set_direct_env_color")(self._h, _f3(color)), "set_direct_env_color")
+
+    def reset_samples(self):
+        self.lib.check(self.lib.fn("reset_samples")(self._h), "reset_samples")
+
+    def samples_per_pixel(self) -> int:
+        return self._spp
+
+    def bounce_count(self) -> int:
+        return self._bounces
+
+    def params_bytes(self) -> int:
+        return self.lib.fn("params_bytes")(self._h)
+
+    def weights_file_bytes(self) -> int:
+        return self.lib.fn("weights_file_bytes")(self._h)
+
+    def width(self) -> int:
+        return self.lib.fn("width")(self._h)
+
+    def height(self) -> int:
+        return self.lib.fn("height")(self._h)
+
+    def last_frame_timings(self):
+        ms = (C.c_double * 13)()
+        rays = C.c_int(0)
+        calls = C.c_uint64(0)
+        self.lib.check(self.lib.fn("get_timings")(self._h, ms, C.byref(rays), C.byref(calls)), "get_timings")
+        return list(ms), rays.value, calls.value
+
+    # -- additions over the reference ----------------------------------------------------------------
+    def set_capture(self, v: bool):
+        self._opt(K.OPT_CAPTURE, v)
+
+    def set_tile(self, band_rows: int, rank: int, world: int):
+        self.lib.check(self.lib.fn("set_tile")(self._h, band_rows, rank, world), "set_tile")
+
+    def read_pixels(self) -> np.ndarray:
+        out = np.zeros((self.height(), self.width(), 4), np.uint8)
+        self.lib.check(self.lib.fn("read_pixels")(self._h, out.ctypes.data, out.nbytes), "read_pixels")
+        return out
+
+    def read_buffer(self, name: str) -> np.ndarray:
+        n = self.width() * self.height() * max(1, self._spp)
+        shape, dt = {"hit_positions": ((n, 3), np.float32), "hit_normals": ((n, 3), np.float32),
+                     "hit_colors": ((n, 3), np.float32), "hit_material_params": ((n, 3), np.float32),
+                     "hit_distances": ((n,), np.float32), "hit_flags": ((n,), np.int32),
+                     "path_radiance": ((n, 3), np.float32),
+                     "accum": ((self.width() * self.height(), 3), np.float32)}[name]
+        out = np.zeros(shape, dt)
+        self.lib.check(self.lib.fn("read_buffer")(self._h, name.encode(), out.ctypes.data, out.nbytes), "read_buffer")
+        return out
+
+    def counters(self):
+        c = (C.c_uint64 * 4)()
+        self.lib.check(self.lib.fn("get_counters")(self._h, c), "get_counters")
+        return dict(kernels=c[0], ray_segments=c[1], neural_queries=c[2], path_vertices=c[3])
+
+    def trace_rays(self, slot: int, mode: int, origins: np.ndarray, directions: np.ndarray) -> np.ndarray:
+        o = np.ascontiguousarray(origins, np.float32)
+        d = np.ascontiguousarray(directions, np.float32)
+        out = np.zeros(len(o), K.HIT_DTYPE)
+        self.lib.check(self.lib.fn("trace_rays_host")(self._h, slot, mode, o.ctypes.data, d.ctypes.data, len(o),
+                                                      out.ctypes.data), "trace_rays_host")
+        return out
+
+    def neural_query(self, inputs: np.ndarray) -> np.ndarray:
+        x = np.ascontiguousarray(inputs, np.float32)
+        assert x.shape[1] == self.input_dims()
+        out = np.zeros((len(x), 16), np.float16)
+        self.lib.check(self.lib.fn("neural_query_host")(self._h, x.ctypes.data, len(x), out.ctypes.data),
+                       "neural_query_host")
+        return out
+
+    def input_dims(self) -> int:
+        return self.lib.fn("input_dims")(self._h)
+
+    def sync(self):
+        self.lib.check(self.lib.fn("sync")(self._h), "sync")
+
+    @property
+    def handle(self):
+        return self._h

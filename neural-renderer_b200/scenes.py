@@ -1,0 +1,143 @@
+"""Deterministic synthetic scenes, shells, environments and weights (SURVEY.md §8d / BASELINE.md §3.3).
+
+The reference tree holds no scene data (dbrt_data/ is absent), so every test and benchmark input is
+generated here with fixed seeds, in the formats the reference consumes: indexed triangle meshes,
+fp32 equirect environment, raw fp16 weight block in [hg | mlp] order
+(src/cuda_renderer_neural.cu:1752-1808).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def uv_sphere(stacks: int = 48, slices: int = 96, radius: float = 1.0):
+    """GenerateUvSphere (reference src/mesh_loader.cpp:719-764): vertices, normals, uvs, indices."""
+    kPi = np.float32(3.14159265358979323846)
+    i = np.arange(stacks + 1, dtype=np.float32)[:, None] / np.float32(stacks)
+    j = np.arange(slices + 1, dtype=np.float32)[None, :] / np.float32(slices)
+    phi = (i * kPi).astype(np.float32)
+    theta = (j * np.float32(2.0) * kPi).astype(np.float32)
+    x = (np.sin(phi) * np.cos(theta)).astype(np.float32)
+    y = (np.cos(phi) * np.ones_like(theta)).astype(np.float32)
+    z = (np.sin(phi) * np.sin(theta)).astype(np.float32)
+    n = np.stack([x, y, z], -1).reshape(-1, 3)
+    v = (n * np.float32(radius)).astype(np.float32)
+    uv = np.stack([np.broadcast_to(j, x.shape), np.broadcast_to(i, x.shape)], -1).reshape(-1, 2).astype(np.float32)
+    ii, jj = np.meshgrid(np.arange(stacks), np.arange(slices), indexing="ij")
+    p0 = (ii * (slices + 1) + jj).reshape(-1)
+    p1, p2 = p0 + 1, p0 + (slices + 1)
+    p3 = p2 + 1
+    idx = np.stack([np.stack([p0, p2, p1], -1), np.stack([p1, p2, p3], -1)], 1).reshape(-1, 3).astype(np.uint32)
+    return v, n.astype(np.float32), uv, idx
+
+
+def icosphere(subdivisions: int):
+    """Unit icosphere: 20 * 4**subdivisions triangles, outward-facing (CCW seen from outside)."""
+    t = (1.0 + 5.0 ** 0.5) / 2.0
+    v = np.array([[-1, t, 0], [1, t, 0], [-1, -t, 0], [1, -t, 0], [0, -1, t], [0, 1, t], [0, -1, -t], [0, 1, -t],
+                  [t, 0, -1], [t, 0, 1], [-t, 0, -1], [-t, 0, 1]], np.float64)
+    v /= np.linalg.norm(v, axis=1, keepdims=True)
+    f = np.array([[0, 11, 5], [0, 5, 1], [0, 1, 7], [0, 7, 10], [0, 10, 11], [1, 5, 9], [5, 11, 4], [11, 10, 2],
+                  [10, 7, 6], [7, 1, 8], [3, 9, 4], [3, 4, 2], [3, 2, 6], [3, 6, 8], [3, 8, 9], [4, 9, 5],
+                  [2, 4, 11], [6, 2, 10], [8, 6, 7], [9, 8, 1]], np.int64)
+    for _ in range(subdivisions):
+        e = np.concatenate([f[:, [0, 1]], f[:, [1, 2]], f[:, [2, 0]]], 0)
+        es = np.sort(e, 1)
+        key = es[:, 0] * (len(v) + 1) + es[:, 1]
+        uniq, inv = np.unique(key, return_inverse=True)
+        a, b = uniq // (len(v) + 1), uniq % (len(v) + 1)
+        mid = v[a] + v[b]
+        mid /= np.linalg.norm(mid, axis=1, keepdims=True)
+        base = len(v)
+        v = np.concatenate([v, mid], 0)
+        n = len(f)
+        m01, m12, m20 = base + inv[:n], base + inv[n:2 * n], base + inv[2 * n:]
+        f = np.concatenate([np.stack([f[:, 0], m01, m20], 1), np.stack([f[:, 1], m12, m01], 1),
+                            np.stack([f[:, 2], m20, m12], 1), np.stack([m01, m12, m20], 1)], 0)
+    return v.astype(np.float32), f.astype(np.uint32)
+
+
+def displace(vertices: np.ndarray, amplitude: float = 0.1, seed: int = 1337, octaves: int = 4):
+    """Radial displacement amplitude * mean_k sin(f_k . p + phi_k) with mt19937(seed) frequencies/phases."""
+    rng = np.random.RandomState(seed)
+    p = vertices.astype(np.float64)
+    d = np.zeros(len(p))
+    for k in range(octaves):
+        fvec = rng.uniform(-1, 1, 3) * (3.0 * 2 ** k)
+        phi = rng.uniform(0, 2 * np.pi)
+        d += np.sin(p @ fvec + phi) / (k + 1)
+    d /= sum(1.0 / (k + 1) for k in range(octaves))
+    r = 1.0 + amplitude * d
+    return (p * r[:, None]).astype(np.float32)
+
+
+def vertex_normals(vertices, indices):
+    v = vertices.astype(np.float64)
+    fn = np.cross(v[indices[:, 1]] - v[indices[:, 0]], v[indices[:, 2]] - v[indices[:, 0]])
+    n = np.zeros_like(v)
+    for c in range(3):
+        np.add.at(n, indices[:, c], fn)
+    n /= np.maximum(np.linalg.norm(n, axis=1, keepdims=True), 1e-30)
+    return n.astype(np.float32)
+
+
+def ground_quad(y: float = -1.3, half: float = 4.0):
+    v = np.array([[-half, y, -half], [half, y, -half], [half, y, half], [-half, y, half]], np.float32)
+    idx = np.array([[0, 2, 1], [0, 3, 2]], np.uint32)  # normal +y
+    return v, idx
+
+
+def sky_env(width: int = 2048, height: int = 1024, seed: int = 7):
+    """Synthetic fp32 equirect: vertical gradient + a bright sun lobe + seeded low-amplitude noise."""
+    rng = np.random.RandomState(seed)
+    v = (np.arange(height, dtype=np.float32) + 0.5) / height
+    u = (np.arange(width, dtype=np.float32) + 0.5) / width
+    theta = v[:, None] * np.pi
+    phi = (u[None, :] - 0.5) * 2 * np.pi
+    d = np.stack([np.sin(theta) * np.sin(phi), np.cos(theta) * np.ones_like(phi), -np.sin(theta) * np.cos(phi)], -1)
+    sun = np.array([0.4, 0.7, -0.59])
+    sun /= np.linalg.norm(sun)
+    lobe = np.clip(d @ sun, 0, 1) ** 256
+    grad = 0.5 * (d[..., 1:2] + 1.0)
+    img = (1 - grad) * np.array([0.9, 0.85, 0.8]) + grad * np.array([0.35, 0.55, 1.0])
+    img = img + lobe[..., None] * np.array([60.0, 55.0, 45.0])
+    img = img * (1.0 + 0.05 * rng.standard_normal((height, width, 1)))
+    return np.ascontiguousarray(np.maximum(img, 0.0), np.float32)
+
+
+def network_sizes(log2_hashmap_size=14, base_resolution=16, n_points=3, n_levels=8, n_features=4,
+                  per_level_scale=2.0, sh_degree=4, mlp_width=128, n_hidden=4):
+    """(grid halfs, mlp halfs, per-level offsets) — GridEncodingTemplated ctor, tiny-cuda-nn grid.h:699-730."""
+    offsets = [0]
+    log2s = np.float32(np.log2(np.float32(per_level_scale)))
+    for l in range(n_levels):
+        scale = np.float32(np.exp2(np.float32(l) * log2s)) * np.float32(base_resolution) - np.float32(1.0)
+        res = int(np.ceil(scale)) + 1
+        n = min(res ** 3, 0xFFFFFFFF // 2)
+        n = (n + 7) // 8 * 8
+        n = min(n, 1 << log2_hashmap_size)
+        offsets.append(offsets[-1] + n)
+    enc = n_points * n_levels * n_features + sh_degree * sh_degree
+    mlp = mlp_width * enc + (n_hidden - 1) * mlp_width * mlp_width + 16 * mlp_width
+    return offsets[-1] * n_features, mlp, offsets
+
+
+def make_weights(seed: int = 42, grid_range: float = 0.5, out_bias_hit: float = 0.0, **net):
+    """Seeded weight file in the reference's default [hg | mlp] order: grid U(-r, r), Xavier-uniform MLP."""
+    ng, nm, _ = network_sizes(**net)
+    rng = np.random.RandomState(seed)
+    grid = rng.uniform(-grid_range, grid_range, ng).astype(np.float16)
+    n_points, n_levels, n_features = net.get("n_points", 3), net.get("n_levels", 8), net.get("n_features", 4)
+    shd, w, nh = net.get("sh_degree", 4), net.get("mlp_width", 128), net.get("n_hidden", 4)
+    enc = n_points * n_levels * n_features + shd * shd
+    mats = []
+    fan_in = enc
+    for _ in range(nh):
+        lim = np.sqrt(6.0 / (fan_in + w))
+        mats.append(rng.uniform(-lim, lim, (w, fan_in)))
+        fan_in = w
+    lim = np.sqrt(6.0 / (w + 16))
+    mats.append(rng.uniform(-lim, lim, (16, w)))
+    mlp = np.concatenate([m.reshape(-1) for m in mats]).astype(np.float16)
+    assert len(mlp) == nm
+    return np.concatenate([grid, mlp])
