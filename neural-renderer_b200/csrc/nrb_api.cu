@@ -1,0 +1,864 @@
+// nrb_api.cu — the C ABI of libnrb200.so (include/nrb200.h) and the host orchestration behind it.
+//
+// Mirrors the host side of the reference's RendererNeural (src/cuda_renderer_neural.cu:1632-3003):
+// constructor/network shape, weight loading, buffer lifecycle, accumulation-reset rules and the
+// render() entry point.  The frame itself is enqueued by nrb_frame.cu / nrb_segments.cu /
+// nrb_neural.cu on one non-blocking stream per renderer and joined to the legacy default stream
+// before nrb_render returns (callers issue a plain cudaMemcpy from devicePixels() next,
+// src/evaluate.cu:266).  There is no CPU fallback anywhere in this file: every entry point that
+// needs a device fails with NRB_ERR_CUDA when none is usable.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/nrb200.h"
+#include "nrb_frame.cuh"
+#include "nrb_neural.cuh"
+#include "nrb_trace.cuh"
+
+using namespace nrb;
+
+static_assert(sizeof(nrb_material) == sizeof(MaterialDev), "material layout");
+static_assert(sizeof(nrb_hit) == sizeof(Hit), "hit layout");
+static_assert(sizeof(nrb_bvh_node) == 44, "BvhNode layout");
+
+namespace {
+
+thread_local std::string g_error;
+
+int fail(int code, const std::string& msg) {
+    g_error = msg;
+    return code;
+}
+
+#define NRB_CUDA(expr)                                                                              \
+    do {                                                                                            \
+        cudaError_t err__ = (expr);                                                                 \
+        if (err__ != cudaSuccess)                                                                   \
+            return fail(NRB_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(err__));       \
+    } while (0)
+
+// Owning device allocation.
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    ~DevBuf() { release(); }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+    }
+    cudaError_t alloc(size_t n) {
+        release();
+        if (n == 0) return cudaSuccess;
+        cudaError_t e = cudaMalloc(&p, n);
+        if (e == cudaSuccess) bytes = n;
+        return e;
+    }
+    cudaError_t upload(const void* src, size_t n, cudaStream_t s) {
+        cudaError_t e = alloc(n);
+        if (e != cudaSuccess || n == 0) return e;
+        e = cudaMemcpyAsync(p, src, n, cudaMemcpyHostToDevice, s);
+        if (e != cudaSuccess) return e;
+        return cudaStreamSynchronize(s);  // the host array is borrowed for the call only
+    }
+    template <class T>
+    T* as() const { return static_cast<T*>(p); }
+};
+
+struct MeshSlot {
+    DevBuf nodes, tris, vertices, normals, texcoords, indices, materials, materialMap, materialIds, textures;
+    std::vector<DevBuf> texPixels;
+    MeshDev view{};
+    float boundsMin[3] = {0, 0, 0}, boundsMax[3] = {0, 0, 0};
+    int depth = 0;
+    void clear() {
+        nodes.release(); tris.release(); vertices.release(); normals.release(); texcoords.release();
+        indices.release(); materials.release(); materialMap.release(); materialIds.release(); textures.release();
+        texPixels.clear();
+        view = MeshDev{};
+        depth = 0;
+    }
+};
+
+}  // namespace
+
+struct nrb_renderer {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t evStart = nullptr, evStop = nullptr, evJoin = nullptr;
+
+    // scene
+    MeshSlot mesh[4];
+    DevBuf envPixels;
+    int envW = 0, envH = 0;
+    float envStrength = 1.0f;
+    MaterialDev globalMaterial{};
+
+    // network
+    nrb_nn_config cfg{};
+    NetDev net{};
+    DevBuf grid, mlp;
+    size_t gridParams = 0, mlpParams = 0;
+    bool weightsLoaded = false;
+
+    // RendererNeural state (src/cuda_renderer_neural.h:216-277)
+    float fwd[3] = {0, 0, -1}, right[3] = {1, 0, 0}, up[3] = {0, 1, 0}, fovY = 0.785f;
+    int width = 0, height = 0;
+    bool lambertView = false, useNeuralQuery = false;
+    int samplesPerPixel = 1, bounceCount = 0, classicMeshIndex = 0;
+    float envmapRotation = 0.0f;
+    bool useConstantNeuralColor = false, useDirectEnvColor = false, useAdditionalMesh = true;
+    float constantNeuralColor[3] = {0.8f, 0.8f, 0.8f}, directEnvColor[3] = {0, 0, 0};
+    uint32_t accumSampleCount = 0;
+    bool lastUseNeuralQuery = true, lastLambertView = false, lastUseAdditionalMesh = true, hasLastCamera = false;
+    int lastBounceCount = -1, lastSamplesPerPixel = -1, lastClassicMeshIndex = -1;
+    float lastEnvmapRotation = 0.0f, lastCam[3] = {0, 0, 0}, lastFwd[3], lastRight[3], lastUp[3], lastFovY = 0.0f;
+    int capture = 0;
+    int bandRows = 16, rank = 0, world = 1;
+
+    // wavefront state
+    std::vector<DevBuf> pool;
+    State st{};
+    DevBuf accum, pixels;
+    size_t stateElems = 0, accumPixels = 0, pixelCount = 0;
+    int localHeight = 0;
+
+    // last frame
+    double lastMs = 0.0;
+    bool lastNeural = false;
+    int lastRayCount = 0, lastLaunches = 0;
+    uint64_t lastStats[8] = {0};
+    DevBuf scratchA, scratchB, scratchC;  // host-variant batch entry points
+};
+
+namespace {
+
+int local_rows(const nrb_renderer* r) {
+    if (r->world <= 1) return r->height;
+    int rows = 0;
+    for (int y0 = r->rank * r->bandRows; y0 < r->height; y0 += r->world * r->bandRows)
+        rows += std::min(r->bandRows, r->height - y0);
+    return rows;
+}
+
+// ---- network shape (RendererNeural ctor :1647-1688; GridEncodingTemplated ctor, tiny-cuda-nn
+// encodings/grid.h:673-737; grid_scale / grid_resolution, common_device.h:886-895) --------------
+int configure_network(nrb_renderer* r, const nrb_nn_config* c) {
+    nrb_nn_config d{};
+    if (c) d = *c;
+    if (d.log2_hashmap_size <= 0) d.log2_hashmap_size = 14;
+    if (d.base_resolution <= 0) d.base_resolution = 16;
+    if (d.n_points <= 0) d.n_points = 3;
+    if (d.n_levels <= 0) d.n_levels = 8;
+    if (d.n_features_per_level <= 0) d.n_features_per_level = 4;
+    if (d.per_level_scale <= 0.0f) d.per_level_scale = 2.0f;
+    if (d.sh_degree == 0) d.sh_degree = 4;
+    else if (d.sh_degree < 0) d.sh_degree = 0;
+    if (d.mlp_width <= 0) d.mlp_width = 128;
+    if (d.n_hidden_layers <= 0) d.n_hidden_layers = 4;
+    if (d.n_levels > kMaxLevels || d.n_points > 4 || d.sh_degree > 4 || d.log2_hashmap_size > 28)
+        return fail(NRB_ERR_INVALID, "network shape out of range");
+    r->cfg = d;
+    NetDev& n = r->net;
+    n = NetDev{};
+    n.nPoints = d.n_points; n.nLevels = d.n_levels; n.nFeatures = d.n_features_per_level;
+    n.shDegree = d.sh_degree; n.width = d.mlp_width; n.nHidden = d.n_hidden_layers;
+    n.inputDims = 3 * d.n_points + (d.sh_degree > 0 ? 3 : 0);
+    n.encDims = d.n_points * d.n_levels * d.n_features_per_level + d.sh_degree * d.sh_degree;
+    const float log2Scale = std::log2(d.per_level_scale);
+    uint32_t offset = 0;
+    for (int l = 0; l < d.n_levels; ++l) {
+        const float scale = exp2f(l * log2Scale) * d.base_resolution - 1.0f;
+        const uint32_t res = static_cast<uint32_t>(ceilf(scale)) + 1u;
+        const uint32_t cap = 0xFFFFFFFFu / 2u;
+        uint32_t entries = std::pow(static_cast<float>(res), 3) > static_cast<float>(cap) ? cap : res * res * res;
+        entries = (entries + 7u) / 8u * 8u;
+        entries = std::min(entries, 1u << d.log2_hashmap_size);
+        n.levelOffset[l] = offset;
+        n.levelSize[l] = entries;
+        n.levelRes[l] = res;
+        n.levelScale[l] = scale;
+        // grid_index: linear while res^3 fits the level, else hashed (stride overflow guard at 0x659)
+        const bool fits = res <= 0x659u && static_cast<uint64_t>(res) * res * res <= entries;
+        n.levelDense[l] = fits ? 1 : 0;
+        n.levelPow2[l] = (entries & (entries - 1u)) == 0 ? 1 : 0;
+        offset += entries;
+    }
+    r->gridParams = static_cast<size_t>(offset) * d.n_features_per_level;
+    const size_t w = d.mlp_width;
+    r->mlpParams = w * n.encDims + static_cast<size_t>(d.n_hidden_layers - 1) * w * w + 16 * w;
+    int warps = 0;
+    if (neural_query_smem(n, &warps) == 0) return fail(NRB_ERR_INVALID, "unsupported network shape for the fused query kernel");
+    return NRB_OK;
+}
+
+// ---- BVH re-layout ------------------------------------------------------------------------------
+int relayout_mesh(nrb_renderer* r, MeshSlot& m, const nrb_mesh_desc* d) {
+    const int nn = d->num_nodes, nt = d->num_triangles;
+    const nrb_bvh_node* src = d->nodes;
+    if (!src || nn <= 0 || !d->vertices || !d->indices) return fail(NRB_ERR_INVALID, "mesh without nodes/vertices/indices");
+    for (int i = 0; i < 3 * nt; ++i)
+        if (d->indices[i] >= static_cast<uint32_t>(d->num_vertices)) return fail(NRB_ERR_INVALID, "vertex index out of range");
+
+    // triangle blocks in leaf (= primitive id) order; same operation order as the reference's
+    // per-candidate normalize(cross(v1 - v0, v2 - v0)) (src/mesh_traversal.cuh:163)
+    std::vector<TriBlock> tris(nt);
+    for (int i = 0; i < nt; ++i) {
+        const V3 v0 = ld3(d->vertices, d->indices[3 * i]), v1 = ld3(d->vertices, d->indices[3 * i + 1]),
+                 v2 = ld3(d->vertices, d->indices[3 * i + 2]);
+        const V3 e1 = v1 - v0, e2 = v2 - v0;
+        const V3 n = normalize(cross(e1, e2));
+        tris[i].p = make_float4(v0.x, v0.y, v0.z, n.x);
+        tris[i].q = make_float4(e1.x, e1.y, e1.z, n.y);
+        tris[i].r = make_float4(e2.x, e2.y, e2.z, n.z);
+    }
+
+    auto check_leaf = [&](const nrb_bvh_node& n) {
+        return n.count >= 1 && n.count <= (1 << kLeafCountBits) && n.first >= 0 && n.first + n.count <= nt &&
+               n.first < (1 << (31 - kLeafCountBits));
+    };
+    std::vector<NodePair> pairs;
+    MeshDev& v = m.view;
+    std::memcpy(v.rootMin, src[0].bounds_min, 12);
+    std::memcpy(v.rootMax, src[0].bounds_max, 12);
+    int maxDepth = 1;
+    if (src[0].is_leaf) {
+        if (!check_leaf(src[0])) return fail(NRB_ERR_INVALID, "bad root leaf");
+        v.rootRef = leaf_ref(src[0].first, src[0].count);
+    } else {
+        // DFS pre-order numbering of inner nodes keeps a subtree's pairs adjacent in memory
+        struct Item { int node, pair, depth; };
+        std::vector<Item> todo;
+        pairs.reserve(nn / 2 + 1);
+        pairs.emplace_back();
+        todo.push_back({0, 0, 1});
+        std::vector<char> seen(nn, 0);
+        while (!todo.empty()) {
+            const Item it = todo.back();
+            todo.pop_back();
+            const nrb_bvh_node& n = src[it.node];
+            maxDepth = std::max(maxDepth, it.depth);
+            const int kids[2] = {n.left, n.right};
+            int refs[2];
+            for (int k = 0; k < 2; ++k) {
+                const int c = kids[k];
+                if (c <= 0 || c >= nn || seen[c]) return fail(NRB_ERR_INVALID, "bad child index in BVH");
+                seen[c] = 1;
+                if (src[c].is_leaf) {
+                    if (!check_leaf(src[c])) return fail(NRB_ERR_INVALID, "leaf range out of bounds (or > 32 triangles)");
+                    refs[k] = leaf_ref(src[c].first, src[c].count);
+                } else {
+                    refs[k] = static_cast<int>(pairs.size());
+                    pairs.emplace_back();
+                }
+            }
+            // right first on the stack so the left subtree is numbered first
+            if (!src[kids[1]].is_leaf) todo.push_back({kids[1], refs[1], it.depth + 1});
+            if (!src[kids[0]].is_leaf) todo.push_back({kids[0], refs[0], it.depth + 1});
+            const nrb_bvh_node& L = src[kids[0]];
+            const nrb_bvh_node& R = src[kids[1]];
+            NodePair& p = pairs[it.pair];
+            p.a = make_float4(L.bounds_min[0], L.bounds_min[1], L.bounds_min[2], L.bounds_max[0]);
+            p.b = make_float4(L.bounds_max[1], L.bounds_max[2], R.bounds_min[0], R.bounds_min[1]);
+            p.c = make_float4(R.bounds_min[2], R.bounds_max[0], R.bounds_max[1], R.bounds_max[2]);
+            p.d = make_int4(refs[0], refs[1], L.is_leaf ? L.count : 0, R.is_leaf ? R.count : 0);
+        }
+        v.rootRef = 0;
+    }
+    if (maxDepth >= kTraceStack) return fail(NRB_ERR_INVALID, "BVH deeper than the traversal stack (64)");
+    m.depth = maxDepth;
+    NRB_CUDA(m.nodes.upload(pairs.data(), pairs.size() * sizeof(NodePair), r->stream));
+    NRB_CUDA(m.tris.upload(tris.data(), tris.size() * sizeof(TriBlock), r->stream));
+    v.nodes = m.nodes.as<NodePair>();
+    v.tris = m.tris.as<TriBlock>();
+    v.numPairs = static_cast<int>(pairs.size());
+    v.numTriangles = nt;
+    return NRB_OK;
+}
+
+}  // namespace
+
+// =================================================================================================
+// C entry points
+// =================================================================================================
+extern "C" {
+
+const char* nrb_last_error(void) { return g_error.c_str(); }
+int nrb_abi_version(void) { return NRB_ABI_VERSION; }
+
+int nrb_create(const nrb_nn_config* cfg, int device, nrb_renderer** out) {
+    if (!out) return fail(NRB_ERR_INVALID, "out is null");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(NRB_ERR_CUDA, std::string("no usable CUDA device (libnrb200 has no CPU path): ") +
+                                      (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0"));
+    if (device < 0) NRB_CUDA(cudaGetDevice(&device));
+    if (device >= count) return fail(NRB_ERR_INVALID, "device index out of range");
+    NRB_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop{};
+    NRB_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(NRB_ERR_CUDA, "libnrb200 is built for sm_100a only; device is sm_" + std::to_string(prop.major) +
+                                      std::to_string(prop.minor));
+    nrb_renderer* r = new nrb_renderer();
+    r->device = device;
+    int rc = configure_network(r, cfg);
+    if (rc != NRB_OK) { delete r; return rc; }
+    if (cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&r->evStart) != cudaSuccess || cudaEventCreate(&r->evStop) != cudaSuccess ||
+        cudaEventCreateWithFlags(&r->evJoin, cudaEventDisableTiming) != cudaSuccess) {
+        delete r;
+        return fail(NRB_ERR_CUDA, "stream/event creation failed");
+    }
+    // Material::defaultMaterial(), src/material.h:86-106
+    MaterialDev& g = r->globalMaterial;
+    std::memset(&g, 0, sizeof(g));
+    g.base_color.value[0] = g.base_color.value[1] = g.base_color.value[2] = 0.8f;
+    g.clearcoat_gloss.value = 1.0f;
+    g.emission_scale = 1.0f;
+    g.ior = 1.5f;
+    *out = r;
+    return NRB_OK;
+}
+
+void nrb_destroy(nrb_renderer* r) {
+    if (!r) return;
+    cudaSetDevice(r->device);
+    if (r->stream) cudaStreamSynchronize(r->stream);
+    if (r->evStart) cudaEventDestroy(r->evStart);
+    if (r->evStop) cudaEventDestroy(r->evStop);
+    if (r->evJoin) cudaEventDestroy(r->evJoin);
+    if (r->stream) cudaStreamDestroy(r->stream);
+    delete r;
+}
+
+int nrb_update_mesh(nrb_renderer* r, int slot, const nrb_mesh_desc* d) {
+    if (!r || slot < 0 || slot >= NRB_MESH_SLOT_COUNT) return fail(NRB_ERR_INVALID, "bad renderer/slot");
+    NRB_CUDA(cudaSetDevice(r->device));
+    NRB_CUDA(cudaStreamSynchronize(r->stream));
+    MeshSlot& m = r->mesh[slot];
+    m.clear();
+    if (!d || d->num_triangles <= 0) return NRB_OK;
+    int rc = relayout_mesh(r, m, d);
+    if (rc != NRB_OK) { m.clear(); return rc; }
+    MeshDev& v = m.view;
+    cudaStream_t s = r->stream;
+    NRB_CUDA(m.vertices.upload(d->vertices, sizeof(float) * 3 * d->num_vertices, s));
+    NRB_CUDA(m.indices.upload(d->indices, sizeof(uint32_t) * 3 * d->num_triangles, s));
+    v.vertices = m.vertices.as<float>();
+    v.indices = m.indices.as<uint32_t>();
+    if (d->normals) {
+        NRB_CUDA(m.normals.upload(d->normals, sizeof(float) * 3 * d->num_vertices, s));
+        v.normals = m.normals.as<float>();
+    }
+    if (d->texcoords) {
+        NRB_CUDA(m.texcoords.upload(d->texcoords, sizeof(float) * 2 * d->num_vertices, s));
+        v.texcoords = m.texcoords.as<float>();
+    }
+    if (d->materials && d->num_materials > 0) {
+        NRB_CUDA(m.materials.upload(d->materials, sizeof(nrb_material) * d->num_materials, s));
+        v.materials = m.materials.as<MaterialDev>();
+        v.numMaterials = d->num_materials;
+    }
+    if (d->material_map && d->material_ids && d->num_primitives > 0) {
+        NRB_CUDA(m.materialMap.upload(d->material_map, sizeof(uint32_t) * d->num_primitives, s));
+        NRB_CUDA(m.materialIds.upload(d->material_ids, sizeof(int32_t) * d->num_primitives, s));
+        v.materialMap = m.materialMap.as<uint32_t>();
+        v.materialIds = m.materialIds.as<int>();
+        v.numPrimitives = d->num_primitives;
+    }
+    if (d->textures && d->num_textures > 0) {
+        std::vector<TexDev> tv(d->num_textures);
+        m.texPixels.resize(d->num_textures);
+        for (int i = 0; i < d->num_textures; ++i) {
+            const nrb_texture& t = d->textures[i];
+            const size_t bytes = static_cast<size_t>(t.width) * t.height * t.channels;
+            if (t.pixels && bytes) NRB_CUDA(m.texPixels[i].upload(t.pixels, bytes, s));
+            tv[i] = TexDev{m.texPixels[i].as<unsigned char>(), t.width, t.height, t.channels, t.srgb};
+        }
+        NRB_CUDA(m.textures.upload(tv.data(), sizeof(TexDev) * tv.size(), s));
+        v.textures = m.textures.as<TexDev>();
+        v.numTextures = d->num_textures;
+    }
+    v.textureNearest = d->texture_nearest;
+    v.hasMeshMaterials = d->has_mesh_materials;
+    std::memcpy(m.boundsMin, d->bounds_min, 12);
+    std::memcpy(m.boundsMax, d->bounds_max, 12);
+    return NRB_OK;
+}
+
+int nrb_update_env(nrb_renderer* r, const float* rgb, int width, int height, float strength) {
+    if (!r) return fail(NRB_ERR_INVALID, "null renderer");
+    NRB_CUDA(cudaSetDevice(r->device));
+    NRB_CUDA(cudaStreamSynchronize(r->stream));
+    r->envPixels.release();
+    r->envW = r->envH = 0;
+    r->envStrength = strength;
+    if (rgb && width > 0 && height > 0) {
+        NRB_CUDA(r->envPixels.upload(rgb, sizeof(float) * 3 * static_cast<size_t>(width) * height, r->stream));
+        r->envW = width;
+        r->envH = height;
+    }
+    return NRB_OK;
+}
+
+int nrb_set_global_material(nrb_renderer* r, const nrb_material* m) {
+    if (!r || !m) return fail(NRB_ERR_INVALID, "null argument");
+    std::memcpy(&r->globalMaterial, m, sizeof(MaterialDev));
+    return NRB_OK;
+}
+
+size_t nrb_params_bytes(const nrb_renderer* r) { return (r->gridParams * r->cfg.n_points + r->mlpParams) * 2; }
+size_t nrb_weights_file_bytes(const nrb_renderer* r) { return (r->gridParams + r->mlpParams) * 2; }
+
+int nrb_load_weights(nrb_renderer* r, const void* fp16, size_t bytes, int swap_order) {
+    if (!r || !fp16) return fail(NRB_ERR_INVALID, "null argument");
+    const size_t expect = nrb_weights_file_bytes(r);
+    if (bytes != expect)
+        return fail(NRB_ERR_SIZE, "Weights file size mismatch: expected " + std::to_string(expect) + " bytes, got " +
+                                      std::to_string(bytes));
+    NRB_CUDA(cudaSetDevice(r->device));
+    NRB_CUDA(cudaStreamSynchronize(r->stream));
+    const uint16_t* file = static_cast<const uint16_t*>(fp16);
+    const uint16_t* srcMlp = swap_order ? file + r->gridParams : file;
+    const uint16_t* srcGrid = swap_order ? file : file + r->mlpParams;
+    NRB_CUDA(r->grid.upload(srcGrid, r->gridParams * 2, r->stream));
+    NRB_CUDA(r->mlp.upload(srcMlp, r->mlpParams * 2, r->stream));
+    r->net.grid = r->grid.as<__half>();
+    r->net.mlp = r->mlp.as<__half>();
+    r->weightsLoaded = true;
+    return NRB_OK;
+}
+
+int nrb_load_weights_file(nrb_renderer* r, const char* path, int swap_order) {
+    if (!r || !path) return fail(NRB_ERR_INVALID, "null argument");
+    FILE* f = std::fopen(path, "rb");
+    if (!f) return fail(NRB_ERR_INVALID, std::string("Failed to open weights file: ") + path);
+    std::fseek(f, 0, SEEK_END);
+    const long size = std::ftell(f);
+    std::fseek(f, 0, SEEK_SET);
+    std::vector<unsigned char> data(size > 0 ? static_cast<size_t>(size) : 0);
+    const size_t got = data.empty() ? 0 : std::fread(data.data(), 1, data.size(), f);
+    std::fclose(f);
+    if (got != data.size()) return fail(NRB_ERR_INVALID, std::string("Failed to read weights file: ") + path);
+    return nrb_load_weights(r, data.data(), data.size(), swap_order);
+}
+
+int nrb_resize(nrb_renderer* r, int width, int height) {
+    if (!r) return fail(NRB_ERR_INVALID, "null renderer");
+    if (width == r->width && height == r->height) return NRB_OK;
+    NRB_CUDA(cudaSetDevice(r->device));
+    NRB_CUDA(cudaStreamSynchronize(r->stream));
+    r->width = width;
+    r->height = height;
+    // RendererNeural::resize frees every buffer (src/cuda_renderer_neural.cu:1736-1746)
+    r->pool.clear();
+    r->accum.release();
+    r->pixels.release();
+    r->stateElems = r->accumPixels = r->pixelCount = 0;
+    r->accumSampleCount = 0;
+    return NRB_OK;
+}
+
+int nrb_set_camera_basis(nrb_renderer* r, const float forward[3], const float right[3], const float up[3], float fov_y) {
+    if (!r) return fail(NRB_ERR_INVALID, "null renderer");
+    std::memcpy(r->fwd, forward, 12);
+    std::memcpy(r->right, right, 12);
+    std::memcpy(r->up, up, 12);
+    r->fovY = fov_y;
+    return NRB_OK;
+}
+
+int nrb_set_option(nrb_renderer* r, int option, int value) {
+    if (!r) return fail(NRB_ERR_INVALID, "null renderer");
+    switch (option) {
+        case NRB_OPT_USE_NEURAL_QUERY: r->useNeuralQuery = value != 0; break;
+        case NRB_OPT_SAMPLES_PER_PIXEL: r->samplesPerPixel = value; break;
+        case NRB_OPT_BOUNCE_COUNT: r->bounceCount = value; break;
+        case NRB_OPT_LAMBERT_VIEW: r->lambertView = value != 0; break;
+        case NRB_OPT_CLASSIC_MESH_INDEX: r->classicMeshIndex = value; break;
+        case NRB_OPT_USE_ADDITIONAL_MESH: r->useAdditionalMesh = value != 0; break;
+        case NRB_OPT_USE_CONSTANT_NEURAL_COLOR: r->useConstantNeuralColor = value != 0; break;
+        case NRB_OPT_USE_DIRECT_ENV_COLOR: r->useDirectEnvColor = value != 0; break;
+        case NRB_OPT_CAPTURE: r->capture = value; break;
+        case NRB_OPT_USE_HARDWARE_RT: break;  // accepted, ignored: there is no OptiX path
+        default: return fail(NRB_ERR_INVALID, "unknown option");
+    }
+    return NRB_OK;
+}
+
+int nrb_get_option(const nrb_renderer* r, int option) {
+    switch (option) {
+        case NRB_OPT_USE_NEURAL_QUERY: return r->useNeuralQuery;
+        case NRB_OPT_SAMPLES_PER_PIXEL: return r->samplesPerPixel;
+        case NRB_OPT_BOUNCE_COUNT: return r->bounceCount;
+        case NRB_OPT_LAMBERT_VIEW: return r->lambertView;
+        case NRB_OPT_CLASSIC_MESH_INDEX: return r->classicMeshIndex;
+        case NRB_OPT_USE_ADDITIONAL_MESH: return r->useAdditionalMesh;
+        case NRB_OPT_USE_CONSTANT_NEURAL_COLOR: return r->useConstantNeuralColor;
+        case NRB_OPT_USE_DIRECT_ENV_COLOR: return r->useDirectEnvColor;
+        case NRB_OPT_CAPTURE: return r->capture;
+        default: return 0;
+    }
+}
+
+int nrb_set_envmap_rotation(nrb_renderer* r, float degrees) { r->envmapRotation = degrees; return NRB_OK; }
+int nrb_set_constant_neural_color(nrb_renderer* r, const float rgb[3]) { std::memcpy(r->constantNeuralColor, rgb, 12); return NRB_OK; }
+int nrb_set_direct_env_color(nrb_renderer* r, const float rgb[3]) { std::memcpy(r->directEnvColor, rgb, 12); return NRB_OK; }
+
+int nrb_set_tile(nrb_renderer* r, int band_rows, int rank, int world) {
+    if (!r || band_rows <= 0 || world <= 0 || rank < 0 || rank >= world) return fail(NRB_ERR_INVALID, "bad tile spec");
+    if (band_rows != r->bandRows || rank != r->rank || world != r->world) {
+        r->bandRows = band_rows; r->rank = rank; r->world = world;
+        r->pool.clear();
+        r->accum.release();
+        r->stateElems = r->accumPixels = 0;
+        r->accumSampleCount = 0;
+    }
+    return NRB_OK;
+}
+
+int nrb_width(const nrb_renderer* r) { return r->width; }
+int nrb_height(const nrb_renderer* r) { return r->height; }
+uint32_t nrb_accum_sample_count(const nrb_renderer* r) { return r->accumSampleCount; }
+void* nrb_device_pixels(const nrb_renderer* r) { return r->pixels.p; }
+void* nrb_stream(const nrb_renderer* r) { return r->stream; }
+int nrb_input_dims(const nrb_renderer* r) { return r->net.inputDims; }
+int nrb_output_dims(const nrb_renderer*) { return 16; }
+
+int nrb_sync(nrb_renderer* r) {
+    NRB_CUDA(cudaSetDevice(r->device));
+    NRB_CUDA(cudaStreamSynchronize(r->stream));
+    return NRB_OK;
+}
+
+}  // extern "C"
+
+// =================================================================================================
+// Buffers and the frame
+// =================================================================================================
+namespace {
+
+// ensureNetworkBuffers / ensureAccumBuffer (src/cuda_renderer_neural.cu:2826-2975): one pool of
+// 16-byte-record SoA arrays sized for the elements this renderer owns.
+int ensure_state(nrb_renderer* r, size_t nElems, size_t localPixels, size_t framePixels) {
+    if (nElems != r->stateElems) {
+        r->pool.clear();
+        r->st = State{};
+        const size_t n = (nElems + 255) / 256 * 256;
+        auto take = [&](size_t bytes, void** out) -> cudaError_t {
+            r->pool.emplace_back();
+            cudaError_t e = r->pool.back().alloc(bytes);
+            *out = r->pool.back().p;
+            return e;
+        };
+        State& s = r->st;
+        for (int k = 0; k < 3; ++k) {
+            NRB_CUDA(take(n * 16, reinterpret_cast<void**>(&s.rec[k].P)));
+            NRB_CUDA(take(n * 16, reinterpret_cast<void**>(&s.rec[k].N)));
+            NRB_CUDA(take(n * 16, reinterpret_cast<void**>(&s.rec[k].C)));
+            NRB_CUDA(take(n * 8, reinterpret_cast<void**>(&s.rec[k].M)));
+            if (k == 1) break;  // rec[2] is reserved (the hybrid-mesh hit is merged in registers)
+        }
+        float4** f4s[] = {&s.T, &s.L, &s.rayO, &s.rayD, &s.rayW, &s.prevD, &s.segE, &s.segD, &s.segX};
+        for (float4** p : f4s) NRB_CUDA(take(n * 16, reinterpret_cast<void**>(p)));
+        NRB_CUDA(take(n * 8, reinterpret_cast<void**>(&s.segI)));
+        for (int q = 0; q < 4; ++q) NRB_CUDA(take(n * 4, reinterpret_cast<void**>(&s.queue[q])));
+        NRB_CUDA(take(64 * sizeof(int), reinterpret_cast<void**>(&s.counts)));
+        NRB_CUDA(take(16 * sizeof(unsigned long long), reinterpret_cast<void**>(&s.stats)));
+        NRB_CUDA(take(n * r->net.inputDims * sizeof(float), reinterpret_cast<void**>(&s.netIn)));
+        NRB_CUDA(take(n * 16 * sizeof(__half), reinterpret_cast<void**>(&s.netOut)));
+        r->stateElems = nElems;
+    }
+    if (localPixels != r->accumPixels) {
+        NRB_CUDA(r->accum.alloc(localPixels * 3 * sizeof(float)));
+        NRB_CUDA(cudaMemsetAsync(r->accum.p, 0, r->accum.bytes, r->stream));
+        r->accumPixels = localPixels;
+        r->accumSampleCount = 0;
+    }
+    if (framePixels != r->pixelCount) {
+        NRB_CUDA(r->pixels.alloc(framePixels * sizeof(uchar4)));
+        NRB_CUDA(cudaMemsetAsync(r->pixels.p, 0, r->pixels.bytes, r->stream));
+        r->pixelCount = framePixels;
+    }
+    r->st.accum = r->accum.as<float>();
+    r->st.pixels = r->pixels.as<uchar4>();
+    return NRB_OK;
+}
+
+bool differs(const float* a, const float* b, float eps) {
+    return std::fabs(a[0] - b[0]) > eps || std::fabs(a[1] - b[1]) > eps || std::fabs(a[2] - b[2]) > eps;
+}
+
+V3 to_v3(const float* p) { return V3{p[0], p[1], p[2]}; }
+
+}  // namespace
+
+extern "C" {
+
+int nrb_reset_samples(nrb_renderer* r) {
+    if (!r) return fail(NRB_ERR_INVALID, "null renderer");
+    NRB_CUDA(cudaSetDevice(r->device));
+    if (r->accum.p) NRB_CUDA(cudaMemsetAsync(r->accum.p, 0, r->accum.bytes, r->stream));
+    r->accumSampleCount = 0;
+    return NRB_OK;
+}
+
+int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
+    if (!r || !cam_pos) return fail(NRB_ERR_INVALID, "null argument");
+    if (r->width <= 0 || r->height <= 0) return NRB_OK;  // the reference returns silently (:2086-2091)
+    NRB_CUDA(cudaSetDevice(r->device));
+    const int maxBounces = std::max(0, r->bounceCount);
+    const int spp = r->samplesPerPixel <= 0 ? 1 : r->samplesPerPixel;
+
+    // classic mesh selection (:2119-2125)
+    int classicSlot = NRB_MESH_ORIGINAL;
+    if (r->classicMeshIndex == 1 && r->mesh[NRB_MESH_INNER_SHELL].view.numTriangles > 0) classicSlot = NRB_MESH_INNER_SHELL;
+    else if (r->classicMeshIndex == 2 && r->mesh[NRB_MESH_OUTER_SHELL].view.numTriangles > 0) classicSlot = NRB_MESH_OUTER_SHELL;
+
+    const size_t framePixels = static_cast<size_t>(r->width) * r->height;
+    r->localHeight = local_rows(r);
+    const size_t localPixels = static_cast<size_t>(r->width) * r->localHeight;
+    const size_t nElems = localPixels * spp;
+    if (nElems >= (1ull << 31)) return fail(NRB_ERR_INVALID, "width*height*spp exceeds 2^31 elements; render in smaller spp batches");
+    int rc = ensure_state(r, nElems, localPixels, framePixels);
+    if (rc != NRB_OK) return rc;
+
+    // accumulation reset rules (:2190-2217)
+    bool cameraMoved = !r->hasLastCamera;
+    const float kEps = 1e-4f;
+    if (!cameraMoved)
+        cameraMoved = differs(cam_pos, r->lastCam, kEps) || differs(r->fwd, r->lastFwd, kEps) ||
+                      differs(r->right, r->lastRight, kEps) || differs(r->up, r->lastUp, kEps) ||
+                      std::fabs(r->fovY - r->lastFovY) > kEps;
+    if (cameraMoved || r->useNeuralQuery != r->lastUseNeuralQuery || r->lambertView != r->lastLambertView ||
+        maxBounces != r->lastBounceCount || spp != r->lastSamplesPerPixel || r->classicMeshIndex != r->lastClassicMeshIndex ||
+        r->envmapRotation != r->lastEnvmapRotation || r->useAdditionalMesh != r->lastUseAdditionalMesh) {
+        rc = nrb_reset_samples(r);
+        if (rc != NRB_OK) return rc;
+    }
+    r->lastUseNeuralQuery = r->useNeuralQuery; r->lastLambertView = r->lambertView; r->lastBounceCount = maxBounces;
+    r->lastSamplesPerPixel = spp; r->lastClassicMeshIndex = r->classicMeshIndex; r->lastEnvmapRotation = r->envmapRotation;
+    r->lastUseAdditionalMesh = r->useAdditionalMesh; r->lastFovY = r->fovY; r->hasLastCamera = true;
+    std::memcpy(r->lastCam, cam_pos, 12); std::memcpy(r->lastFwd, r->fwd, 12);
+    std::memcpy(r->lastRight, r->right, 12); std::memcpy(r->lastUp, r->up, 12);
+
+    Frame f{};
+    FrameParams& fp = f.fp;
+    fp.camPos = to_v3(cam_pos); fp.camForward = to_v3(r->fwd); fp.camRight = to_v3(r->right); fp.camUp = to_v3(r->up);
+    const MeshSlot& outer = r->mesh[NRB_MESH_OUTER_SHELL];
+    fp.outerMin = to_v3(outer.boundsMin);
+    for (int k = 0; k < 3; ++k) {  // (:2171-2178)
+        const float ext = outer.boundsMax[k] - outer.boundsMin[k];
+        (&fp.outerInvExtent.x)[k] = ext != 0.0f ? 1.0f / ext : 0.0f;
+    }
+    const MeshSlot& classic = r->mesh[classicSlot];
+    const float sx = classic.boundsMax[0] - classic.boundsMin[0], sy = classic.boundsMax[1] - classic.boundsMin[1],
+                sz = classic.boundsMax[2] - classic.boundsMin[2];
+    float sceneScale = sqrtf(sx * sx + sy * sy + sz * sz);  // (:2180-2189)
+    if (sceneScale < 1e-6f) sceneScale = 1.0f;
+    fp.constantNeuralColor = to_v3(r->constantNeuralColor);
+    fp.directEnvColor = to_v3(r->directEnvColor);
+    fp.tanHalfFov = tanf(r->fovY * 0.5f);
+    fp.aspect = static_cast<float>(r->width) / static_cast<float>(r->height);
+    fp.maxRadiance = 100.0f;
+    fp.sceneScale = sceneScale;
+    fp.useConstantNeuralColor = r->useConstantNeuralColor;
+    fp.useDirectEnvColor = r->useDirectEnvColor;
+    fp.maxBounces = maxBounces;
+    fp.width = r->width; fp.height = r->height; fp.pixelCount = static_cast<int>(framePixels); fp.spp = spp;
+    fp.sampleOffset = r->accumSampleCount;
+    fp.bandRows = r->bandRows; fp.rank = r->rank; fp.world = r->world; fp.localHeight = r->localHeight;
+    fp.localPixels = static_cast<int>(localPixels);
+    fp.nElems = static_cast<int>(nElems);
+    fp.nPoints = r->net.nPoints; fp.inputDims = r->net.inputDims;
+    for (int k = 0; k < 4; ++k) f.mesh[k] = r->mesh[k].view;
+    if (!r->useAdditionalMesh) f.mesh[NRB_MESH_ADDITIONAL] = MeshDev{};
+    f.env = EnvDev{r->envPixels.as<float>(), r->envW, r->envH, r->envmapRotation, r->envStrength};
+    f.gmat = r->globalMaterial;
+    f.st = r->st;
+    f.classicSlot = classicSlot;
+    f.additionalEnabled = r->useAdditionalMesh ? 1 : 0;
+
+    cudaStream_t s = r->stream;
+    NRB_CUDA(cudaMemsetAsync(r->st.stats, 0, 16 * sizeof(unsigned long long), s));
+    NRB_CUDA(cudaEventRecord(r->evStart, s));
+    const bool neural = r->useNeuralQuery && r->weightsLoaded && outer.view.numTriangles > 0;  // (:2258-2260)
+    int launches;
+    if (neural) launches = launch_neural_frame(f, r->net, r->lambertView, s);
+    else launches = launch_gt_frame(f, r->lambertView, s);
+    NRB_CUDA(cudaEventRecord(r->evStop, s));
+    NRB_CUDA(cudaGetLastError());
+    if (r->lambertView) r->accumSampleCount = 0;
+    else r->accumSampleCount += static_cast<uint32_t>(spp);
+    r->lastNeural = neural;
+    r->lastLaunches = launches;
+    r->lastRayCount = static_cast<int>(nElems);
+    // join to the legacy default stream: a following cudaMemcpy(devicePixels) sees the frame
+    NRB_CUDA(cudaEventRecord(r->evJoin, s));
+    NRB_CUDA(cudaStreamWaitEvent(cudaStreamLegacy, r->evJoin, 0));
+    return NRB_OK;
+}
+
+int nrb_read_pixels(nrb_renderer* r, void* rgba, size_t bytes) {
+    if (!r || !rgba) return fail(NRB_ERR_INVALID, "null argument");
+    if (bytes != r->pixelCount * 4 || !r->pixels.p) return fail(NRB_ERR_SIZE, "pixel buffer size mismatch");
+    NRB_CUDA(cudaSetDevice(r->device));
+    NRB_CUDA(cudaMemcpyAsync(rgba, r->pixels.p, bytes, cudaMemcpyDeviceToHost, r->stream));
+    NRB_CUDA(cudaStreamSynchronize(r->stream));
+    return NRB_OK;
+}
+
+static int fetch_stats(nrb_renderer* r) {
+    if (!r->st.stats) return NRB_OK;
+    NRB_CUDA(cudaSetDevice(r->device));
+    NRB_CUDA(cudaStreamSynchronize(r->stream));
+    NRB_CUDA(cudaMemcpy(r->lastStats, r->st.stats, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    return NRB_OK;
+}
+
+int nrb_get_timings(nrb_renderer* r, double ms[NRB_TIMING_BUCKETS], int* ray_count, uint64_t* neural_ray_calls) {
+    if (!r || !ms) return fail(NRB_ERR_INVALID, "null argument");
+    int rc = fetch_stats(r);
+    if (rc != NRB_OK) return rc;
+    for (int i = 0; i < NRB_TIMING_BUCKETS; ++i) ms[i] = 0.0;
+    float t = 0.0f;
+    if (r->lastLaunches > 0 && cudaEventElapsedTime(&t, r->evStart, r->evStop) == cudaSuccess) {
+        // stages are fused across the reference's buckets; the frame total is attributed to the
+        // traversal bucket of the active mode (KID_primaryTrace / KID_shellTrace)
+        ms[r->lastNeural ? 2 : 0] = t;
+    }
+    if (ray_count) *ray_count = r->lastRayCount;
+    if (neural_ray_calls) *neural_ray_calls = r->lastStats[1];
+    return NRB_OK;
+}
+
+int nrb_get_counters(nrb_renderer* r, uint64_t out[4]) {
+    if (!r || !out) return fail(NRB_ERR_INVALID, "null argument");
+    int rc = fetch_stats(r);
+    if (rc != NRB_OK) return rc;
+    out[0] = static_cast<uint64_t>(r->lastLaunches);
+    out[1] = r->lastStats[0];
+    out[2] = r->lastStats[1];
+    out[3] = r->lastStats[2];
+    return NRB_OK;
+}
+
+}  // extern "C"
+
+// =================================================================================================
+// Parity/debug read-back and the batch entry points
+// =================================================================================================
+extern "C" {
+
+int nrb_read_buffer(nrb_renderer* r, const char* name, void* dst, size_t bytes) {
+    if (!r || !name || !dst) return fail(NRB_ERR_INVALID, "null argument");
+    if (!r->stateElems) return fail(NRB_ERR_STATE, "no frame has been rendered");
+    NRB_CUDA(cudaSetDevice(r->device));
+    NRB_CUDA(cudaStreamSynchronize(r->stream));
+    const std::string n(name);
+    const size_t elems = r->stateElems;
+    if (n == "accum") {
+        if (bytes != r->accum.bytes) return fail(NRB_ERR_SIZE, "buffer size mismatch for accum");
+        NRB_CUDA(cudaMemcpy(dst, r->accum.p, bytes, cudaMemcpyDeviceToHost));
+        return NRB_OK;
+    }
+    // element buffers are repacked on the host from the 16-byte records into the reference's
+    // triplet/scalar arrays (src/cuda_renderer_neural.h:160-214); debug path, not timed
+    const SurfRec& rec = r->st.rec[0];
+    const float4* src4 = nullptr;
+    const float2* src2 = nullptr;
+    int mode = 0;  // 0: xyz of src4; 1: w of src4 as float; 2: w of src4 as int; 3: (C.w, M.x, M.y)
+    if (n == "hit_positions") src4 = rec.P;
+    else if (n == "hit_normals") src4 = rec.N;
+    else if (n == "hit_colors") src4 = rec.C;
+    else if (n == "path_radiance") src4 = r->st.L;
+    else if (n == "hit_distances") { src4 = rec.N; mode = 1; }
+    else if (n == "hit_flags") { src4 = rec.P; mode = 2; }
+    else if (n == "hit_material_params") { src4 = rec.C; src2 = rec.M; mode = 3; }
+    else return fail(NRB_ERR_INVALID, "unknown buffer " + n);
+    const size_t per = (mode == 1 || mode == 2) ? 1 : 3;
+    if (bytes != elems * per * 4) return fail(NRB_ERR_SIZE, "buffer size mismatch for " + n);
+    std::vector<float4> h4(elems);
+    NRB_CUDA(cudaMemcpy(h4.data(), src4, elems * sizeof(float4), cudaMemcpyDeviceToHost));
+    std::vector<float2> h2;
+    if (src2) {
+        h2.resize(elems);
+        NRB_CUDA(cudaMemcpy(h2.data(), src2, elems * sizeof(float2), cudaMemcpyDeviceToHost));
+    }
+    float* out = static_cast<float*>(dst);
+    for (size_t i = 0; i < elems; ++i) {
+        switch (mode) {
+            case 0: out[3 * i] = h4[i].x; out[3 * i + 1] = h4[i].y; out[3 * i + 2] = h4[i].z; break;
+            case 1: out[i] = h4[i].w; break;
+            case 2: std::memcpy(&out[i], &h4[i].w, 4); break;
+            default: out[3 * i] = h4[i].w; out[3 * i + 1] = h2[i].x; out[3 * i + 2] = h2[i].y; break;
+        }
+    }
+    return NRB_OK;
+}
+
+int nrb_trace_rays(nrb_renderer* r, int slot, int mode, const float* d_origins, const float* d_directions, size_t n,
+                   nrb_hit* d_out) {
+    if (!r || slot < 0 || slot >= NRB_MESH_SLOT_COUNT || mode < 0 || mode > 2) return fail(NRB_ERR_INVALID, "bad argument");
+    if (n >= (1ull << 31)) return fail(NRB_ERR_INVALID, "too many rays for one call");
+    NRB_CUDA(cudaSetDevice(r->device));
+    if (!r->scratchC.p) {
+        NRB_CUDA(r->scratchC.alloc(16 * sizeof(unsigned long long)));
+    }
+    NRB_CUDA(cudaMemsetAsync(r->scratchC.p, 0, r->scratchC.bytes, r->stream));
+    launch_trace_rays(r->mesh[slot].view, mode, d_origins, d_directions, n, reinterpret_cast<Hit*>(d_out),
+                      r->scratchC.as<unsigned long long>(), r->stream);
+    NRB_CUDA(cudaGetLastError());
+    return NRB_OK;
+}
+
+int nrb_trace_rays_host(nrb_renderer* r, int slot, int mode, const float* origins, const float* directions, size_t n,
+                        nrb_hit* out) {
+    if (!r || !origins || !directions || !out) return fail(NRB_ERR_INVALID, "null argument");
+    if (n == 0) return NRB_OK;
+    NRB_CUDA(cudaSetDevice(r->device));
+    DevBuf o, d, h;
+    NRB_CUDA(o.alloc(n * 12)); NRB_CUDA(d.alloc(n * 12)); NRB_CUDA(h.alloc(n * sizeof(nrb_hit)));
+    NRB_CUDA(cudaMemcpyAsync(o.p, origins, n * 12, cudaMemcpyHostToDevice, r->stream));
+    NRB_CUDA(cudaMemcpyAsync(d.p, directions, n * 12, cudaMemcpyHostToDevice, r->stream));
+    int rc = nrb_trace_rays(r, slot, mode, o.as<float>(), d.as<float>(), n, h.as<nrb_hit>());
+    if (rc != NRB_OK) return rc;
+    NRB_CUDA(cudaMemcpyAsync(out, h.p, n * sizeof(nrb_hit), cudaMemcpyDeviceToHost, r->stream));
+    NRB_CUDA(cudaStreamSynchronize(r->stream));
+    NRB_CUDA(cudaMemcpy(r->lastStats, r->scratchC.p, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    return NRB_OK;
+}
+
+int nrb_neural_query(nrb_renderer* r, const float* d_inputs, size_t n, void* d_outputs_fp16) {
+    if (!r || !d_inputs || !d_outputs_fp16) return fail(NRB_ERR_INVALID, "null argument");
+    if (!r->weightsLoaded) return fail(NRB_ERR_STATE, "no weights loaded");
+    if (n >= (1ull << 31)) return fail(NRB_ERR_INVALID, "too many queries for one call");
+    NRB_CUDA(cudaSetDevice(r->device));
+    if (launch_neural_query(r->net, d_inputs, n, nullptr, static_cast<__half*>(d_outputs_fp16), r->stream) < 0)
+        return fail(NRB_ERR_INVALID, "unsupported network shape");
+    NRB_CUDA(cudaGetLastError());
+    return NRB_OK;
+}
+
+int nrb_neural_query_host(nrb_renderer* r, const float* inputs, size_t n, void* outputs_fp16) {
+    if (!r || !inputs || !outputs_fp16) return fail(NRB_ERR_INVALID, "null argument");
+    if (n == 0) return NRB_OK;
+    NRB_CUDA(cudaSetDevice(r->device));
+    const size_t inBytes = n * r->net.inputDims * sizeof(float), outBytes = n * 16 * sizeof(__half);
+    if (r->scratchA.bytes < inBytes) NRB_CUDA(r->scratchA.alloc(inBytes));
+    if (r->scratchB.bytes < outBytes) NRB_CUDA(r->scratchB.alloc(outBytes));
+    NRB_CUDA(cudaMemcpyAsync(r->scratchA.p, inputs, inBytes, cudaMemcpyHostToDevice, r->stream));
+    int rc = nrb_neural_query(r, r->scratchA.as<float>(), n, r->scratchB.p);
+    if (rc != NRB_OK) return rc;
+    NRB_CUDA(cudaMemcpyAsync(outputs_fp16, r->scratchB.p, outBytes, cudaMemcpyDeviceToHost, r->stream));
+    NRB_CUDA(cudaStreamSynchronize(r->stream));
+    return NRB_OK;
+}
+
+}  // extern "C"

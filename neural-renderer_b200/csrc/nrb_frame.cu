@@ -1,0 +1,177 @@
+// nrb_frame.cu — frame kernels of the ground-truth (classic mesh) path and the shared shading
+// stages.  Compiled with -fmad=false (see nrb_math.cuh).
+//
+// Reference kernels covered here (src/cuda_renderer_neural.cu):
+//   intersectGroundTruthKernel :244-296 + initializePathStateKernel :303-354  -> k_gt_primary
+//   sampleBounceDirectionsKernel :357-499 + traceGroundTruthBouncesKernel :556-618
+//     + integrateBounceKernel :621-675                                        -> k_gt_bounce
+//   finalizePathTracingKernel :678-709                                        -> k_finalize
+//   lambertKernel :1547-1607                                                  -> k_lambert
+// The reference launches each over all W*H*spp elements and stores every intermediate; here one
+// bounce is ONE kernel over the compacted queue of live paths, with the sampled direction, BRDF
+// weight and pdf living in registers only.
+#include "nrb_frame_dev.cuh"
+
+namespace nrb {
+
+// ---------------------------------------------------------------------------------------------
+
+__global__ void __launch_bounds__(kTileThreads) k_gt_primary(const __grid_constant__ Frame f) {
+    const FrameParams& fp = f.fp;
+    const ElemId id = tile_elem(fp);
+    bool active = false;
+    if (id.valid) {
+        uint32_t rng = rng_seed(id.pixel, fp.sampleOffset, id.s);
+        const V3 dir = primary_direction(fp, id.x, id.gy, rng);
+        V3 pos = v3s(0.0f), nrm = v3s(0.0f), alb = v3s(0.0f), mp;
+        const bool hit = hit_record<TRACE_FORWARD>(f, f.classicSlot, fp.camPos, dir, pos, nrm, alb, mp);
+        rec_store(f.st.rec[0], id.e, pos, hit ? 1 : 0, nrm, 0.0f, alb, mp);
+        V3 L = v3s(0.0f);
+        if (!hit) L = fp.useDirectEnvColor ? fp.directEnvColor : env_clamped(f.env, dir, fp.maxRadiance);
+        f.st.T[id.e] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+        f.st.L[id.e] = make_float4(L.x, L.y, L.z, 0.0f);
+        active = hit && fp.maxBounces > 0;
+    }
+    queue_push(f.st.queue[0], f.st.counts + 0, active, id.e);
+    stat_flush(f.st.stats + 0, id.valid ? 1u : 0u);
+}
+
+__global__ void __launch_bounds__(kQueueThreads) k_gt_bounce(const __grid_constant__ Frame f, int bounce, int qin,
+                                                             int qout) {
+    const FrameParams& fp = f.fp;
+    const int n = f.st.counts[qin];
+    const int nWarpRounded = (n + 31) & ~31;
+    const SurfRec& cur = f.st.rec[bounce == 1 ? 0 : 1];
+    const SurfRec& nxt = f.st.rec[1];
+    unsigned int nTrace = 0, nVert = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nWarpRounded; i += gridDim.x * blockDim.x) {
+        bool alive = false;
+        int e = 0;
+        if (i < n) {
+            e = f.st.queue[qin][i];
+            const ElemId id = queue_elem(fp, e);
+            const float4 P = cur.P[e], N = cur.N[e], C = cur.C[e];
+            const float2 M = cur.M[e];
+            V3 org, wi, weight;
+            float pdf;
+            const V3 prev = bounce == 1 ? v3s(0.0f) : f4v(f.st.prevD[e]);
+            ++nVert;
+            if (sample_vertex(f, id, f4v(P), f4v(N), f4v(C), v3(C.w, M.x, M.y), bounce == 1, prev, org, wi, weight,
+                              pdf)) {
+                V3 pos, nrm, alb, mp;
+                const bool hit = hit_record<TRACE_ANY>(f, f.classicSlot, org, wi, pos, nrm, alb, mp);
+                ++nTrace;
+                V3 T = f4v(f.st.T[e]), L = v3s(0.0f);
+                bool touchedL;
+                if (!hit) L = f4v(f.st.L[e]);
+                alive = integrate_vertex(f, id, bounce, hit, wi, weight, T, L, touchedL);
+                if (touchedL) f.st.L[e] = make_float4(L.x, L.y, L.z, 0.0f);
+                if (alive) {
+                    rec_store(nxt, e, pos, 1, nrm, 0.0f, alb, mp);
+                    f.st.T[e] = make_float4(T.x, T.y, T.z, 0.0f);
+                    f.st.prevD[e] = make_float4(wi.x, wi.y, wi.z, 0.0f);
+                }
+            }
+        }
+        queue_push(f.st.queue[qout], f.st.counts + qout, alive, e);
+    }
+    stat_flush(f.st.stats + 0, nTrace);
+    stat_flush(f.st.stats + 2, nVert);
+}
+
+__global__ void __launch_bounds__(256) k_finalize(const __grid_constant__ Frame f) {
+    const FrameParams& fp = f.fp;
+    const int lp = blockIdx.x * blockDim.x + threadIdx.x;
+    if (lp >= fp.localPixels) return;
+    V3 sum = v3s(0.0f);
+    for (int s = 0; s < fp.spp; ++s) sum = sum + f4v(f.st.L[lp + s * fp.localPixels]);
+    float* a = f.st.accum + 3 * static_cast<size_t>(lp);
+    const V3 acc = v3(a[0], a[1], a[2]) + sum;
+    a[0] = acc.x; a[1] = acc.y; a[2] = acc.z;
+    const float inv = 1.0f / static_cast<float>(fp.sampleOffset + static_cast<uint32_t>(fp.spp));
+    const int ly = lp / fp.width, x = lp - ly * fp.width;
+    f.st.pixels[global_row(fp, ly) * fp.width + x] = to_srgb8(acc * inv);
+}
+
+__global__ void __launch_bounds__(256) k_lambert(const __grid_constant__ Frame f) {
+    const FrameParams& fp = f.fp;
+    const int lp = blockIdx.x * blockDim.x + threadIdx.x;
+    if (lp >= fp.localPixels) return;
+    const int ly = lp / fp.width, x = lp - ly * fp.width;
+    const int gy = global_row(fp, ly), pixel = gy * fp.width + x;
+    V3 sum = v3s(0.0f);
+    for (int s = 0; s < fp.spp; ++s) {
+        const int e = lp + s * fp.localPixels;
+        uint32_t rng = rng_seed(pixel, fp.sampleOffset, s);
+        const V3 dir = primary_direction(fp, x, gy, rng);
+        const float4 P = f.st.rec[0].P[e];
+        V3 c;
+        if (__float_as_int(P.w)) {
+            V3 n = f4v(f.st.rec[0].N[e]);
+            const float nl = length(n);
+            n = nl > 0.0f ? n / nl : v3(0.0f, 1.0f, 0.0f);
+            if (dot(n, dir) > 0.0f) n = n * -1.0f;
+            c = f4v(f.st.rec[0].C[e]) * fmaxf(0.0f, dot(n, -dir));
+        } else {
+            c = env_lookup(f.env, dir);
+        }
+        sum = sum + c;
+    }
+    f.st.pixels[pixel] = to_srgb8(sum * (1.0f / static_cast<float>(fp.spp)));
+}
+
+// traceMeshWithMode on caller rays (the batch entry point nrb_trace_rays).
+__global__ void __launch_bounds__(128) k_trace_rays(const __grid_constant__ MeshDev m, int mode, const float* o,
+                                                    const float* d, size_t n, Hit* out, unsigned long long* stats) {
+    const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    TraceStats st{0u, 0u};
+    if (i < n) {
+        Hit h = trace_mode<true>(m, mode, ld3(o, static_cast<uint32_t>(i)), ld3(d, static_cast<uint32_t>(i)), &st);
+        if (h.t >= 1e30f) h = Hit{1e30f, 0.0f, 0.0f, 0u};
+        out[i] = h;
+    }
+    if (stats) {
+        stat_flush(stats + 3, st.pairs);
+        stat_flush(stats + 4, st.tris);
+        stat_flush(stats + 0, i < n ? 1u : 0u);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+
+void launch_trace_rays(const MeshDev& m, int mode, const float* o, const float* d, size_t n, Hit* out,
+                       unsigned long long* stats, cudaStream_t s) {
+    if (n == 0) return;
+    k_trace_rays<<<static_cast<unsigned>((n + 127) / 128), 128, 0, s>>>(m, mode, o, d, n, out, stats);
+}
+
+int launch_finalize(const Frame& f, cudaStream_t s) {
+    k_finalize<<<(f.fp.localPixels + 255) / 256, 256, 0, s>>>(f);
+    return 1;
+}
+
+int launch_lambert(const Frame& f, cudaStream_t s) {
+    k_lambert<<<(f.fp.localPixels + 255) / 256, 256, 0, s>>>(f);
+    return 1;
+}
+
+int launch_gt_frame(const Frame& f, bool lambert, cudaStream_t s) {
+    const FrameParams& fp = f.fp;
+    int launches = 0;
+    cudaMemsetAsync(f.st.counts, 0, 16 * sizeof(int), s);
+    const dim3 grid((fp.width + 31) / 32, (fp.localHeight + 3) / 4, fp.spp);
+    k_gt_primary<<<grid, kTileThreads, 0, s>>>(f);
+    ++launches;
+    if (lambert) return launches + launch_lambert(f, s);
+    int qin = 0;
+    for (int b = 1; b <= fp.maxBounces; ++b) {
+        const int qout = qin ^ 1;
+        cudaMemsetAsync(f.st.counts + qout, 0, sizeof(int), s);
+        k_gt_bounce<<<queue_grid(fp.nElems), kQueueThreads, 0, s>>>(f, b, qin, qout);
+        ++launches;
+        qin = qout;
+    }
+    return launches + launch_finalize(f, s);
+}
+
+}  // namespace nrb

@@ -1,0 +1,29 @@
+// nrb_frame.cuh — the kernel-argument block shared by all frame kernels and their launchers.
+#pragma once
+
+#include "nrb_state.cuh"
+
+namespace nrb {
+
+// Passed by value as a __grid_constant__ kernel parameter (lives in the constant bank; the
+// reference passes RenderParams + MeshDeviceView + a dozen pointers the same way).
+struct Frame {
+    FrameParams fp;
+    MeshDev mesh[4];
+    EnvDev env;
+    MaterialDev gmat;
+    State st;
+    int classicSlot;
+    int additionalEnabled;
+};
+
+// Launchers implemented in nrb_frame.cu / nrb_neural.cu (all enqueue on `s`, none synchronises).
+struct NetDev;
+void launch_trace_rays(const MeshDev& m, int mode, const float* o, const float* d, size_t n, Hit* out,
+                       unsigned long long* stats, cudaStream_t s);
+int launch_gt_frame(const Frame& f, bool lambert, cudaStream_t s);       // returns kernels launched
+int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStream_t s);
+int launch_finalize(const Frame& f, cudaStream_t s);
+int launch_lambert(const Frame& f, cudaStream_t s);
+
+}  // namespace nrb

@@ -1,0 +1,37 @@
+// nrb_neural.cuh — device description of the neural query network.
+//
+// Replaces tiny-cuda-nn's NetworkWithInputEncoding<__half> on this path (reference
+// src/cuda_renderer_neural.cu:1647-1702): Composite(n_points x HashGrid + SphericalHarmonics) ->
+// fully fused MLP (LeakyReLU 0.01, no biases, 16 padded outputs).  The reference tiles ONE grid
+// table into n_points identical copies (:1798-1804); here the table is stored once and shared.
+#pragma once
+
+#include <cuda_fp16.h>
+#include <stdint.h>
+
+namespace nrb {
+
+constexpr int kMaxLevels = 16;
+
+struct NetDev {
+    const __half* grid;   // [offsets[L]][F]
+    const __half* mlp;    // W0 [W][E] | W1..W(H-1) [W][W] | Wlast [16][W], row-major [out][in]
+    int nPoints, nLevels, nFeatures, shDegree, width, nHidden;
+    int inputDims;        // 3*nPoints (+3 when shDegree > 0)
+    int encDims;          // nPoints*nLevels*nFeatures + shDegree^2
+    uint32_t levelOffset[kMaxLevels];
+    uint32_t levelSize[kMaxLevels];     // hashmap_size of the level (entries)
+    uint32_t levelRes[kMaxLevels];
+    float levelScale[kMaxLevels];
+    uint8_t levelDense[kMaxLevels];     // res^3 <= size: linear index, else coherent-prime hash
+    uint8_t levelPow2[kMaxLevels];      // size is a power of two (mask instead of %)
+};
+
+// Enqueue the query for n rows: inputs fp32 [n][inputDims] (or, with dCount != nullptr, the row
+// count is read on the device from *dCount and n is only the launch bound), outputs fp16 [n][16].
+int launch_neural_query(const NetDev& net, const float* in, size_t n, const int* dCount, __half* out,
+                        cudaStream_t s);
+// Bytes of dynamic shared memory the query kernel needs for this network (0 = unsupported shape).
+size_t neural_query_smem(const NetDev& net, int* warpsOut);
+
+}  // namespace nrb

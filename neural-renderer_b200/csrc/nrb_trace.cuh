@@ -1,0 +1,239 @@
+// nrb_trace.cuh — closest-hit BVH traversal and hit-record construction.
+//
+// Same results as the reference's traceMeshWithMode (src/mesh_traversal.cuh:118-222) with a
+// different machine mapping: both child boxes come from one 64-byte NodePair (4 x LDG.128), the
+// near child is followed directly instead of being pushed and popped, the far child is pushed
+// together with its entry distance so the reference's "re-test the popped box against the
+// current best t" becomes a register compare, and candidate triangles are 3 x LDG.128
+// TriBlocks with the facing normal pre-computed.  The visit ORDER of triangles is the
+// reference's (near child first by the same rightNear < leftNear rule, leaf triangles
+// ascending), so ties in t resolve to the same primitive id.
+#pragma once
+
+#include "nrb_scene.cuh"
+
+namespace nrb {
+
+constexpr int kTraceStack = 64;       // checked against the tree depth at upload
+constexpr int kLeafCountBits = 5;     // leaf ref = ~((first << 5) | (count - 1))
+
+__host__ __device__ __forceinline__ int leaf_ref(int first, int count) {
+    return ~((first << kLeafCountBits) | (count - 1));
+}
+
+// intersectAabb, reference src/mesh_traversal.cuh:61-93 (same operations, same order).
+__device__ __forceinline__ bool slab(V3 o, V3 inv, float mnx, float mny, float mnz, float mxx, float mxy,
+                                     float mxz, float tMax, float& tNear) {
+    const float kPad = 1e-10f;
+    mnx -= kPad; mny -= kPad; mnz -= kPad;
+    mxx += kPad; mxy += kPad; mxz += kPad;
+    float t1 = (mnx - o.x) * inv.x, t2 = (mxx - o.x) * inv.x;
+    float tmin = fminf(t1, t2), tmax = fmaxf(t1, t2);
+    t1 = (mny - o.y) * inv.y; t2 = (mxy - o.y) * inv.y;
+    tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
+    t1 = (mnz - o.z) * inv.z; t2 = (mxz - o.z) * inv.z;
+    tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
+    tNear = tmin;
+    return !(tmax < 0.0f || tmin > tMax || tmin > tmax);
+}
+
+// Counters for the roofline's algorithmic bytes (node pairs fetched, triangles fetched).
+struct TraceStats {
+    unsigned int pairs, tris;
+};
+
+template <int MODE, bool STATS = false>
+__device__ __forceinline__ Hit trace_closest(const MeshDev& m, V3 o, V3 d, TraceStats* st = nullptr) {
+    Hit best{1e30f, 0.0f, 0.0f, 0u};
+    if (m.numTriangles <= 0) return best;
+    const V3 inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    float tn;
+    if (!slab(o, inv, m.rootMin[0], m.rootMin[1], m.rootMin[2], m.rootMax[0], m.rootMax[1], m.rootMax[2], best.t, tn))
+        return best;
+
+    int2 stack[kTraceStack];
+    int sp = 0;
+    int ref = m.rootRef;
+    const NodePair* __restrict__ nodes = m.nodes;
+    const TriBlock* __restrict__ tris = m.tris;
+
+    for (;;) {
+        if (ref >= 0) {
+            const float4 a = __ldg(&nodes[ref].a), b = __ldg(&nodes[ref].b), c = __ldg(&nodes[ref].c);
+            const int4 k = __ldg(&nodes[ref].d);
+            if (STATS) st->pairs++;
+            float ln, rn;
+            const bool hl = slab(o, inv, a.x, a.y, a.z, a.w, b.x, b.y, best.t, ln);
+            const bool hr = slab(o, inv, b.z, b.w, c.x, c.y, c.z, c.w, best.t, rn);
+            if (hl && hr) {
+                int nearRef = k.x, farRef = k.y;
+                float farT = rn;
+                if (rn < ln) { nearRef = k.y; farRef = k.x; farT = ln; }
+                if (sp < kTraceStack) stack[sp++] = make_int2(farRef, __float_as_int(farT));
+                ref = nearRef;
+                continue;
+            }
+            if (hl) { ref = k.x; continue; }
+            if (hr) { ref = k.y; continue; }
+        } else {
+            const int packed = ~ref;
+            const int first = packed >> kLeafCountBits;
+            const int end = first + (packed & ((1 << kLeafCountBits) - 1)) + 1;
+            for (int i = first; i < end; ++i) {
+                const float4 p = __ldg(&tris[i].p), q = __ldg(&tris[i].q), r = __ldg(&tris[i].r);
+                if (STATS) st->tris++;
+                if (MODE != TRACE_ANY) {
+                    const float facing = dot(v3(p.w, q.w, r.w), d);
+                    if (MODE == TRACE_FORWARD && facing >= 0.0f) continue;
+                    if (MODE == TRACE_BACKWARD && facing <= 0.0f) continue;
+                }
+                // intersectTriangleIndexed, reference src/mesh_intersection.cuh:15-46
+                const V3 e1 = v3(q.x, q.y, q.z), e2 = v3(r.x, r.y, r.z);
+                const V3 pv = cross(d, e2);
+                const float det = dot(e1, pv);
+                if (fabsf(det) < 1e-8f) continue;
+                const float invDet = 1.0f / det;
+                const V3 tv = o - v3(p.x, p.y, p.z);
+                const float u = dot(tv, pv) * invDet;
+                if (u < 0.0f || u > 1.0f) continue;
+                const V3 qv = cross(tv, e1);
+                const float v = dot(d, qv) * invDet;
+                if (v < 0.0f || u + v > 1.0f) continue;
+                const float t = dot(e2, qv) * invDet;
+                if (t <= 1e-8f) continue;
+                if (t > 1e-6f && t < best.t) best = Hit{t, u, v, static_cast<uint32_t>(i)};
+            }
+        }
+        // pop: skip entries whose box entry distance is now beyond the best hit
+        bool found = false;
+        while (sp > 0) {
+            const int2 e = stack[--sp];
+            if (__int_as_float(e.y) > best.t) continue;
+            ref = e.x;
+            found = true;
+            break;
+        }
+        if (!found) break;
+    }
+    return best;
+}
+
+template <bool STATS = false>
+__device__ __forceinline__ Hit trace_mode(const MeshDev& m, int mode, V3 o, V3 d, TraceStats* st = nullptr) {
+    if (mode == TRACE_FORWARD) return trace_closest<TRACE_FORWARD, STATS>(m, o, d, st);
+    if (mode == TRACE_BACKWARD) return trace_closest<TRACE_BACKWARD, STATS>(m, o, d, st);
+    return trace_closest<TRACE_ANY, STATS>(m, o, d, st);
+}
+
+// ---- hit record (computeHitData, reference src/mesh_intersection.cuh:168-238) -----------------
+
+struct Surface {
+    V3 position, normal;  // shading normal
+    V2 uv;
+    int materialId;
+};
+
+// sampleTextureRawDev, reference src/mesh_intersection.cuh:109-152 (8-bit texels, wrap, bilinear
+// over (w-1) or nearest).  Returns x < 0 when the texture is unusable.
+__device__ inline V3 tex_sample(const TexDev& t, float u, float v, bool nearest) {
+    if (!t.pixels || t.width <= 0 || t.height <= 0 || t.channels <= 0) return v3(-1.0f, -1.0f, -1.0f);
+    u = u - floorf(u);
+    v = v - floorf(v);
+    auto texel = [&](int xi, int yi) {
+        const unsigned char* px = t.pixels + (yi * t.width + xi) * t.channels;
+        const float k = 1.0f / 255.0f;
+        return v3(px[0] * k, t.channels > 1 ? px[1] * k : 0.0f, t.channels > 2 ? px[2] * k : 0.0f);
+    };
+    if (nearest) {
+        int x = static_cast<int>(u * static_cast<float>(t.width));
+        int y = static_cast<int>(v * static_cast<float>(t.height));
+        x = max(0, min(x, t.width - 1));
+        y = max(0, min(y, t.height - 1));
+        return texel(x, y);
+    }
+    const float x = u * static_cast<float>(t.width - 1), y = v * static_cast<float>(t.height - 1);
+    const int x0 = static_cast<int>(floorf(x)), y0 = static_cast<int>(floorf(y));
+    const int x1 = min(x0 + 1, t.width - 1), y1 = min(y0 + 1, t.height - 1);
+    const float tx = x - static_cast<float>(x0), ty = y - static_cast<float>(y0);
+    const V3 top = mix3(texel(x0, y0), texel(x1, y0), tx);
+    const V3 bot = mix3(texel(x0, y1), texel(x1, y1), tx);
+    return mix3(top, bot, ty);
+}
+
+// getMaterialIdForTriangle, reference src/mesh_intersection.cuh:53-85.
+__device__ inline int material_of(const MeshDev& m, uint32_t tri) {
+    if (!m.hasMeshMaterials || m.numPrimitives <= 0) return -1;
+    uint32_t lo = 0, hi = static_cast<uint32_t>(m.numPrimitives);
+    if (m.materialMap) {
+        while (lo < hi) {
+            const uint32_t mid = lo + (hi - lo) / 2;
+            if (m.materialMap[mid] <= tri) lo = mid + 1; else hi = mid;
+        }
+    } else {
+        lo = 0;
+    }
+    const uint32_t prim = lo > 0 ? lo - 1 : 0;
+    if (prim < static_cast<uint32_t>(m.numPrimitives) && m.materialIds) return m.materialIds[prim];
+    return -1;
+}
+
+__device__ inline Surface surface_at(const MeshDev& m, const Hit& h) {
+    Surface s;
+    const uint32_t i0 = m.indices[3 * h.prim], i1 = m.indices[3 * h.prim + 1], i2 = m.indices[3 * h.prim + 2];
+    const float w = 1.0f - h.u - h.v;
+    const TriBlock& tb = m.tris[h.prim];
+    const V3 geo = v3(tb.p.w, tb.q.w, tb.r.w);
+    s.normal = m.normals ? normalize(ld3(m.normals, i0) * w + ld3(m.normals, i1) * h.u + ld3(m.normals, i2) * h.v) : geo;
+    s.position = ld3(m.vertices, i0) * w + ld3(m.vertices, i1) * h.u + ld3(m.vertices, i2) * h.v;
+    if (m.texcoords) {
+        const float* t = m.texcoords;
+        s.uv.x = t[2 * i0] * w + t[2 * i1] * h.u + t[2 * i2] * h.v;
+        s.uv.y = t[2 * i0 + 1] * w + t[2 * i1 + 1] * h.u + t[2 * i2 + 1] * h.v;
+    } else {
+        s.uv = V2{h.u, h.v};
+    }
+    s.materialId = material_of(m, h.prim);
+    if (s.materialId >= 0 && s.materialId < m.numMaterials && m.materials) {
+        const MaterialDev& mat = m.materials[s.materialId];
+        if (mat.normal.textured && mat.normal.tex < static_cast<uint32_t>(m.numTextures)) {
+            const V3 tn = tex_sample(m.textures[mat.normal.tex], s.uv.x, s.uv.y, m.textureNearest != 0);
+            if (tn.x >= 0.0f) {
+                const V3 ts = normalize(tn * 2.0f - v3s(1.0f));
+                // orthoBasis, reference src/mesh_intersection.cuh:91-103
+                V3 bt = v3s(0.0f);
+                if (fabsf(s.normal.x) < 0.6f) bt.x = 1.0f;
+                else if (fabsf(s.normal.y) < 0.6f) bt.y = 1.0f;
+                else bt.z = 1.0f;
+                const V3 tg = normalize(cross(bt, s.normal));
+                bt = normalize(cross(s.normal, tg));
+                s.normal = normalize(tg * ts.x + bt * ts.y + s.normal * ts.z);
+            }
+        }
+    }
+    return s;
+}
+
+// resolveMaterial restricted to what the kernels consume (albedo, metallic, roughness, specular):
+// reference src/mesh_intersection.cuh:244-337 and the block at cuda_renderer_neural.cu:218-229.
+__device__ inline float mat_scalar(const MatParam& p, V2 uv, const MeshDev& m) {
+    if (!p.textured) return p.value;
+    if (p.tex >= static_cast<uint32_t>(m.numTextures) || !m.textures) return p.value;
+    const V3 s = tex_sample(m.textures[p.tex], uv.x, uv.y, m.textureNearest != 0);
+    if (s.x < 0.0f) return p.value;
+    return p.channel == 1 ? s.y : (p.channel == 2 ? s.z : s.x);
+}
+
+__device__ inline void resolve_surface_material(const MeshDev& m, const Surface& s, const MaterialDev& global,
+                                                V3& albedo, V3& mparams) {
+    const MaterialDev* mat = &global;
+    if (s.materialId >= 0 && s.materialId < m.numMaterials && m.materials) mat = &m.materials[s.materialId];
+    albedo = v3(mat->base_color.value[0], mat->base_color.value[1], mat->base_color.value[2]);
+    if (mat->base_color.textured && mat->base_color.tex < static_cast<uint32_t>(m.numTextures) && m.textures) {
+        const V3 raw = tex_sample(m.textures[mat->base_color.tex], s.uv.x, s.uv.y, m.textureNearest != 0);
+        if (raw.x >= 0.0f) albedo = raw;  // (the reference's sRGB->linear step is commented out)
+    }
+    mparams = v3(mat_scalar(mat->metallic, s.uv, m), mat_scalar(mat->roughness, s.uv, m),
+                 mat_scalar(mat->specular, s.uv, m));
+}
+
+}  // namespace nrb

@@ -141,3 +141,84 @@ def make_weights(seed: int = 42, grid_range: float = 0.5, out_bias_hit: float = 
     mlp = np.concatenate([m.reshape(-1) for m in mats]).astype(np.float16)
     assert len(mlp) == nm
     return np.concatenate([grid, mlp])
+
+
+# ---- scene assembly ---------------------------------------------------------------------------------
+
+def build_bvh(vertices, indices):
+    """nrb_build_bvh (host SAH builder of libnrb200): -> (nodes, leaf-ordered indices, prim ids)."""
+    import ctypes as C
+    from . import _capi as K
+    lib = K.product_lib()
+    v = np.ascontiguousarray(vertices, np.float32)
+    idx = np.ascontiguousarray(indices, np.uint32).copy()
+    nodes = np.zeros(2 * len(idx), K.BVH_NODE_DTYPE)
+    prim = np.zeros(len(idx), np.uint32)
+    n = C.c_int(0)
+    rc = lib.fn("build_bvh")(v.ctypes.data, len(v), idx.ctypes.data, len(idx), nodes.ctypes.data, C.byref(n),
+                             prim.ctypes.data)
+    if rc != 0:
+        raise K.NrbError(f"nrb_build_bvh failed ({rc})")
+    return nodes[: n.value].copy(), idx, prim
+
+
+def mesh_from(vertices, indices, normals=None, texcoords=None, **kw):
+    from .renderer import MeshData
+    nodes, idx, _ = build_bvh(vertices, indices)
+    return MeshData(vertices=vertices, indices=idx, nodes=nodes, normals=normals, texcoords=texcoords, **kw)
+
+
+def checker_texture(size: int = 64, seed: int = 3):
+    rng = np.random.RandomState(seed)
+    y, x = np.mgrid[0:size, 0:size]
+    base = (((x // 8) + (y // 8)) % 2).astype(np.float32)
+    img = np.stack([0.25 + 0.6 * base, 0.3 + 0.4 * (1 - base), 0.35 + 0.3 * base], -1)
+    img = img + 0.05 * rng.standard_normal(img.shape)
+    return np.clip(img * 255.0, 0, 255).astype(np.uint8)
+
+
+def make_scene(kind: str = "ico", subdivisions: int = 4, shells: bool = True, env: bool = True,
+               additional: bool = False, shell_delta: float = 0.12, textured: bool = False,
+               env_size=(512, 256), roughness: float = 0.5, metallic: float = 0.0, specular: float = 0.5):
+    """Synthetic scene in the reference's Scene layout: a displaced icosphere (or the
+    reference's UV sphere) as original mesh, +-shell_delta icosphere hulls as inner/outer shells, an
+    optional ground quad as the additional mesh and a seeded equirect environment."""
+    from . import _capi as K
+    from .renderer import Scene
+    if kind == "sphere":
+        v, n, uv, idx = uv_sphere(48, 96, 1.0)
+    elif kind == "sphere_small":
+        v, n, uv, idx = uv_sphere(12, 24, 1.0)
+    else:
+        v0, idx = icosphere(subdivisions)
+        v = displace(v0, 0.1)
+        n = vertex_normals(v, idx)
+        uv = np.stack([np.arctan2(v0[:, 0], v0[:, 2]) / (2 * np.pi) + 0.5, np.arccos(np.clip(v0[:, 1], -1, 1)) / np.pi],
+                      -1).astype(np.float32)
+    extra = {}
+    if textured:
+        m = K.Material.from_config(base_color=(0.8, 0.8, 0.8), roughness=roughness, metallic=metallic, specular=specular)
+        m.base_color.textured = 1
+        m.base_color.texture_id = 0
+        extra = dict(materials=[m], material_map=np.array([0], np.uint32), material_ids=np.array([0], np.int32),
+                     textures=[(checker_texture(), False)], has_mesh_materials=True)
+    scene = Scene(original_mesh=mesh_from(v, idx, normals=n, texcoords=uv, **extra))
+    if shells:
+        hv, hidx = icosphere(3)
+        scene.inner_shell = mesh_from((hv * np.float32(1.0 - shell_delta)).astype(np.float32), hidx)
+        scene.outer_shell = mesh_from((hv * np.float32(1.0 + shell_delta)).astype(np.float32), hidx)
+    if additional:
+        gv, gidx = ground_quad()
+        scene.additional_mesh = mesh_from(gv, gidx)
+    if env:
+        scene.env_pixels = sky_env(*env_size)
+    scene.global_material = K.Material.from_config(base_color=(0.8, 0.8, 0.8), roughness=roughness, metallic=metallic,
+                                                   specular=specular)
+    return scene
+
+
+def default_camera(radius: float = 1.0, fov_y: float = 0.785):
+    """Look-at camera of SURVEY.md §8d: eye (2.0, 1.2, 2.0) * r toward the origin."""
+    from .renderer import look_at_basis
+    eye = np.array([2.0, 1.2, 2.0], np.float32) * np.float32(radius)
+    return eye, look_at_basis(eye, (0.0, 0.0, 0.0), fov_y)
