@@ -12,6 +12,9 @@
 // weight and pdf living in registers only.
 #include "nrb_frame_dev.cuh"
 
+#include <cstdio>
+#include <cstdlib>
+
 namespace nrb {
 
 // ---------------------------------------------------------------------------------------------
@@ -139,19 +142,30 @@ __global__ void __launch_bounds__(128) k_trace_rays(const __grid_constant__ Mesh
 
 // ---------------------------------------------------------------------------------------------
 
+void debug_check(const char* what, cudaStream_t s) {
+    static const bool on = getenv("NRB_DEBUG") != nullptr;
+    if (!on) return;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    fprintf(stderr, "[nrb] %s: %s\n", what, cudaGetErrorString(e));
+}
+
 void launch_trace_rays(const MeshDev& m, int mode, const float* o, const float* d, size_t n, Hit* out,
                        unsigned long long* stats, cudaStream_t s) {
     if (n == 0) return;
     k_trace_rays<<<static_cast<unsigned>((n + 127) / 128), 128, 0, s>>>(m, mode, o, d, n, out, stats);
+    NRB_LAUNCHED("k_trace_rays", s);
 }
 
 int launch_finalize(const Frame& f, cudaStream_t s) {
     k_finalize<<<(f.fp.localPixels + 255) / 256, 256, 0, s>>>(f);
+    NRB_LAUNCHED("k_finalize", s);
     return 1;
 }
 
 int launch_lambert(const Frame& f, cudaStream_t s) {
     k_lambert<<<(f.fp.localPixels + 255) / 256, 256, 0, s>>>(f);
+    NRB_LAUNCHED("k_lambert", s);
     return 1;
 }
 
@@ -161,6 +175,7 @@ int launch_gt_frame(const Frame& f, bool lambert, cudaStream_t s) {
     cudaMemsetAsync(f.st.counts, 0, 16 * sizeof(int), s);
     const dim3 grid((fp.width + 31) / 32, (fp.localHeight + 3) / 4, fp.spp);
     k_gt_primary<<<grid, kTileThreads, 0, s>>>(f);
+    NRB_LAUNCHED("k_gt_primary", s);
     ++launches;
     if (lambert) return launches + launch_lambert(f, s);
     int qin = 0;
@@ -168,6 +183,7 @@ int launch_gt_frame(const Frame& f, bool lambert, cudaStream_t s) {
         const int qout = qin ^ 1;
         cudaMemsetAsync(f.st.counts + qout, 0, sizeof(int), s);
         k_gt_bounce<<<queue_grid(fp.nElems), kQueueThreads, 0, s>>>(f, b, qin, qout);
+        NRB_LAUNCHED("k_gt_bounce", s);
         ++launches;
         qin = qout;
     }

@@ -17,6 +17,10 @@ struct Frame {
     int additionalEnabled;
 };
 
+// Debug aid: with NRB_DEBUG=1 in the environment every launch is followed by a synchronise + report.
+void debug_check(const char* what, cudaStream_t s);
+#define NRB_LAUNCHED(what, s) ::nrb::debug_check(what, s)
+
 // Launchers implemented in nrb_frame.cu / nrb_neural.cu (all enqueue on `s`, none synchronises).
 struct NetDev;
 void launch_trace_rays(const MeshDev& m, int mode, const float* o, const float* d, size_t n, Hit* out,

@@ -308,9 +308,11 @@ static int run_segments(const Frame& f, const NetDev& net, int recIdx, cudaStrea
         const int qout = qin == 2 ? 3 : 2;
         cudaMemsetAsync(f.st.counts + qout, 0, sizeof(int), s);
         k_seg_exits<<<grid, kQueueThreads, 0, s>>>(f, qin);
+        NRB_LAUNCHED("k_seg_exits", s);
         launches += 1 + launch_neural_query(net, f.st.netIn, static_cast<size_t>(f.fp.nElems), f.st.counts + qin,
                                             f.st.netOut, s);
         k_seg_apply<<<grid, kQueueThreads, 0, s>>>(f, qin, qout, recIdx);
+        NRB_LAUNCHED("k_seg_apply", s);
         ++launches;
         qin = qout;
     }
@@ -323,9 +325,11 @@ int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStr
     cudaMemsetAsync(f.st.counts, 0, 16 * sizeof(int), s);
     const dim3 tiles((fp.width + 31) / 32, (fp.localHeight + 3) / 4, fp.spp);
     k_entry_camera<<<tiles, kTileThreads, 0, s>>>(f);
+    NRB_LAUNCHED("k_entry_camera", s);
     ++launches;
     launches += run_segments(f, net, 0, s);
     k_primary_finish<<<tiles, kTileThreads, 0, s>>>(f);
+    NRB_LAUNCHED("k_primary_finish", s);
     ++launches;
     if (lambert) return launches + launch_lambert(f, s);
     const int grid = queue_grid(fp.nElems);
@@ -333,10 +337,12 @@ int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStr
         // path queue 0 -> ray queue 1 (+ segment queue 2) -> path queue 0
         cudaMemsetAsync(f.st.counts + 1, 0, 3 * sizeof(int), s);
         k_bounce_begin<<<grid, kQueueThreads, 0, s>>>(f, b, 0, 1);
+        NRB_LAUNCHED("k_bounce_begin", s);
         ++launches;
         launches += run_segments(f, net, 1, s);
         cudaMemsetAsync(f.st.counts + 0, 0, sizeof(int), s);
         k_bounce_finish<<<grid, kQueueThreads, 0, s>>>(f, b, 1, 0);
+        NRB_LAUNCHED("k_bounce_finish", s);
         ++launches;
     }
     return launches + launch_finalize(f, s);
