@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""bench.py — neural-render Mrays/s at 1080p (BASELINE.json metric) for libnrb200 on N B200s.
+
+One "step" = one RendererNeural::render() call = one frame of the hot path (ray generation, shell
+BVH traversal, neural query on the shell segments, Disney-BRDF bounces, accumulation + sRGB) over
+W*H*spp camera paths; Mrays/s = W*H*spp / frame time (the reference's KernelTimings.rayCount
+convention, src/cuda_renderer_neural.cu:2741).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+                  [--mode neural|gt] [--width 1920 --height 1080 --spp 1 --bounces 3 --subdiv 7]
+
+JSON keys: value = device-timed, scene and state resident in HBM; e2e = the same metric through the
+public host API including the per-step host->device parameter upload and the device->host read of
+the frame; roofline = dominant kernel from per-launch CUDA events (second pass of the same K steps
+with NRB_OPT_PROFILE); cpu_baseline = the CPU oracle timed on the host cores on a bounded sample.
+--impl reference times the reference's own CPU code for this path (oracle/_ref when present, else the
+restatement) on all host cores.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+FLOPS_PER_QUERY = 2 * (112 * 128 + 3 * 128 * 128 + 128 * 16)  # 131072 for the reference network
+HBM_BYTES_PER_QUERY = 36 + 16
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="nrb200", choices=["nrb200", "reference"])
+    ap.add_argument("--mode", default="neural", choices=["neural", "gt"])
+    ap.add_argument("--width", type=int, default=1920)
+    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--spp", type=int, default=1)
+    ap.add_argument("--bounces", type=int, default=3)
+    ap.add_argument("--subdiv", type=int, default=7)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sustained=d["bf16_tflops_sustained"], src="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, src="fallback")
+
+
+def workload_name(a):
+    net = "3xHashGrid(L8,F4,T2^14)+SH4->112->128x4->16"
+    if a.mode == "neural":
+        return f"neural render {a.width}x{a.height} spp{a.spp} bounces{a.bounces}, displaced icosphere 20*4^{a.subdiv} tris in +-12% shells, {net}"
+    return f"ground-truth BVH path trace {a.width}x{a.height} spp{a.spp} bounces{a.bounces}, displaced icosphere 20*4^{a.subdiv} tris"
+
+
+def build_scene(nrb, a):
+    return nrb.scenes.make_scene("ico", a.subdiv, shells=True, env=True, env_size=(2048, 1024))
+
+
+def setup(nrb, a, scene, lib=None):
+    r = nrb.RendererNeural(scene, lib=lib)
+    eye, basis = nrb.scenes.default_camera()
+    r.resize(a.width, a.height)
+    r.set_camera_basis(basis)
+    r.set_samples_per_pixel(a.spp)
+    r.set_bounce_count(a.bounces)
+    if a.mode == "neural":
+        r.load_weights(nrb.scenes.make_weights())
+        r.set_use_neural_query(True)
+    return r, eye, basis
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [r for (t, r) in self.rows if t0 - 0.05 <= t <= t1 + 0.15 and len(r) >= 8] or [r for _, r in self.rows if len(r) >= 8]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm = sorted(float(r[0]) for r in rows)
+        reasons = set()
+        for r in rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "reasons": sorted(reasons),
+                "samples": len(rows), "power_w_max": max(float(r[2]) for r in rows)}
+
+
+def cpu_sample(nrb, a, scene, seconds, steps=1):
+    """Time the CPU oracle on a bounded sample of the same workload: a band of rows around the image
+    centre, grown until one frame of it costs about `seconds`.  Returns (Mrays/s, dict)."""
+    from oracle import loader
+    lib = loader.oracle_lib("auto")
+    kind = "reference" if lib.fn("backend")().decode() == "reference" else "port"
+    r, eye, _ = setup(nrb, a, scene, lib=lib)
+    cores = lib.fn("set_threads")(r.handle, 0)
+    rows, mid = 8, a.height // 2
+    best = None
+    while True:
+        y0, y1 = max(0, mid - rows // 2), min(a.height, mid + (rows + 1) // 2)
+        lib.fn("set_row_range")(r.handle, y0, y1)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            r.render(eye)
+        dt = (time.perf_counter() - t0) / steps
+        rays = (y1 - y0) * a.width * a.spp
+        best = (rays / dt / 1e6, dict(kind=kind, cores=int(cores), rows=[y0, y1], seconds=dt))
+        if dt >= seconds * 0.4 or (y1 - y0) >= a.height:
+            break
+        rows = min(a.height, int(rows * min(8.0, max(2.0, seconds * 0.8 / max(dt, 1e-6)))))
+    r.close()
+    v, d = best
+    d["sample"] = (f"rows {d['rows'][0]}..{d['rows'][1]} of {a.height} ({d['rows'][1] - d['rows'][0]}x{a.width}x{a.spp} paths) "
+                   f"of the same workload, {d['seconds']:.2f} s per frame-slice")
+    return v, d
+
+
+def run_reference(a, rank):
+    """--impl reference: the reference's CPU implementation of the path on the host cores."""
+    if rank != 0:
+        return
+    nrb = importlib.import_module("neural-renderer_b200")
+    scene = build_scene(nrb, a)
+    from oracle import loader
+    lib = loader.oracle_lib("auto")
+    kind = "reference" if lib.fn("backend")().decode() == "reference" else "port"
+    r, eye, _ = setup(nrb, a, scene, lib=lib)
+    cores = lib.fn("set_threads")(r.handle, 0)
+    # bounded sample: a centred band of rows sized so K + W steps end within a few minutes
+    probe_rows = 8
+    mid = a.height // 2
+    lib.fn("set_row_range")(r.handle, mid - probe_rows // 2, mid + probe_rows // 2)
+    t0 = time.perf_counter()
+    r.render(eye)
+    per_row = (time.perf_counter() - t0) / probe_rows
+    budget = 120.0 / max(1, a.steps + a.warmup)
+    rows = int(max(8, min(a.height, budget / max(per_row, 1e-9))))
+    y0, y1 = max(0, mid - rows // 2), min(a.height, mid + (rows + 1) // 2)
+    lib.fn("set_row_range")(r.handle, y0, y1)
+    for _ in range(a.warmup):
+        r.render(eye)
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        r.render(eye)
+    dt = (time.perf_counter() - t0) / a.steps
+    rays = (y1 - y0) * a.width * a.spp
+    v = rays / dt / 1e6
+    sample = f"rows {y0}..{y1} of {a.height} per step ({rays} paths), all host threads"
+    print(json.dumps({
+        "impl": "reference", "metric": "neural-render Mrays/s at 1080p", "value": v, "unit": "Mrays/s", "n_gpus": a.gpus,
+        "steps": a.steps, "warmup": a.warmup, "ms_per_step": dt * 1e3 * (a.height / (y1 - y0)), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32+f16", "data": "synthetic",
+        "config": {"workload": workload_name(a), "mode": a.mode},
+        "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": int(cores), "kind": kind, "sample": sample},
+        "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def main():
+    a = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if a.impl == "reference":
+        run_reference(a, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU path)"
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    nrb = importlib.import_module("neural-renderer_b200")
+    scene = build_scene(nrb, a)
+    r, eye, basis = setup(nrb, a, scene)
+    band = 16
+    if world > 1:
+        r.set_tile(band, rank, world)
+    stream = torch.cuda.ExternalStream(r.stream_ptr(), device=torch.device("cuda", local_rank))
+    rays_per_step = a.width * a.height * a.spp
+
+    class Pixels:  # zero-copy torch view of devicePixels()
+        def __init__(self, ptr, n):
+            self.__cuda_array_interface__ = {"shape": (n,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+    def frame_tensor():
+        return torch.as_tensor(Pixels(r.device_pixels(), a.width * a.height * 4), device=torch.device("cuda", local_rank))
+
+    gathered = None
+
+    def gather():
+        """The one exchange step: every rank owns row bands; rank 0 ends up with the whole frame."""
+        nonlocal gathered
+        if world == 1:
+            return
+        t = frame_tensor()
+        if gathered is None:
+            gathered = torch.empty_like(t)
+        gathered.copy_(t)  # non-owned rows are zero on every rank, so a sum over ranks is the gather
+        dist.reduce(gathered, dst=0, op=dist.ReduceOp.SUM)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(steps, body):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.time()
+        e0.record(torch.cuda.current_stream())
+        for _ in range(steps):
+            body()
+        e1.record(torch.cuda.current_stream())  # render() joins its stream into the legacy default stream
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, t0, time.time()
+
+    def step_device():
+        r.render(eye)
+        gather()
+
+    host_frame = torch.empty(a.width * a.height * 4, dtype=torch.uint8).pin_memory()
+
+    def step_e2e():
+        r.set_camera_basis(basis)          # host inputs of the step (camera), uploaded with the launches
+        r.render(eye)
+        gather()
+        if rank == 0:
+            src = gathered if world > 1 else frame_tensor()
+            host_frame.copy_(src, non_blocking=False)   # device->host read of the step's result
+
+    for _ in range(max(3, a.warmup)):
+        step_device()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    ms, t0, t1 = timed(a.steps, step_device)
+    clocks = sampler.stop(t0, t1) if sampler else None
+    counters = r.counters()
+    for _ in range(2):
+        step_e2e()
+    ms_e2e, _, _ = timed(a.steps, step_e2e)
+
+    # second pass with per-launch events -> dominant kernel and its roofline
+    r.set_profile(True)
+    r.reset_stages()
+    for _ in range(a.steps):
+        r.render(eye)
+    r.sync()
+    stages = r.stages()
+    r.set_profile(False)
+    total_stage_ms = sum(v[0] for v in stages.values()) or 1.0
+    neural_q = counters["neural_queries"]
+    launches_per_step = counters["kernels"]
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    pk = peaks()
+    value = rays_per_step * a.steps / (ms * 1e-3) / 1e6
+    e2e = rays_per_step * a.steps / (ms_e2e * 1e-3) / 1e6
+    top = max(stages.items(), key=lambda kv: kv[1][0])
+    per_kernel = {k: {"ms_per_step": v[0] / a.steps, "launches_per_step": v[1] / a.steps, "share": v[0] / total_stage_ms}
+                  for k, v in sorted(stages.items(), key=lambda kv: -kv[1][0])}
+    roof = None
+    if "k_neural_query" in stages and a.mode == "neural":
+        q_ms = stages["k_neural_query"][0] / a.steps
+        tf = neural_q * FLOPS_PER_QUERY / (q_ms * 1e-3) / 1e12
+        roof = {"kernel": "k_neural_query", "bound": "tensor", "achieved": tf, "peak": pk["tf_sustained"], "unit": "TFLOP/s",
+                "frac": tf / pk["tf_sustained"], "traffic": None, "peak_source": pk["src"] + " sustained bf16 (fp16 same pipe rate)",
+                "queries_per_step": neural_q, "flops_per_query": FLOPS_PER_QUERY, "ms_per_step": q_ms,
+                "hbm_gbs": neural_q * HBM_BYTES_PER_QUERY / (q_ms * 1e-3) / 1e9,
+                "l2_gather_gbs": neural_q * 1536 / (q_ms * 1e-3) / 1e9, "top_kernel_by_time": top[0]}
+    else:
+        k, v = top
+        roof = {"kernel": k, "bound": "hbm", "achieved": None, "peak": pk["hbm"], "unit": "GB/s", "frac": None, "traffic": None,
+                "ms_per_step": v[0] / a.steps}
+
+    line = {
+        "metric": "neural-render Mrays/s at 1080p", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": a.steps,
+        "warmup": max(3, a.warmup), "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32 geometry + f16 network (f32 accumulate)", "data": "synthetic",
+        "config": {"workload": workload_name(a), "mode": a.mode, "partition": f"{band}-row bands round-robin, scene+weights replicated",
+                   "l2": "per-frame wavefront state (~0.4 KB/path) exceeds L2; BVH and hash tables are L2-resident by design; "
+                         "every step draws new samples (progressive accumulation)"},
+        "clocks": clocks,
+        "e2e": {"value": e2e, "unit": "Mrays/s", "h2d_bytes_per_step": 1224 * int(launches_per_step),
+                "d2h_bytes_per_step": a.width * a.height * 4, "ms_per_step": ms_e2e / a.steps},
+        "gpu_launches": int(launches_per_step) * a.steps,
+        "roofline": roof,
+        "kernels": per_kernel,
+        "per_step": {"ray_segments": counters["ray_segments"], "neural_queries": neural_q, "path_vertices": counters["path_vertices"],
+                     "segments_per_s_M": counters["ray_segments"] * a.steps / (ms * 1e-3) / 1e6},
+    }
+    if world == 1 and not a.no_cpu_baseline:
+        v, d = cpu_sample(nrb, a, scene, a.cpu_seconds)
+        line["cpu_baseline"] = {"value": v, "unit": "Mrays/s", "cores": d["cores"], "kind": d["kind"], "sample": d["sample"]}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -198,7 +198,8 @@ typedef enum nrb_option {
     NRB_OPT_USE_CONSTANT_NEURAL_COLOR = 6, /* setConstantNeuralColor(use, .) */
     NRB_OPT_USE_DIRECT_ENV_COLOR = 7, /* setDirectEnvColor(use, .) */
     NRB_OPT_CAPTURE = 8,              /* (new) keep per-element debug buffers for nrb_read_buffer */
-    NRB_OPT_USE_HARDWARE_RT = 9       /* setUseHardwareRT: accepted, ignored (no OptiX path) */
+    NRB_OPT_USE_HARDWARE_RT = 9,      /* setUseHardwareRT: accepted, ignored (no OptiX path) */
+    NRB_OPT_PROFILE = 10              /* (new) record a CUDA event after every kernel launch: nrb_get_stage */
 } nrb_option;
 int nrb_set_option(nrb_renderer* r, int option, int value);
 int nrb_get_option(const nrb_renderer* r, int option);
@@ -234,6 +235,12 @@ uint32_t nrb_accum_sample_count(const nrb_renderer* r);
 #define NRB_TIMING_BUCKETS 13
 int nrb_get_timings(nrb_renderer* r, double ms[NRB_TIMING_BUCKETS], int* ray_count,
                     uint64_t* neural_ray_calls);
+/* (new) per-kernel device time accumulated over the frames rendered with NRB_OPT_PROFILE = 1 (the
+ * always-available counterpart of the reference's -DPROFILE_KERNELS event pairs,
+ * src/cuda_renderer_neural.cu:39-57).  Returns 0 and fills the outputs for index < number of distinct
+ * kernels, 1 past the end.  nrb_reset_stages clears the totals. */
+int nrb_get_stage(nrb_renderer* r, int index, const char** name, double* total_ms, uint64_t* launches);
+int nrb_reset_stages(nrb_renderer* r);
 /* (new) counters of the last frame: [0] kernels launched, [1] rays traced (segments),
  * [2] neural queries, [3] path vertices shaded. */
 int nrb_get_counters(nrb_renderer* r, uint64_t out[4]);

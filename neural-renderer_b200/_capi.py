@@ -93,7 +93,7 @@ SLOT_ORIGINAL, SLOT_INNER, SLOT_OUTER, SLOT_ADDITIONAL = 0, 1, 2, 3
 TRACE_ANY, TRACE_FORWARD_ONLY, TRACE_BACKWARD_ONLY = 0, 1, 2
 (OPT_USE_NEURAL_QUERY, OPT_SAMPLES_PER_PIXEL, OPT_BOUNCE_COUNT, OPT_LAMBERT_VIEW, OPT_CLASSIC_MESH_INDEX,
  OPT_USE_ADDITIONAL_MESH, OPT_USE_CONSTANT_NEURAL_COLOR, OPT_USE_DIRECT_ENV_COLOR, OPT_CAPTURE,
- OPT_USE_HARDWARE_RT) = range(10)
+ OPT_USE_HARDWARE_RT, OPT_PROFILE) = range(11)
 
 PRODUCT_LIB = os.path.join(HERE, "libnrb200.so")
 
@@ -143,6 +143,7 @@ class Lib:
             "neural_query": ([vp, vp, sz, vp], i), "neural_query_host": ([vp, vp, sz, vp], i),
             "input_dims": ([vp], i), "output_dims": ([vp], i), "sync": ([vp], i), "stream": ([vp], vp),
             "build_bvh": ([vp, i, vp, i, vp, P(i), vp], i), "abi_version": ([], i),
+            "get_stage": ([vp, i, P(C.c_char_p), P(C.c_double), P(C.c_uint64)], i), "reset_stages": ([vp], i),
             "set_threads": ([vp, i], i), "set_row_range": ([vp, i, i], i), "backend": ([], C.c_char_p),
         }
         for name, (args, res) in table.items():

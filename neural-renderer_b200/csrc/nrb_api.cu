@@ -10,6 +10,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -140,6 +141,13 @@ struct nrb_renderer {
     int lastRayCount = 0, lastLaunches = 0;
     uint64_t lastStats[8] = {0};
     DevBuf scratchA, scratchB, scratchC;  // host-variant batch entry points
+
+    // per-kernel device time (NRB_OPT_PROFILE)
+    int profile = 0;
+    StageProfiler prof;
+    bool profPending = false;
+    std::map<std::string, std::pair<double, uint64_t>> stages;  // name -> (total ms, launches)
+    std::vector<std::string> stageOrder;
 };
 
 namespace {
@@ -341,6 +349,8 @@ void nrb_destroy(nrb_renderer* r) {
     if (r->evStart) cudaEventDestroy(r->evStart);
     if (r->evStop) cudaEventDestroy(r->evStop);
     if (r->evJoin) cudaEventDestroy(r->evJoin);
+    if (r->prof.ready)
+        for (int i = 0; i <= StageProfiler::kMaxMarks; ++i) cudaEventDestroy(r->prof.ev[i]);
     if (r->stream) cudaStreamDestroy(r->stream);
     delete r;
 }
@@ -494,6 +504,7 @@ int nrb_set_option(nrb_renderer* r, int option, int value) {
         case NRB_OPT_USE_CONSTANT_NEURAL_COLOR: r->useConstantNeuralColor = value != 0; break;
         case NRB_OPT_USE_DIRECT_ENV_COLOR: r->useDirectEnvColor = value != 0; break;
         case NRB_OPT_CAPTURE: r->capture = value; break;
+        case NRB_OPT_PROFILE: r->profile = value; break;
         case NRB_OPT_USE_HARDWARE_RT: break;  // accepted, ignored: there is no OptiX path
         default: return fail(NRB_ERR_INVALID, "unknown option");
     }
@@ -511,6 +522,7 @@ int nrb_get_option(const nrb_renderer* r, int option) {
         case NRB_OPT_USE_CONSTANT_NEURAL_COLOR: return r->useConstantNeuralColor;
         case NRB_OPT_USE_DIRECT_ENV_COLOR: return r->useDirectEnvColor;
         case NRB_OPT_CAPTURE: return r->capture;
+        case NRB_OPT_PROFILE: return r->profile;
         default: return 0;
     }
 }
@@ -596,6 +608,27 @@ int ensure_state(nrb_renderer* r, size_t nElems, size_t localPixels, size_t fram
     }
     r->st.accum = r->accum.as<float>();
     r->st.pixels = r->pixels.as<uchar4>();
+    return NRB_OK;
+}
+
+// Turn the event marks of the last profiled frame into per-kernel totals.
+int drain_profiler(nrb_renderer* r) {
+    if (!r->profPending) return NRB_OK;
+    r->profPending = false;
+    NRB_CUDA(cudaStreamSynchronize(r->stream));
+    for (int i = 0; i < r->prof.marks; ++i) {
+        float ms = 0.0f;
+        if (cudaEventElapsedTime(&ms, r->prof.ev[i], r->prof.ev[i + 1]) != cudaSuccess) continue;
+        const std::string key(r->prof.name[i]);
+        auto it = r->stages.find(key);
+        if (it == r->stages.end()) {
+            r->stageOrder.push_back(key);
+            it = r->stages.emplace(key, std::make_pair(0.0, 0ull)).first;
+        }
+        it->second.first += ms;
+        it->second.second += 1;
+    }
+    r->prof.marks = 0;
     return NRB_OK;
 }
 
@@ -694,12 +727,27 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     f.additionalEnabled = r->useAdditionalMesh ? 1 : 0;
 
     cudaStream_t s = r->stream;
+    if (r->profile) {
+        rc = drain_profiler(r);
+        if (rc != NRB_OK) return rc;
+        if (!r->prof.ready) {
+            for (int i = 0; i <= StageProfiler::kMaxMarks; ++i) NRB_CUDA(cudaEventCreate(&r->prof.ev[i]));
+            r->prof.ready = true;
+        }
+    }
     NRB_CUDA(cudaMemsetAsync(r->st.stats, 0, 16 * sizeof(unsigned long long), s));
     NRB_CUDA(cudaEventRecord(r->evStart, s));
+    if (r->profile) {
+        r->prof.marks = 0;
+        NRB_CUDA(cudaEventRecord(r->prof.ev[0], s));
+        set_stage_profiler(&r->prof);
+    }
     const bool neural = r->useNeuralQuery && r->weightsLoaded && outer.view.numTriangles > 0;  // (:2258-2260)
     int launches;
     if (neural) launches = launch_neural_frame(f, r->net, r->lambertView, s);
     else launches = launch_gt_frame(f, r->lambertView, s);
+    set_stage_profiler(nullptr);
+    r->profPending = r->profile != 0;
     NRB_CUDA(cudaEventRecord(r->evStop, s));
     NRB_CUDA(cudaGetLastError());
     if (r->lambertView) r->accumSampleCount = 0;
@@ -744,6 +792,27 @@ int nrb_get_timings(nrb_renderer* r, double ms[NRB_TIMING_BUCKETS], int* ray_cou
     if (ray_count) *ray_count = r->lastRayCount;
     if (neural_ray_calls) *neural_ray_calls = r->lastStats[1];
     return NRB_OK;
+}
+
+int nrb_get_stage(nrb_renderer* r, int index, const char** name, double* total_ms, uint64_t* launches) {
+    if (!r || index < 0) return fail(NRB_ERR_INVALID, "bad argument");
+    NRB_CUDA(cudaSetDevice(r->device));
+    int rc = drain_profiler(r);
+    if (rc != NRB_OK) return rc;
+    if (index >= static_cast<int>(r->stageOrder.size())) return 1;  // past the end
+    const auto& e = *r->stages.find(r->stageOrder[index]);
+    if (name) *name = e.first.c_str();
+    if (total_ms) *total_ms = e.second.first;
+    if (launches) *launches = e.second.second;
+    return NRB_OK;
+}
+
+int nrb_reset_stages(nrb_renderer* r) {
+    if (!r) return fail(NRB_ERR_INVALID, "null renderer");
+    int rc = drain_profiler(r);
+    r->stages.clear();
+    r->stageOrder.clear();
+    return rc;
 }
 
 int nrb_get_counters(nrb_renderer* r, uint64_t out[4]) {

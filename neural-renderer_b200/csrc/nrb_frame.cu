@@ -142,8 +142,16 @@ __global__ void __launch_bounds__(128) k_trace_rays(const __grid_constant__ Mesh
 
 // ---------------------------------------------------------------------------------------------
 
+static thread_local StageProfiler* g_profiler = nullptr;
+void set_stage_profiler(StageProfiler* p) { g_profiler = p; }
+
 void debug_check(const char* what, cudaStream_t s) {
     static const bool on = getenv("NRB_DEBUG") != nullptr;
+    if (g_profiler && g_profiler->marks < StageProfiler::kMaxMarks) {
+        StageProfiler& p = *g_profiler;
+        p.name[p.marks] = what;
+        cudaEventRecord(p.ev[++p.marks], s);
+    }
     if (!on) return;
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaStreamSynchronize(s);

@@ -17,7 +17,18 @@ struct Frame {
     int additionalEnabled;
 };
 
-// Debug aid: with NRB_DEBUG=1 in the environment every launch is followed by a synchronise + report.
+// Per-launch hook.  NRB_DEBUG=1 in the environment: synchronise + report after every launch.
+// With a StageProfiler installed (NRB_OPT_PROFILE): record a CUDA event after every launch so the
+// host can attribute device time to kernels (the reference's PROF_BEGIN/PROF_END pairs,
+// src/cuda_renderer_neural.cu:39-57, always compiled in here).
+struct StageProfiler {
+    static constexpr int kMaxMarks = 1024;
+    cudaEvent_t ev[kMaxMarks + 1];
+    const char* name[kMaxMarks];
+    int marks = 0;
+    bool ready = false;
+};
+void set_stage_profiler(StageProfiler* p);
 void debug_check(const char* what, cudaStream_t s);
 #define NRB_LAUNCHED(what, s) ::nrb::debug_check(what, s)
 

@@ -18,6 +18,7 @@
 // others.  Accumulation is fp32 (tiny-cuda-nn accumulates in fp16; fp32 is closer to exact).
 // The tcgen05/TMEM variant lives in nrb_neural_tc.cu.
 #include "nrb_neural.cuh"
+#include "nrb_frame.cuh"
 
 #include <cuda_runtime.h>
 
@@ -308,6 +309,7 @@ int launch_neural_query(const NetDev& net, const float* in, size_t n, const int*
             attr = true;
         }
         k_neural_query<128><<<grid, threads, p.total, s>>>(net, in, static_cast<int>(n), dCount, out, p.ek, p.warps);
+        NRB_LAUNCHED("k_neural_query", s);
     } else {
         static bool attr = false;
         if (!attr) {
@@ -315,6 +317,7 @@ int launch_neural_query(const NetDev& net, const float* in, size_t n, const int*
             attr = true;
         }
         k_neural_query<64><<<grid, threads, p.total, s>>>(net, in, static_cast<int>(n), dCount, out, p.ek, p.warps);
+        NRB_LAUNCHED("k_neural_query", s);
     }
     return 1;
 }

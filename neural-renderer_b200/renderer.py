@@ -284,6 +284,28 @@ class RendererNeural:
     def set_capture(self, v: bool):
         self._opt(K.OPT_CAPTURE, v)
 
+    def set_profile(self, v: bool):
+        """Per-kernel device timing (the reference's -DPROFILE_KERNELS), read with stages()."""
+        self._opt(K.OPT_PROFILE, v)
+
+    def stages(self):
+        """-> {kernel name: (total ms, launches)} accumulated since reset_stages()."""
+        out, i = {}, 0
+        while True:
+            name, ms, n = C.c_char_p(), C.c_double(0), C.c_uint64(0)
+            rc = self.lib.fn("get_stage")(self._h, i, C.byref(name), C.byref(ms), C.byref(n))
+            if rc != 0:
+                break
+            out[name.value.decode()] = (ms.value, n.value)
+            i += 1
+        return out
+
+    def reset_stages(self):
+        self.lib.check(self.lib.fn("reset_stages")(self._h), "reset_stages")
+
+    def stream_ptr(self) -> int:
+        return self.lib.fn("stream")(self._h)
+
     def set_tile(self, band_rows: int, rank: int, world: int):
         self.lib.check(self.lib.fn("set_tile")(self._h, band_rows, rank, world), "set_tile")
 
