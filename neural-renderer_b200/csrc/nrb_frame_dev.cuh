@@ -58,7 +58,7 @@ __device__ __forceinline__ V3 global_mparams(const MaterialDev& g) {
 template <int MODE>
 __device__ __forceinline__ bool hit_record(const Frame& f, int slot, V3 o, V3 d, V3& pos, V3& nrm, V3& alb, V3& mp) {
     const MeshDev& m = f.mesh[slot];
-    const Hit h = trace_closest<MODE>(m, o, d);
+    const Hit h = trace_dyn(target_of(m), MODE, o, d);
     if (h.t >= 1e30f) {
         mp = global_mparams(f.gmat);
         return false;

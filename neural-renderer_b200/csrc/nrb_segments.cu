@@ -65,9 +65,9 @@ __global__ void __launch_bounds__(kQueueThreads) k_seg_exits(const __grid_consta
         const int e = f.st.queue[qin][i];
         const V3 entry = f4v(f.st.segE[e]), dir = f4v(f.st.segD[e]);
         const V3 shifted = entry + dir * kSegEps;
-        const Hit ho = trace_closest<TRACE_BACKWARD>(f.mesh[NRB_SLOT_OUTER], shifted, dir);
+        const Hit ho = trace_dyn(target_of(f.mesh[NRB_SLOT_OUTER]), TRACE_BACKWARD, shifted, dir);
         const float exitT = ho.t < 1e30f ? ho.t : kSegEps;
-        const Hit hi = trace_closest<TRACE_ANY>(f.mesh[NRB_SLOT_INNER], shifted, dir);
+        const Hit hi = trace_dyn(target_of(f.mesh[NRB_SLOT_INNER]), TRACE_ANY, shifted, dir);
         const bool hitInner = hi.t < 1e30f;
         const float innerT = hitInner ? hi.t : 1e30f;
         const bool innerFirst = hitInner && (innerT < exitT);
@@ -135,7 +135,7 @@ __global__ void __launch_bounds__(kQueueThreads) k_seg_apply(const __grid_consta
                 rec_store(rec, e, pos, 1, nrm, distance, col, global_mparams(f.gmat));
             } else {
                 const V3 shiftedExit = f4v(X) + dir * kSegEps;
-                const Hit hr = trace_closest<TRACE_FORWARD>(f.mesh[NRB_SLOT_OUTER], shiftedExit, dir);
+                const Hit hr = trace_dyn(target_of(f.mesh[NRB_SLOT_OUTER]), TRACE_FORWARD, shiftedExit, dir);
                 ++nTrace;
                 const bool re = hr.t < 1e30f;
                 if (re || innerHit) {
@@ -200,56 +200,71 @@ __global__ void __launch_bounds__(kQueueThreads) k_bounce_begin(const __grid_con
     const int n = f.st.counts[qin];
     const int nWarpRounded = (n + 31) & ~31;
     const SurfRec& cur = f.st.rec[bounce == 1 ? 0 : 1];
-    const MeshDev& outer = f.mesh[NRB_SLOT_OUTER];
-    const MeshDev& inner = f.mesh[NRB_SLOT_INNER];
+    const TraceTarget tOuter = target_of(f.mesh[NRB_SLOT_OUTER]), tInner = target_of(f.mesh[NRB_SLOT_INNER]);
     unsigned int nTrace = 0, nVert = 0;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nWarpRounded; i += gridDim.x * blockDim.x) {
         bool alive = false, enters = false;
-        int e = 0;
+        int e = 0, stage = 5;
+        V3 org = v3s(0.0f), wi = v3(0.0f, 0.0f, 1.0f), weight = v3s(0.0f);
+        float pdf = 0.0f, carried = 0.0f;
         if (i < n) {
             e = f.st.queue[qin][i];
             const ElemId id = queue_elem(fp, e);
             const float4 P = cur.P[e], N = cur.N[e], C = cur.C[e];
             const float2 M = cur.M[e];
-            V3 org, wi, weight;
-            float pdf;
             const V3 prev = bounce == 1 ? v3s(0.0f) : f4v(f.st.prevD[e]);
             ++nVert;
             alive = sample_vertex(f, id, f4v(P), f4v(N), f4v(C), v3(C.w, M.x, M.y), bounce == 1, prev, org, wi, weight,
                                   pdf);
-            const float carried = N.w;
-            if (alive && carried > 0.0f) {  // checkBounceEarlyTerminationKernel
-                const Hit ho = trace_closest<TRACE_ANY>(outer, org, wi);
-                const Hit hi = trace_closest<TRACE_ANY>(inner, org, wi);
-                nTrace += 2;
-                if (hi.t < 1e30f && ho.t < 1e30f && hi.t < ho.t) alive = false;
-            }
-            if (alive) {
-                f.st.rayO[e] = make_float4(org.x, org.y, org.z, pdf);
-                f.st.rayD[e] = make_float4(wi.x, wi.y, wi.z, carried);
-                f.st.rayW[e] = make_float4(weight.x, weight.y, weight.z, 0.0f);
-                rec_clear(f.st.rec[1], e);
-                // traceOuterShellEntryFromRaysKernel
-                Hit h = trace_closest<TRACE_FORWARD>(outer, org, wi);
+            carried = N.w;
+            // stage of this lane's trace sequence: 0/1 = early-termination outer/inner (ANY),
+            // 2 = shell entry (FORWARD), 3 = exit when starting inside (BACKWARD), 4 = re-entry
+            if (alive) stage = carried > 0.0f ? 0 : 2;
+        }
+        // checkBounceEarlyTerminationKernel + traceOuterShellEntryFromRaysKernel as one convergent
+        // loop: every lane that still has a trace to do runs the same out-of-line traversal
+        Hit hEntry{1e30f, 0.0f, 0.0f, 0u};
+        float outerAnyT = 1e30f, baseOffset = 0.0f;
+        V3 entryOrigin = org;
+        while (__any_sync(0xffffffffu, stage < 5)) {
+            if (stage < 5) {
+                const TraceTarget tgt = pick_target(stage == 1, tInner, tOuter);
+                const int mode = stage <= 1 ? TRACE_ANY : (stage == 3 ? TRACE_BACKWARD : TRACE_FORWARD);
+                const Hit h = trace_dyn(tgt, mode, stage == 4 ? entryOrigin : org, wi);
                 ++nTrace;
-                float baseOffset = 0.0f;
-                V3 entryOrigin = org;
-                if (h.t >= 1e30f) {
-                    const Hit hx = trace_closest<TRACE_BACKWARD>(outer, org, wi);
-                    ++nTrace;
-                    if (hx.t < 1e30f) {
-                        baseOffset = hx.t + kSegEps;
+                if (stage == 0) {
+                    outerAnyT = h.t;
+                    stage = 1;
+                } else if (stage == 1) {
+                    if (h.t < 1e30f && outerAnyT < 1e30f && h.t < outerAnyT) { alive = false; stage = 5; }
+                    else stage = 2;
+                } else if (stage == 2) {
+                    if (h.t < 1e30f) { hEntry = h; stage = 5; }
+                    else stage = 3;
+                } else if (stage == 3) {
+                    if (h.t < 1e30f) {
+                        baseOffset = h.t + kSegEps;
                         entryOrigin = org + wi * baseOffset;
-                        h = trace_closest<TRACE_FORWARD>(outer, entryOrigin, wi);
-                        ++nTrace;
+                        stage = 4;
+                    } else {
+                        stage = 5;
                     }
+                } else {
+                    hEntry = h;
+                    stage = 5;
                 }
-                if (h.t < 1e30f) {
-                    const V3 p = entryOrigin + wi * h.t;
-                    f.st.segE[e] = make_float4(p.x, p.y, p.z, baseOffset + h.t);
-                    f.st.segD[e] = make_float4(wi.x, wi.y, wi.z, 0.0f);
-                    enters = true;
-                }
+            }
+        }
+        if (alive) {
+            f.st.rayO[e] = make_float4(org.x, org.y, org.z, pdf);
+            f.st.rayD[e] = make_float4(wi.x, wi.y, wi.z, carried);
+            f.st.rayW[e] = make_float4(weight.x, weight.y, weight.z, 0.0f);
+            rec_clear(f.st.rec[1], e);
+            if (hEntry.t < 1e30f) {
+                const V3 p = entryOrigin + wi * hEntry.t;
+                f.st.segE[e] = make_float4(p.x, p.y, p.z, baseOffset + hEntry.t);
+                f.st.segD[e] = make_float4(wi.x, wi.y, wi.z, 0.0f);
+                enters = true;
             }
         }
         queue_push(f.st.queue[qray], f.st.counts + qray, alive, e);
@@ -302,9 +317,12 @@ __global__ void __launch_bounds__(kQueueThreads) k_bounce_finish(const __grid_co
 // The segment loop of traceNeuralSegmentsForRays: fixed kMaxSegIters iterations, device counts.
 static int run_segments(const Frame& f, const NetDev& net, int recIdx, cudaStream_t s) {
     int launches = 0;
-    const int grid = queue_grid(f.fp.nElems);
     int qin = 2;
     for (int it = 0; it < kMaxSegIters; ++it) {
+        // Iterations past the first see only rays that left a shell segment without a hit and
+        // re-entered it: usually none, rarely many.  They get a one-wave grid (grid-stride loops make
+        // any count correct) so that an empty iteration costs a minimal launch.
+        const int grid = it == 0 ? queue_grid(f.fp.nElems) : 148;
         const int qout = qin == 2 ? 3 : 2;
         cudaMemsetAsync(f.st.counts + qout, 0, sizeof(int), s);
         k_seg_exits<<<grid, kQueueThreads, 0, s>>>(f, qin);

@@ -118,6 +118,99 @@ __device__ __forceinline__ Hit trace_closest(const MeshDev& m, V3 o, V3 d, Trace
     return best;
 }
 
+// Out-of-line traversal with the mesh and the facing mode chosen at run time, per lane.  One copy of
+// the loop per kernel instead of one per call site keeps the multi-trace stages (bounce entry,
+// segment exits) inside the instruction cache, and lets lanes that are at different steps of a
+// stage's trace sequence (or tracing different meshes) execute the same instructions together.
+struct TraceTarget {
+    const NodePair* nodes;
+    const TriBlock* tris;
+    int rootRef, numTriangles;
+    V3 bmin, bmax;
+};
+
+__device__ __forceinline__ TraceTarget target_of(const MeshDev& m) {
+    return TraceTarget{m.nodes, m.tris, m.rootRef, m.numTriangles, v3(m.rootMin[0], m.rootMin[1], m.rootMin[2]),
+                       v3(m.rootMax[0], m.rootMax[1], m.rootMax[2])};
+}
+
+__device__ __forceinline__ TraceTarget pick_target(bool first, const TraceTarget& a, const TraceTarget& b) {
+    TraceTarget t;
+    t.nodes = first ? a.nodes : b.nodes;
+    t.tris = first ? a.tris : b.tris;
+    t.rootRef = first ? a.rootRef : b.rootRef;
+    t.numTriangles = first ? a.numTriangles : b.numTriangles;
+    t.bmin = first ? a.bmin : b.bmin;
+    t.bmax = first ? a.bmax : b.bmax;
+    return t;
+}
+
+static __device__ __noinline__ Hit trace_dyn(TraceTarget m, int mode, V3 o, V3 d) {
+    Hit best{1e30f, 0.0f, 0.0f, 0u};
+    if (m.numTriangles <= 0) return best;
+    const V3 inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    float tn;
+    if (!slab(o, inv, m.bmin.x, m.bmin.y, m.bmin.z, m.bmax.x, m.bmax.y, m.bmax.z, best.t, tn)) return best;
+    int2 stack[kTraceStack];
+    int sp = 0;
+    int ref = m.rootRef;
+    const NodePair* __restrict__ nodes = m.nodes;
+    const TriBlock* __restrict__ tris = m.tris;
+    for (;;) {
+        if (ref >= 0) {
+            const float4 a = __ldg(&nodes[ref].a), b = __ldg(&nodes[ref].b), c = __ldg(&nodes[ref].c);
+            const int4 k = __ldg(&nodes[ref].d);
+            float ln, rn;
+            const bool hl = slab(o, inv, a.x, a.y, a.z, a.w, b.x, b.y, best.t, ln);
+            const bool hr = slab(o, inv, b.z, b.w, c.x, c.y, c.z, c.w, best.t, rn);
+            if (hl && hr) {
+                int nearRef = k.x, farRef = k.y;
+                float farT = rn;
+                if (rn < ln) { nearRef = k.y; farRef = k.x; farT = ln; }
+                if (sp < kTraceStack) stack[sp++] = make_int2(farRef, __float_as_int(farT));
+                ref = nearRef;
+                continue;
+            }
+            if (hl) { ref = k.x; continue; }
+            if (hr) { ref = k.y; continue; }
+        } else {
+            const int packed = ~ref;
+            const int first = packed >> kLeafCountBits;
+            const int end = first + (packed & ((1 << kLeafCountBits) - 1)) + 1;
+            for (int i = first; i < end; ++i) {
+                const float4 p = __ldg(&tris[i].p), q = __ldg(&tris[i].q), r = __ldg(&tris[i].r);
+                const float facing = dot(v3(p.w, q.w, r.w), d);
+                if (mode == TRACE_FORWARD && facing >= 0.0f) continue;
+                if (mode == TRACE_BACKWARD && facing <= 0.0f) continue;
+                const V3 e1 = v3(q.x, q.y, q.z), e2 = v3(r.x, r.y, r.z);
+                const V3 pv = cross(d, e2);
+                const float det = dot(e1, pv);
+                if (fabsf(det) < 1e-8f) continue;
+                const float invDet = 1.0f / det;
+                const V3 tv = o - v3(p.x, p.y, p.z);
+                const float u = dot(tv, pv) * invDet;
+                if (u < 0.0f || u > 1.0f) continue;
+                const V3 qv = cross(tv, e1);
+                const float v = dot(d, qv) * invDet;
+                if (v < 0.0f || u + v > 1.0f) continue;
+                const float t = dot(e2, qv) * invDet;
+                if (t <= 1e-8f) continue;
+                if (t > 1e-6f && t < best.t) best = Hit{t, u, v, static_cast<uint32_t>(i)};
+            }
+        }
+        bool found = false;
+        while (sp > 0) {
+            const int2 e = stack[--sp];
+            if (__int_as_float(e.y) > best.t) continue;
+            ref = e.x;
+            found = true;
+            break;
+        }
+        if (!found) break;
+    }
+    return best;
+}
+
 template <bool STATS = false>
 __device__ __forceinline__ Hit trace_mode(const MeshDev& m, int mode, V3 o, V3 d, TraceStats* st = nullptr) {
     if (mode == TRACE_FORWARD) return trace_closest<TRACE_FORWARD, STATS>(m, o, d, st);

@@ -302,3 +302,10 @@ void OrcNetwork::forward(const float* inputs, int n, uint16_t* out) const {
         }
     }
 }
+
+// C entry points of the software fp16 helpers (tests/test_oracle_pinning.py checks them against numpy).
+extern "C" {
+uint16_t orc_c_float_to_half(float f) { return orc_float_to_half(f); }
+float orc_c_half_to_float(uint16_t h) { return orc_half_to_float(h); }
+uint16_t orc_c_hfma(uint16_t a, uint16_t b, uint16_t c) { return orc_hfma(a, b, c); }
+}

@@ -162,3 +162,23 @@ def test_tiles_reassemble_full_frame(oracle_lib):
             if (y // 8) % 3 == k:
                 merged[y] = p[y]
     assert np.array_equal(merged, full)
+
+
+def test_matches_committed_reference_fixtures():
+    """libnrb200 against tests/golden/frames_v1.npz (outputs of the reference's own headers)."""
+    import os
+    from tests.golden.make_golden import render_all
+    gold = np.load(os.path.join(os.path.dirname(__file__), "golden", "frames_v1.npz"))
+    got = render_all(nrb, None)
+    for k in gold.files:
+        if k.startswith("trace_"):
+            assert np.array_equal(got[k], gold[k]), k
+    for k in ("gt_hit_flags", "gt_hit_positions"):
+        assert np.array_equal(got[k], gold[k]), k
+    assert psnr8(got["gt_pixels"], gold["gt_pixels"]) > 45.0
+    rad = np.abs(got["gt_radiance"] - gold["gt_radiance"])
+    assert np.mean(rad > 1e-3) < 0.01  # bounce directions go through sinf/cosf/powf (CUDA vs glibc ulps)
+    err = rae_ok(got["query"][:, :8], gold["query"][:, :8])
+    assert np.percentile(err, 99) < 1e-2 and err.max() < 5e-2
+    assert np.mean(got["neural_hit_flags"] != gold["neural_hit_flags"]) < 5e-3
+    assert psnr8(got["neural_pixels"], gold["neural_pixels"]) > 30.0
