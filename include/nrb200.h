@@ -199,7 +199,8 @@ typedef enum nrb_option {
     NRB_OPT_USE_DIRECT_ENV_COLOR = 7, /* setDirectEnvColor(use, .) */
     NRB_OPT_CAPTURE = 8,              /* (new) keep per-element debug buffers for nrb_read_buffer */
     NRB_OPT_USE_HARDWARE_RT = 9,      /* setUseHardwareRT: accepted, ignored (no OptiX path) */
-    NRB_OPT_PROFILE = 10              /* (new) record a CUDA event after every kernel launch: nrb_get_stage */
+    NRB_OPT_PROFILE = 10,             /* (new) record a CUDA event after every kernel launch: nrb_get_stage */
+    NRB_OPT_QUERY_KERNEL = 11         /* (new, process-wide) neural query kernel: 0 auto, 1 mma.sync, 2 tcgen05 */
 } nrb_option;
 int nrb_set_option(nrb_renderer* r, int option, int value);
 int nrb_get_option(const nrb_renderer* r, int option);

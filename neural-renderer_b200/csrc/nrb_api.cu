@@ -505,6 +505,7 @@ int nrb_set_option(nrb_renderer* r, int option, int value) {
         case NRB_OPT_USE_DIRECT_ENV_COLOR: r->useDirectEnvColor = value != 0; break;
         case NRB_OPT_CAPTURE: r->capture = value; break;
         case NRB_OPT_PROFILE: r->profile = value; break;
+        case NRB_OPT_QUERY_KERNEL: set_query_kernel(value); break;
         case NRB_OPT_USE_HARDWARE_RT: break;  // accepted, ignored: there is no OptiX path
         default: return fail(NRB_ERR_INVALID, "unknown option");
     }
@@ -523,6 +524,7 @@ int nrb_get_option(const nrb_renderer* r, int option) {
         case NRB_OPT_USE_DIRECT_ENV_COLOR: return r->useDirectEnvColor;
         case NRB_OPT_CAPTURE: return r->capture;
         case NRB_OPT_PROFILE: return r->profile;
+        case NRB_OPT_QUERY_KERNEL: return query_kernel();
         default: return 0;
     }
 }

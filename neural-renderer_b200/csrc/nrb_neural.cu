@@ -17,7 +17,7 @@
 // barrier after the weight preload, so gather latency of one warp overlaps tensor work of the
 // others.  Accumulation is fp32 (tiny-cuda-nn accumulates in fp16; fp32 is closer to exact).
 // The tcgen05/TMEM variant lives in nrb_neural_tc.cu.
-#include "nrb_neural.cuh"
+#include "nrb_encode.cuh"
 #include "nrb_frame.cuh"
 
 #include <cuda_runtime.h>
@@ -40,92 +40,6 @@ __device__ __forceinline__ void mma16816(float (&c)[4], uint32_t a0, uint32_t a1
     asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
                  : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
                  : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
-}
-
-// fp32 accumulator -> fp16, LeakyReLU evaluated in fp16 as tiny-cuda-nn does.
-__device__ __forceinline__ __half leaky_h(float v) {
-    const __half h = __float2half_rn(v);
-    return __hgt(h, __float2half_rn(0.0f)) ? h : __hmul(h, __float2half_rn(0.01f));
-}
-
-// grid_index (common_device.h:848-884) with the coherent prime hash.
-__device__ __forceinline__ uint32_t level_index(bool dense, bool pow2, uint32_t size, uint32_t res, uint32_t x,
-                                                uint32_t y, uint32_t z) {
-    uint32_t idx = dense ? x + y * res + z * res * res : (x ^ (y * 2654435761u) ^ (z * 805459861u));
-    return pow2 ? (idx & (size - 1u)) : (idx % size);
-}
-
-// One (row, point, level) item: 8 corner gathers, fp16 FMA chain in tiny-cuda-nn's corner order.
-template <int F>
-__device__ __forceinline__ void encode_item(const NetDev& net, int level, const float* x, __half* dst) {
-    const float scale = net.levelScale[level];
-    const uint32_t res = net.levelRes[level], size = net.levelSize[level];
-    const bool dense = net.levelDense[level], pow2 = net.levelPow2[level];
-    const __half* table = net.grid + static_cast<size_t>(net.levelOffset[level]) * F;
-    float w[3];
-    uint32_t g[3];
-#pragma unroll
-    for (int d = 0; d < 3; ++d) {
-        const float p = fmaf(scale, x[d], 0.5f);
-        const float fl = floorf(p);
-        g[d] = static_cast<uint32_t>(static_cast<int>(fl));
-        w[d] = p - fl;
-    }
-    // issue all 8 gathers first (independent loads), then run the dependent fp16 chain
-    uint32_t raw[8][F / 2];
-#pragma unroll
-    for (int c = 0; c < 8; ++c) {
-        const uint32_t cx = g[0] + (c & 1), cy = g[1] + ((c >> 1) & 1), cz = g[2] + ((c >> 2) & 1);
-        const uint32_t idx = level_index(dense, pow2, size, res, cx, cy, cz);
-        if (F == 4) {
-            const uint2 v = __ldg(reinterpret_cast<const uint2*>(table + static_cast<size_t>(idx) * 4));
-            raw[c][0] = v.x;
-            raw[c][F / 2 - 1] = v.y;
-        } else {
-            raw[c][0] = __ldg(reinterpret_cast<const uint32_t*>(table + static_cast<size_t>(idx) * 2));
-        }
-    }
-    __half2 acc[F / 2];
-#pragma unroll
-    for (int k = 0; k < F / 2; ++k) acc[k] = __float2half2_rn(0.0f);
-#pragma unroll
-    for (int c = 0; c < 8; ++c) {
-        float wt = 1.0f;
-#pragma unroll
-        for (int d = 0; d < 3; ++d) wt *= (c & (1 << d)) ? w[d] : 1.0f - w[d];
-        const __half2 wh = __half2half2(__float2half_rn(wt));
-#pragma unroll
-        for (int k = 0; k < F / 2; ++k) acc[k] = __hfma2(wh, *reinterpret_cast<const __half2*>(&raw[c][k]), acc[k]);
-    }
-#pragma unroll
-    for (int k = 0; k < F / 2; ++k) *reinterpret_cast<__half2*>(dst + 2 * k) = acc[k];
-}
-
-// sh_enc (common_device.h:476-502) up to degree 4, fp32 -> fp16.
-__device__ __forceinline__ void encode_sh(int degree, const float* d, __half* dst) {
-    const float x = d[0] * 2.f - 1.f, y = d[1] * 2.f - 1.f, z = d[2] * 2.f - 1.f;
-    const float xy = x * y, xz = x * z, yz = y * z, x2 = x * x, y2 = y * y, z2 = z * z;
-    float o[16];
-    o[0] = 0.28209479177387814f;
-    o[1] = -0.48860251190291987f * y;
-    o[2] = 0.48860251190291987f * z;
-    o[3] = -0.48860251190291987f * x;
-    o[4] = 1.0925484305920792f * xy;
-    o[5] = -1.0925484305920792f * yz;
-    o[6] = 0.94617469575755997f * z2 - 0.31539156525251999f;
-    o[7] = -1.0925484305920792f * xz;
-    o[8] = 0.54627421529603959f * x2 - 0.54627421529603959f * y2;
-    o[9] = 0.59004358992664352f * y * (-3.0f * x2 + y2);
-    o[10] = 2.8906114426405538f * xy * z;
-    o[11] = 0.45704579946446572f * y * (1.0f - 5.0f * z2);
-    o[12] = 0.3731763325901154f * z * (5.0f * z2 - 3.0f);
-    o[13] = 0.45704579946446572f * x * (1.0f - 5.0f * z2);
-    o[14] = 1.4453057213202769f * z * (x2 - y2);
-    o[15] = 0.59004358992664352f * x * (-x2 + 3.0f * y2);
-    const int n = degree * degree;
-#pragma unroll
-    for (int i = 0; i < 16; ++i)
-        if (i < n) dst[i] = __float2half_rn(o[i]);
 }
 
 struct SmemPlan {
@@ -293,9 +207,14 @@ size_t neural_query_smem(const NetDev& net, int* warpsOut) {
     return p.warps > 0 ? p.total : 0;
 }
 
+static int g_queryKernel = 0;
+void set_query_kernel(int which) { g_queryKernel = which; }
+int query_kernel() { return g_queryKernel; }
+
 int launch_neural_query(const NetDev& net, const float* in, size_t n, const int* dCount, __half* out,
                         cudaStream_t s) {
     if (n == 0) return 0;
+    if (g_queryKernel != 1 && neural_query_tc_supported(net)) return launch_neural_query_tc(net, in, n, dCount, out, s);
     const SmemPlan p = plan_smem(net);
     if (p.warps <= 0) return -1;
     const int tiles = static_cast<int>((n + kRows - 1) / kRows);

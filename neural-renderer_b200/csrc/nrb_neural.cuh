@@ -31,6 +31,13 @@ struct NetDev {
 // count is read on the device from *dCount and n is only the launch bound), outputs fp16 [n][16].
 int launch_neural_query(const NetDev& net, const float* in, size_t n, const int* dCount, __half* out,
                         cudaStream_t s);
+// The tcgen05/TMEM kernel (nrb_neural_tc.cu) and the kernel choice: 0 = automatic (tcgen05 when the
+// shape is supported), 1 = force the mma.sync kernel, 2 = force tcgen05.
+bool neural_query_tc_supported(const NetDev& net);
+int launch_neural_query_tc(const NetDev& net, const float* in, size_t n, const int* dCount, __half* out,
+                           cudaStream_t s);
+void set_query_kernel(int which);
+int query_kernel();
 // Bytes of dynamic shared memory the query kernel needs for this network (0 = unsupported shape).
 size_t neural_query_smem(const NetDev& net, int* warpsOut);
 

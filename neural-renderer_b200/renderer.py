@@ -288,6 +288,10 @@ class RendererNeural:
         """Per-kernel device timing (the reference's -DPROFILE_KERNELS), read with stages()."""
         self._opt(K.OPT_PROFILE, v)
 
+    def set_query_kernel(self, which: int):
+        """0 = automatic, 1 = mma.sync kernel, 2 = tcgen05/TMEM kernel (process-wide)."""
+        self._opt(K.OPT_QUERY_KERNEL, which)
+
     def stages(self):
         """-> {kernel name: (total ms, launches)} accumulated since reset_stages()."""
         out, i = {}, 0

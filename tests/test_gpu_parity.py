@@ -58,12 +58,14 @@ def _weights(**net):
     return nrb.scenes.make_weights(seed=42, **net)
 
 
-def test_neural_query_matches_oracle(oracle_lib):
+@pytest.mark.parametrize("kernel", [1, 2], ids=["mma_sync", "tcgen05"])
+def test_neural_query_matches_oracle(oracle_lib, kernel):
     scene = nrb.scenes.make_scene("ico", 1, env=False)
     w = _weights()
     prod, orc, _ = make_pair(scene, oracle_lib, 8, 8, weights=w)
+    prod.set_query_kernel(kernel)
     rng = np.random.RandomState(99)
-    for n in (1, 15, 16, 257, 4096):
+    for n in (1, 15, 16, 127, 129, 257, 4096, 40000):
         x = rng.uniform(0, 1, (n, prod.input_dims())).astype(np.float32)
         a, b = prod.neural_query(x), orc.neural_query(x)
         err = rae_ok(a[:, :8], b[:, :8])
@@ -71,9 +73,11 @@ def test_neural_query_matches_oracle(oracle_lib):
         # rounded to fp16 per layer -> a few fp16 ulps after 5 layers
         assert np.percentile(err, 99) < 1e-2, (n, np.percentile(err, 99))
         assert err.max() < 5e-2, (n, err.max())
+    prod.set_query_kernel(0)
 
 
-def test_neural_query_other_shape(oracle_lib):
+@pytest.mark.parametrize("kernel", [1, 2], ids=["mma_sync", "tcgen05"])
+def test_neural_query_other_shape(oracle_lib, kernel):
     """BASELINE config 5 shape: 1 x HashGrid(16 levels, 2 features, T=2^15, scale 1.5) -> 32 -> 64 x 2 -> 16."""
     cfg = nrb.NNConfig(log2_hashmap_size=15, base_resolution=16, n_points=1, n_levels=16, n_features_per_level=2,
                        per_level_scale=1.5, sh_degree=-1, mlp_width=64, n_hidden_layers=2)
@@ -81,8 +85,10 @@ def test_neural_query_other_shape(oracle_lib):
                sh_degree=0, mlp_width=64, n_hidden=2)
     scene = nrb.scenes.make_scene("ico", 1, env=False)
     prod, orc, _ = make_pair(scene, oracle_lib, 8, 8, weights=_weights(**net), nn_config=cfg)
+    prod.set_query_kernel(kernel)
     x = np.random.RandomState(5).uniform(0, 1, (1000, prod.input_dims())).astype(np.float32)
     err = rae_ok(prod.neural_query(x), orc.neural_query(x))
+    prod.set_query_kernel(0)
     assert np.percentile(err, 99) < 1e-2 and err.max() < 5e-2
 
 
