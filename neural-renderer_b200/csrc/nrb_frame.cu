@@ -129,8 +129,14 @@ __global__ void __launch_bounds__(128) k_trace_rays(const __grid_constant__ Mesh
     const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     TraceStats st{0u, 0u};
     if (i < n) {
-        Hit h = trace_mode<true>(m, mode, ld3(o, static_cast<uint32_t>(i)), ld3(d, static_cast<uint32_t>(i)), &st);
-        if (h.t >= 1e30f) h = Hit{1e30f, 0.0f, 0.0f, 0u};
+        Hit h;
+        if (mode == 3) {  // parity hook for the fused three-mode pass: t = ANY, u = FORWARD, v = BACKWARD distances
+            trace_multi(target_of(m), 7, ld3(o, i), ld3(d, i), h.t, h.u, h.v);
+            h.prim = 0u;
+        } else {
+            h = trace_mode<true>(m, mode, ld3(o, i), ld3(d, i), &st);
+            if (h.t >= 1e30f) h = Hit{1e30f, 0.0f, 0.0f, 0u};
+        }
         out[i] = h;
     }
     if (stats) {

@@ -162,8 +162,8 @@ __global__ void __launch_bounds__(512, 1)
             const int r0 = lane >> 2, c0 = (lane & 3) * 2;
 #pragma unroll
             for (int j = 0; j < WIDTH / 8; ++j) {
-                *reinterpret_cast<__half2*>(act + r0 * ldA + j * 8 + c0) = __halves2half2(leaky_h(acc[j][0]), leaky_h(acc[j][1]));
-                *reinterpret_cast<__half2*>(act + (r0 + 8) * ldA + j * 8 + c0) = __halves2half2(leaky_h(acc[j][2]), leaky_h(acc[j][3]));
+                *reinterpret_cast<uint32_t*>(act + r0 * ldA + j * 8 + c0) = leaky_pack2(acc[j][0], acc[j][1]);
+                *reinterpret_cast<uint32_t*>(act + (r0 + 8) * ldA + j * 8 + c0) = leaky_pack2(acc[j][2], acc[j][3]);
             }
             __syncwarp();
             W = layer == 0 ? wh : W + WIDTH * ldw;
@@ -214,7 +214,11 @@ int query_kernel() { return g_queryKernel; }
 int launch_neural_query(const NetDev& net, const float* in, size_t n, const int* dCount, __half* out,
                         cudaStream_t s) {
     if (n == 0) return 0;
-    if (g_queryKernel != 1 && neural_query_tc_supported(net)) return launch_neural_query_tc(net, in, n, dCount, out, s);
+    if ((g_queryKernel & 0xff) != 1 && neural_query_tc_supported(net)) {
+        NetDev tmp = net;
+        tmp.debug = g_queryKernel >> 8;
+        return launch_neural_query_tc(tmp, in, n, dCount, out, s);
+    }
     const SmemPlan p = plan_smem(net);
     if (p.warps <= 0) return -1;
     const int tiles = static_cast<int>((n + kRows - 1) / kRows);

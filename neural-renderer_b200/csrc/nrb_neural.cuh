@@ -19,6 +19,7 @@ struct NetDev {
     int nPoints, nLevels, nFeatures, shDegree, width, nHidden;
     int inputDims;        // 3*nPoints (+3 when shDegree > 0)
     int encDims;          // nPoints*nLevels*nFeatures + shDegree^2
+    int debug;            // experiments only: bit 0 = skip the table loads, bit 1 = skip the MLP
     uint32_t levelOffset[kMaxLevels];
     uint32_t levelSize[kMaxLevels];     // hashmap_size of the level (entries)
     uint32_t levelRes[kMaxLevels];

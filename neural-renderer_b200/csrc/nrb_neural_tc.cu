@@ -10,7 +10,7 @@
 //     one K=16 step, SBO = K*16 B between 8-row groups) and are read by the tensor core directly
 //     through the async proxy - no ldmatrix traffic through the LSU, which is what bounded the
 //     mma.sync kernel (ncu: L1/TEX 69 % busy, tensor pipe 29 %);
-//   * warp-specialised, persistent CTA of 16 warps: warps 4..15 gather and encode tile i+1 straight
+//   * warp-specialised, persistent CTA of 28 warps: warps 4..27 gather and encode tile i+1 straight
 //     into the layer-0 A operand X while warps 0..3 run the MLP of tile i: one elected thread issues
 //     tcgen05.mma (7 or 8 K-steps per layer) and commits to an mbarrier; the 128 epilogue threads
 //     read their query's row from TMEM (tcgen05.ld 32x32b), apply fp16 LeakyReLU and write the next
@@ -29,7 +29,7 @@ namespace {
 
 constexpr int kTileM = 128;
 constexpr int kMlpThreads = 128;    // warps 0..3: TMEM lane quarter = warp index
-constexpr int kEncThreads = 384;    // warps 4..15
+constexpr int kEncThreads = 768;    // warps 4..27
 constexpr int kInpStride = 17;      // floats per staged input row (odd stride: conflict-free)
 
 __device__ __forceinline__ uint32_t s32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
@@ -154,8 +154,7 @@ __device__ __forceinline__ void stage_weights(unsigned char* dst, const __half* 
 }
 
 __device__ __forceinline__ uint32_t pack_leaky(uint32_t a, uint32_t b) {
-    const __half2 h = __halves2half2(leaky_h(__uint_as_float(a)), leaky_h(__uint_as_float(b)));
-    return *reinterpret_cast<const uint32_t*>(&h);
+    return leaky_pack2(__uint_as_float(a), __uint_as_float(b));
 }
 __device__ __forceinline__ uint32_t pack_plain(uint32_t a, uint32_t b) {
     const __half2 h = __floats2half2_rn(__uint_as_float(a), __uint_as_float(b));
@@ -232,8 +231,8 @@ __global__ void __launch_bounds__(kMlpThreads + kEncThreads, 1)
                 const int p = pl / net.nLevels, level = pl - p * net.nLevels;
                 const float* x = inp + r * kInpStride + 3 * p;
                 __half* dst = reinterpret_cast<__half*>(X + canon_off(r, pl * F, EK));
-                if (F == 4) encode_item<4>(net, level, x, dst);
-                else encode_item<2>(net, level, x, dst);
+                if (F == 4) encode_item_paired<4>(net, level, x, dst);
+                else encode_item_paired<2>(net, level, x, dst);
             }
             if (shN > 0 && et < kTileM) {
                 __half sh[16];
@@ -256,6 +255,10 @@ __global__ void __launch_bounds__(kMlpThreads + kEncThreads, 1)
             const int q0 = tile * kTileM;
             mbar_wait(barXFull, it & 1);
             tc_fence_after();
+            if (net.debug & 2) {
+                if (tid == 0) mbar_arrive(barXEmpty);
+                continue;
+            }
             if (tid == 0) {
                 const uint32_t idesc = instr_desc(WIDTH);
                 const uint64_t a0 = smem_desc(descX, EK), b0 = smem_desc(s32(w0), EK);

@@ -217,38 +217,34 @@ __global__ void __launch_bounds__(kQueueThreads) k_bounce_begin(const __grid_con
             alive = sample_vertex(f, id, f4v(P), f4v(N), f4v(C), v3(C.w, M.x, M.y), bounce == 1, prev, org, wi, weight,
                                   pdf);
             carried = N.w;
-            // stage of this lane's trace sequence: 0/1 = early-termination outer/inner (ANY),
-            // 2 = shell entry (FORWARD), 3 = exit when starting inside (BACKWARD), 4 = re-entry
-            if (alive) stage = carried > 0.0f ? 0 : 2;
         }
-        // checkBounceEarlyTerminationKernel + traceOuterShellEntryFromRaysKernel as one convergent
-        // loop: every lane that still has a trace to do runs the same out-of-line traversal
-        Hit hEntry{1e30f, 0.0f, 0.0f, 0u};
-        float outerAnyT = 1e30f, baseOffset = 0.0f;
+        // checkBounceEarlyTerminationKernel + traceOuterShellEntryFromRaysKernel.  The three outer-shell
+        // queries of a bounce ray (ANY for early termination, FORWARD entry, BACKWARD exit when the
+        // origin is inside the shell) are ONE fused depth-first pass (trace_multi, exact per mode); the
+        // inner-shell ANY trace and the re-entry trace then run in a convergent loop over the
+        // out-of-line traversal so lanes at different steps still execute the same instructions.
+        float tAny = 1e30f, tFwd = 1e30f, tBwd = 1e30f;
+        if (alive) {
+            trace_multi(tOuter, (carried > 0.0f ? 1 : 0) | 2 | 4, org, wi, tAny, tFwd, tBwd);
+            nTrace += (carried > 0.0f ? 1u : 0u) + 1u + (tFwd >= 1e30f ? 1u : 0u);
+        }
+        const int afterTermination = tFwd < 1e30f ? 5 : (tBwd < 1e30f ? 4 : 5);  // 4 = re-entry trace needed
+        if (alive) stage = carried > 0.0f ? 1 : afterTermination;
+        Hit hEntry{tFwd, 0.0f, 0.0f, 0u};
+        float baseOffset = 0.0f;
         V3 entryOrigin = org;
         while (__any_sync(0xffffffffu, stage < 5)) {
             if (stage < 5) {
+                if (stage == 4) {
+                    baseOffset = tBwd + kSegEps;
+                    entryOrigin = org + wi * baseOffset;
+                }
                 const TraceTarget tgt = pick_target(stage == 1, tInner, tOuter);
-                const int mode = stage <= 1 ? TRACE_ANY : (stage == 3 ? TRACE_BACKWARD : TRACE_FORWARD);
-                const Hit h = trace_dyn(tgt, mode, stage == 4 ? entryOrigin : org, wi);
+                const Hit h = trace_dyn(tgt, stage == 1 ? TRACE_ANY : TRACE_FORWARD, stage == 4 ? entryOrigin : org, wi);
                 ++nTrace;
-                if (stage == 0) {
-                    outerAnyT = h.t;
-                    stage = 1;
-                } else if (stage == 1) {
-                    if (h.t < 1e30f && outerAnyT < 1e30f && h.t < outerAnyT) { alive = false; stage = 5; }
-                    else stage = 2;
-                } else if (stage == 2) {
-                    if (h.t < 1e30f) { hEntry = h; stage = 5; }
-                    else stage = 3;
-                } else if (stage == 3) {
-                    if (h.t < 1e30f) {
-                        baseOffset = h.t + kSegEps;
-                        entryOrigin = org + wi * baseOffset;
-                        stage = 4;
-                    } else {
-                        stage = 5;
-                    }
+                if (stage == 1) {
+                    if (h.t < 1e30f && tAny < 1e30f && h.t < tAny) { alive = false; stage = 5; }
+                    else stage = afterTermination;
                 } else {
                     hEntry = h;
                     stage = 5;

@@ -211,6 +211,117 @@ static __device__ __noinline__ Hit trace_dyn(TraceTarget m, int mode, V3 o, V3 d
     return best;
 }
 
+// Slab test split into its best-independent part (ok) and the entry distance; the reference's full
+// test is  ok && !(tNear > tMax).
+__device__ __forceinline__ bool slab_base(V3 o, V3 inv, float mnx, float mny, float mnz, float mxx, float mxy,
+                                          float mxz, float& tNear) {
+    const float kPad = 1e-10f;
+    mnx -= kPad; mny -= kPad; mnz -= kPad;
+    mxx += kPad; mxy += kPad; mxz += kPad;
+    float t1 = (mnx - o.x) * inv.x, t2 = (mxx - o.x) * inv.x;
+    float tmin = fminf(t1, t2), tmax = fmaxf(t1, t2);
+    t1 = (mny - o.y) * inv.y; t2 = (mxy - o.y) * inv.y;
+    tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
+    t1 = (mnz - o.z) * inv.z; t2 = (mxz - o.z) * inv.z;
+    tmin = fmaxf(tmin, fminf(t1, t2)); tmax = fminf(tmax, fmaxf(t1, t2));
+    tNear = tmin;
+    return !(tmax < 0.0f || tmin > tmax);
+}
+
+// Three closest-hit queries along ONE ray in ONE depth-first pass: bit 0 = ANY, bit 1 = FORWARD_ONLY,
+// bit 2 = BACKWARD_ONLY (`want` selects which are live).  Exact by construction: every node and
+// stack entry carries the set of modes whose own traversal (traceMeshWithMode run separately for
+// that mode) would have visited it - a mode stays in the set only while the node's entry distance
+// is not beyond THAT mode's current best t - and the near/far order depends on the boxes only, so
+// each mode sees its triangles in exactly the order of its separate traversal.  The bounce entry
+// needs all three on the outer shell (early-termination ANY, entry FORWARD, exit BACKWARD when the
+// origin is inside); one pass replaces up to three.
+__device__ __noinline__ static void trace_multi(TraceTarget m, int want, V3 o, V3 d, float& tAny, float& tFwd,
+                                                 float& tBwd) {
+    float best0 = 1e30f, best1 = 1e30f, best2 = 1e30f;
+    tAny = tFwd = tBwd = 1e30f;
+    if (m.numTriangles <= 0 || want == 0) return;
+    const V3 inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    float tn;
+    if (!slab_base(o, inv, m.bmin.x, m.bmin.y, m.bmin.z, m.bmax.x, m.bmax.y, m.bmax.z, tn) || tn > 1e30f) return;
+    int2 stack[kTraceStack];
+    unsigned char smask[kTraceStack];
+    int sp = 0, ref = m.rootRef, mask = want;
+    const NodePair* __restrict__ nodes = m.nodes;
+    const TriBlock* __restrict__ tris = m.tris;
+    auto live = [&](int set, float tNear) {
+        int out = 0;
+        if ((set & 1) && !(tNear > best0)) out |= 1;
+        if ((set & 2) && !(tNear > best1)) out |= 2;
+        if ((set & 4) && !(tNear > best2)) out |= 4;
+        return out;
+    };
+    for (;;) {
+        if (ref >= 0) {
+            const float4 a = __ldg(&nodes[ref].a), b = __ldg(&nodes[ref].b), c = __ldg(&nodes[ref].c);
+            const int4 k = __ldg(&nodes[ref].d);
+            float ln, rn;
+            const bool bl = slab_base(o, inv, a.x, a.y, a.z, a.w, b.x, b.y, ln);
+            const bool br = slab_base(o, inv, b.z, b.w, c.x, c.y, c.z, c.w, rn);
+            const int ml = bl ? live(mask, ln) : 0, mr = br ? live(mask, rn) : 0;
+            if (ml && mr) {
+                const bool rightFirst = rn < ln;
+                if (sp < kTraceStack) {
+                    stack[sp] = make_int2(rightFirst ? k.x : k.y, __float_as_int(rightFirst ? ln : rn));
+                    smask[sp++] = static_cast<unsigned char>(rightFirst ? ml : mr);
+                }
+                ref = rightFirst ? k.y : k.x;
+                mask = rightFirst ? mr : ml;
+                continue;
+            }
+            if (ml) { ref = k.x; mask = ml; continue; }
+            if (mr) { ref = k.y; mask = mr; continue; }
+        } else {
+            const int packed = ~ref;
+            const int first = packed >> kLeafCountBits;
+            const int end = first + (packed & ((1 << kLeafCountBits) - 1)) + 1;
+            for (int i = first; i < end; ++i) {
+                const float4 p = __ldg(&tris[i].p), q = __ldg(&tris[i].q), r = __ldg(&tris[i].r);
+                const float facing = dot(v3(p.w, q.w, r.w), d);
+                int acc = mask & 1;
+                if ((mask & 2) && !(facing >= 0.0f)) acc |= 2;
+                if ((mask & 4) && !(facing <= 0.0f)) acc |= 4;
+                if (!acc) continue;
+                const V3 e1 = v3(q.x, q.y, q.z), e2 = v3(r.x, r.y, r.z);
+                const V3 pv = cross(d, e2);
+                const float det = dot(e1, pv);
+                if (fabsf(det) < 1e-8f) continue;
+                const float invDet = 1.0f / det;
+                const V3 tv = o - v3(p.x, p.y, p.z);
+                const float u = dot(tv, pv) * invDet;
+                if (u < 0.0f || u > 1.0f) continue;
+                const V3 qv = cross(tv, e1);
+                const float v = dot(d, qv) * invDet;
+                if (v < 0.0f || u + v > 1.0f) continue;
+                const float t = dot(e2, qv) * invDet;
+                if (t <= 1e-8f || !(t > 1e-6f)) continue;
+                if ((acc & 1) && t < best0) best0 = t;
+                if ((acc & 2) && t < best1) best1 = t;
+                if ((acc & 4) && t < best2) best2 = t;
+            }
+        }
+        bool found = false;
+        while (sp > 0) {
+            --sp;
+            const int again = live(smask[sp], __int_as_float(stack[sp].y));
+            if (!again) continue;
+            ref = stack[sp].x;
+            mask = again;
+            found = true;
+            break;
+        }
+        if (!found) break;
+    }
+    tAny = best0;
+    tFwd = best1;
+    tBwd = best2;
+}
+
 template <bool STATS = false>
 __device__ __forceinline__ Hit trace_mode(const MeshDev& m, int mode, V3 o, V3 d, TraceStats* st = nullptr) {
     if (mode == TRACE_FORWARD) return trace_closest<TRACE_FORWARD, STATS>(m, o, d, st);

@@ -188,3 +188,17 @@ def test_matches_committed_reference_fixtures():
     assert np.percentile(err, 99) < 1e-2 and err.max() < 5e-2
     assert np.mean(got["neural_hit_flags"] != gold["neural_hit_flags"]) < 5e-3
     assert psnr8(got["neural_pixels"], gold["neural_pixels"]) > 30.0
+
+
+def test_fused_three_mode_traversal_is_exact(oracle_lib):
+    """trace_multi (one DFS for ANY + FORWARD + BACKWARD, used by the bounce entry) against three separate
+    reference traversals: distances must be bit-identical."""
+    scene = nrb.scenes.make_scene("ico", 4, additional=True, env=False)
+    prod, orc, eye = make_pair(scene, oracle_lib, 8, 8)
+    o, d = random_rays(30000, seed=321)
+    o[:10000] *= 0.3  # many origins inside the shells
+    for slot in (nrb.SLOT_OUTER, nrb.SLOT_INNER, nrb.SLOT_ORIGINAL):
+        fused = prod.trace_rays(slot, 3, o, d)
+        for mode, key in ((nrb.TRACE_ANY, "t"), (nrb.TRACE_FORWARD_ONLY, "u"), (nrb.TRACE_BACKWARD_ONLY, "v")):
+            ref = orc.trace_rays(slot, mode, o, d)
+            assert np.array_equal(fused[key], ref["t"]), (slot, mode)
