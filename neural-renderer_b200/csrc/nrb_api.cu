@@ -238,8 +238,15 @@ int relayout_mesh(nrb_renderer* r, MeshSlot& m, const nrb_mesh_desc* d) {
     };
     std::vector<NodePair> pairs;
     MeshDev& v = m.view;
-    std::memcpy(v.rootMin, src[0].bounds_min, 12);
-    std::memcpy(v.rootMax, src[0].bounds_max, 12);
+    // intersectAabb pads every box by 1e-10 before the slab test (src/mesh_traversal.cuh:67-69); the
+    // padded boxes are stored so the kernels skip 12 additions per node pair (same fp32 operations)
+    const float kPad = 1e-10f;
+    auto lo = [&](float x) { return x - kPad; };
+    auto hi = [&](float x) { return x + kPad; };
+    for (int k = 0; k < 3; ++k) {
+        v.rootMin[k] = lo(src[0].bounds_min[k]);
+        v.rootMax[k] = hi(src[0].bounds_max[k]);
+    }
     int maxDepth = 1;
     if (src[0].is_leaf) {
         if (!check_leaf(src[0])) return fail(NRB_ERR_INVALID, "bad root leaf");
@@ -277,9 +284,9 @@ int relayout_mesh(nrb_renderer* r, MeshSlot& m, const nrb_mesh_desc* d) {
             const nrb_bvh_node& L = src[kids[0]];
             const nrb_bvh_node& R = src[kids[1]];
             NodePair& p = pairs[it.pair];
-            p.a = make_float4(L.bounds_min[0], L.bounds_min[1], L.bounds_min[2], L.bounds_max[0]);
-            p.b = make_float4(L.bounds_max[1], L.bounds_max[2], R.bounds_min[0], R.bounds_min[1]);
-            p.c = make_float4(R.bounds_min[2], R.bounds_max[0], R.bounds_max[1], R.bounds_max[2]);
+            p.a = make_float4(lo(L.bounds_min[0]), lo(L.bounds_min[1]), lo(L.bounds_min[2]), hi(L.bounds_max[0]));
+            p.b = make_float4(hi(L.bounds_max[1]), hi(L.bounds_max[2]), lo(R.bounds_min[0]), lo(R.bounds_min[1]));
+            p.c = make_float4(lo(R.bounds_min[2]), hi(R.bounds_max[0]), hi(R.bounds_max[1]), hi(R.bounds_max[2]));
             p.d = make_int4(refs[0], refs[1], L.is_leaf ? L.count : 0, R.is_leaf ? R.count : 0);
         }
         v.rootRef = 0;

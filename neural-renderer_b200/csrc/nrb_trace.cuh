@@ -24,9 +24,8 @@ __host__ __device__ __forceinline__ int leaf_ref(int first, int count) {
 // intersectAabb, reference src/mesh_traversal.cuh:61-93 (same operations, same order).
 __device__ __forceinline__ bool slab(V3 o, V3 inv, float mnx, float mny, float mnz, float mxx, float mxy,
                                      float mxz, float tMax, float& tNear) {
-    const float kPad = 1e-10f;
-    mnx -= kPad; mny -= kPad; mnz -= kPad;
-    mxx += kPad; mxy += kPad; mxz += kPad;
+    // the reference's +-1e-10 padding of the box is applied once at upload (nrb_api.cu:relayout_mesh,
+    // same fp32 subtraction/addition), so the boxes arriving here are already padded
     float t1 = (mnx - o.x) * inv.x, t2 = (mxx - o.x) * inv.x;
     float tmin = fminf(t1, t2), tmax = fmaxf(t1, t2);
     t1 = (mny - o.y) * inv.y; t2 = (mxy - o.y) * inv.y;
@@ -215,9 +214,6 @@ static __device__ __noinline__ Hit trace_dyn(TraceTarget m, int mode, V3 o, V3 d
 // test is  ok && !(tNear > tMax).
 __device__ __forceinline__ bool slab_base(V3 o, V3 inv, float mnx, float mny, float mnz, float mxx, float mxy,
                                           float mxz, float& tNear) {
-    const float kPad = 1e-10f;
-    mnx -= kPad; mny -= kPad; mnz -= kPad;
-    mxx += kPad; mxy += kPad; mxz += kPad;
     float t1 = (mnx - o.x) * inv.x, t2 = (mxx - o.x) * inv.x;
     float tmin = fminf(t1, t2), tmax = fmaxf(t1, t2);
     t1 = (mny - o.y) * inv.y; t2 = (mxy - o.y) * inv.y;
