@@ -306,10 +306,11 @@ def main():
     per_kernel = {k: {"ms_per_step": v[0] / a.steps, "launches_per_step": v[1] / a.steps, "share": v[0] / total_stage_ms}
                   for k, v in sorted(stages.items(), key=lambda kv: -kv[1][0])}
     roof = None
-    if "k_neural_query" in stages and a.mode == "neural":
-        q_ms = stages["k_neural_query"][0] / a.steps
+    qkeys = [k for k in stages if k.startswith("k_neural_query") or k.startswith("k_query_")]
+    if qkeys and a.mode == "neural":
+        q_ms = sum(stages[k][0] for k in qkeys) / a.steps
         tf = neural_q * FLOPS_PER_QUERY / (q_ms * 1e-3) / 1e12
-        roof = {"kernel": "k_neural_query", "bound": "tensor", "achieved": tf, "peak": pk["tf_sustained"], "unit": "TFLOP/s",
+        roof = {"kernel": "+".join(sorted(qkeys)), "bound": "tensor", "achieved": tf, "peak": pk["tf_sustained"], "unit": "TFLOP/s",
                 "frac": tf / pk["tf_sustained"], "traffic": None, "peak_source": pk["src"] + " sustained bf16 (fp16 same pipe rate)",
                 "queries_per_step": neural_q, "flops_per_query": FLOPS_PER_QUERY, "ms_per_step": q_ms,
                 "hbm_gbs": neural_q * HBM_BYTES_PER_QUERY / (q_ms * 1e-3) / 1e9,

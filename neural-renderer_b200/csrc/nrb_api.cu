@@ -109,7 +109,7 @@ struct nrb_renderer {
     // network
     nrb_nn_config cfg{};
     NetDev net{};
-    DevBuf grid, mlp;
+    DevBuf grid, mlp, packedW, xt;
     size_t gridParams = 0, mlpParams = 0;
     bool weightsLoaded = false;
 
@@ -456,6 +456,12 @@ int nrb_load_weights(nrb_renderer* r, const void* fp16, size_t bytes, int swap_o
     NRB_CUDA(r->mlp.upload(srcMlp, r->mlpParams * 2, r->stream));
     r->net.grid = r->grid.as<__half>();
     r->net.mlp = r->mlp.as<__half>();
+    r->net.packedW = nullptr;
+    if (split_query_supported(r->net)) {  // UMMA-operand image of the layers for k_query_mlp
+        NRB_CUDA(r->packedW.alloc(split_packed_bytes(r->net)));
+        r->net.packedW = r->packedW.p;
+        if (split_prepack(r->net, r->packedW.p, r->stream) != 0) return fail(NRB_ERR_CUDA, "weight pre-pack launch failed");
+    }
     r->weightsLoaded = true;
     return NRB_OK;
 }
@@ -620,6 +626,27 @@ int ensure_state(nrb_renderer* r, size_t nElems, size_t localPixels, size_t fram
     return NRB_OK;
 }
 
+// Scratch for the split query's encoded tiles: at most 2^22 rows (the launcher walks larger batches
+// in chunks), grown on demand.
+int ensure_xt(nrb_renderer* r, size_t rows) {
+    if (!r->net.packedW || !split_query_supported(r->net)) {
+        r->net.xt = nullptr;
+        r->net.xtRows = 0;
+        return NRB_OK;
+    }
+    size_t cap = (rows + 127) / 128 * 128;
+    if (cap > (1u << 22)) cap = 1u << 22;
+    if (cap < 128) cap = 128;
+    const size_t need = split_xt_bytes(r->net, cap);
+    if (r->xt.bytes < need) {
+        NRB_CUDA(cudaStreamSynchronize(r->stream));
+        NRB_CUDA(r->xt.alloc(need));
+    }
+    r->net.xt = r->xt.p;
+    r->net.xtRows = static_cast<uint32_t>(r->xt.bytes / split_xt_bytes(r->net, 128) * 128);
+    return NRB_OK;
+}
+
 // Turn the event marks of the last profiled frame into per-kernel totals.
 int drain_profiler(nrb_renderer* r) {
     if (!r->profPending) return NRB_OK;
@@ -678,6 +705,10 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     if (nElems >= (1ull << 31)) return fail(NRB_ERR_INVALID, "width*height*spp exceeds 2^31 elements; render in smaller spp batches");
     int rc = ensure_state(r, nElems, localPixels, framePixels);
     if (rc != NRB_OK) return rc;
+    if (r->useNeuralQuery && r->weightsLoaded) {
+        rc = ensure_xt(r, nElems);
+        if (rc != NRB_OK) return rc;
+    }
 
     // accumulation reset rules (:2190-2217)
     bool cameraMoved = !r->hasLastCamera;
@@ -926,6 +957,10 @@ int nrb_neural_query(nrb_renderer* r, const float* d_inputs, size_t n, void* d_o
     if (!r->weightsLoaded) return fail(NRB_ERR_STATE, "no weights loaded");
     if (n >= (1ull << 31)) return fail(NRB_ERR_INVALID, "too many queries for one call");
     NRB_CUDA(cudaSetDevice(r->device));
+    {
+        const int rcx = ensure_xt(r, n);
+        if (rcx != NRB_OK) return rcx;
+    }
     if (launch_neural_query(r->net, d_inputs, n, nullptr, static_cast<__half*>(d_outputs_fp16), r->stream) < 0)
         return fail(NRB_ERR_INVALID, "unsupported network shape");
     NRB_CUDA(cudaGetLastError());

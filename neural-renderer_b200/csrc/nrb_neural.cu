@@ -214,7 +214,13 @@ int query_kernel() { return g_queryKernel; }
 int launch_neural_query(const NetDev& net, const float* in, size_t n, const int* dCount, __half* out,
                         cudaStream_t s) {
     if (n == 0) return 0;
-    if ((g_queryKernel & 0xff) != 1 && neural_query_tc_supported(net)) {
+    const int which = g_queryKernel & 0xff;
+    if ((which == 0 || which == 3) && net.xtRows > 0 && net.packedW && split_query_supported(net)) {
+        NetDev tmp = net;
+        tmp.debug = g_queryKernel >> 8;
+        return launch_split_query(tmp, in, n, dCount, out, s);
+    }
+    if (which != 1 && neural_query_tc_supported(net)) {
         NetDev tmp = net;
         tmp.debug = g_queryKernel >> 8;
         return launch_neural_query_tc(tmp, in, n, dCount, out, s);

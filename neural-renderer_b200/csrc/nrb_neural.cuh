@@ -19,7 +19,12 @@ struct NetDev {
     int nPoints, nLevels, nFeatures, shDegree, width, nHidden;
     int inputDims;        // 3*nPoints (+3 when shDegree > 0)
     int encDims;          // nPoints*nLevels*nFeatures + shDegree^2
-    int debug;            // experiments only: bit 0 = skip the table loads, bit 1 = skip the MLP
+    int debug;            // experiments only: bit 0 = skip the table loads, bit 1 = skip the MLP,
+                          // bit 2 = split encoder gathers from global memory, bit 3 = 1024-row chunks
+    // split query (nrb_query_split.cu): weights pre-packed as UMMA operands, encoded-row scratch
+    const void* packedW;  // split_packed_bytes(net) bytes, written by split_prepack()
+    void* xt;             // [xtRows/128][EK/8][128][8] fp16 encoded tiles
+    uint32_t xtRows;      // capacity of xt in rows (multiple of 128); 0 = split path unavailable
     uint32_t levelOffset[kMaxLevels];
     uint32_t levelSize[kMaxLevels];     // hashmap_size of the level (entries)
     uint32_t levelRes[kMaxLevels];
@@ -32,11 +37,20 @@ struct NetDev {
 // count is read on the device from *dCount and n is only the launch bound), outputs fp16 [n][16].
 int launch_neural_query(const NetDev& net, const float* in, size_t n, const int* dCount, __half* out,
                         cudaStream_t s);
-// The tcgen05/TMEM kernel (nrb_neural_tc.cu) and the kernel choice: 0 = automatic (tcgen05 when the
-// shape is supported), 1 = force the mma.sync kernel, 2 = force tcgen05.
+// The tcgen05/TMEM kernel (nrb_neural_tc.cu) and the kernel choice: 0 = automatic (split when the
+// shape is supported and scratch is attached, else fused tcgen05, else mma.sync), 1 = mma.sync kernel,
+// 2 = fused tcgen05 kernel, 3 = split encode + tcgen05 MLP.
 bool neural_query_tc_supported(const NetDev& net);
 int launch_neural_query_tc(const NetDev& net, const float* in, size_t n, const int* dCount, __half* out,
                            cudaStream_t s);
+// The split query (nrb_query_split.cu): k_query_encode (one hash-grid level per CTA, the level's table
+// resident in shared memory) -> encoded tiles in HBM/L2 -> k_query_mlp (tcgen05, two tiles in flight per
+// SM, activations fed by bulk async copies).  Kernel choice 3 (and the automatic default when supported).
+bool split_query_supported(const NetDev& net);
+size_t split_packed_bytes(const NetDev& net);
+size_t split_xt_bytes(const NetDev& net, size_t rows);           // rows rounded up to 128 inside
+int split_prepack(const NetDev& net, void* packedW, cudaStream_t s);
+int launch_split_query(const NetDev& net, const float* in, size_t n, const int* dCount, __half* out, cudaStream_t s);
 void set_query_kernel(int which);
 int query_kernel();
 // Bytes of dynamic shared memory the query kernel needs for this network (0 = unsupported shape).

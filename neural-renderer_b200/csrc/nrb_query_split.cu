@@ -1,0 +1,531 @@
+// nrb_query_split.cu — the neural query as two kernels sized for the two different machines it needs.
+//
+// Why split (ncu on the fused kernel, profiles/r1_v2_*): with weights (128 KB) and activation tiles in
+// shared memory there is no room left for the hash tables, so every one of the 192 corner fetches per
+// query is an L2 sector request (fused kernel: 1.05 G queries/s; 2.5 G/s with the table loads removed).
+// The hash grid of the reference network is 8 levels x 128 KB: ONE level fits one SM's shared memory.
+//
+//   k_query_encode  grid = L x S CTAs, CTA (level, slice): stages its level's table in shared memory
+//                   once, then encodes that level for every query of its slice of 128-query tiles
+//                   (P points x 8 corners, tiny-cuda-nn arithmetic bit-faithful: fp32 position, u32
+//                   coherent-prime hash, fp16 __hfma2 corner chain in corner order) and writes the
+//                   level's columns of the encoded tile.  The spherical harmonics and the K padding
+//                   are spread over the level CTAs by row (row % L == level).
+//   k_query_mlp     persistent, one CTA per SM, all layer weights resident in shared memory as K-major
+//                   UMMA operands (pre-packed once at weight load: one bulk copy per CTA).  A producer
+//                   thread streams encoded tiles in with cp.async.bulk; one thread issues tcgen05.mma
+//                   for TWO tiles in flight, offset by half a tile, so that the TMEM -> LeakyReLU ->
+//                   fp16 -> shared-memory epilogue of one tile (4 warps per tile) runs under the MMAs of
+//                   the other; accumulators live in TMEM (one WIDTH-column block per tile in flight).
+//
+// Encoded tile layout (global and shared alike): [tile][k/8][row 0..127][8 halfs] — every 16-byte
+// k-chunk of 128 rows is contiguous (2 KB), which is a legal un-swizzled K-major UMMA operand with
+// LBO = 2048 (between k-chunks) and SBO = 128 (between 8-row groups), is written by the encoder with
+// full-sector stores and is fetched by the MLP kernel as ONE contiguous bulk copy.
+// The K order of layer 0 is permuted to level-major (k' = level*(P*F) + point*F + f; tiny-cuda-nn has
+// k = (point*L + level)*F + f) so that a level CTA owns a contiguous K range; W0's columns are
+// permuted identically at pre-pack time, so the products summed per neuron are the same set.
+#include <cuda_runtime.h>
+
+#include "nrb_encode.cuh"
+#include "nrb_frame.cuh"
+#include "nrb_tc.cuh"
+
+namespace nrb {
+
+namespace {
+
+constexpr int kTileM = 128;
+constexpr int kEncThreads = 1024;
+constexpr int kMlpThreads = 320;  // warp 0 producer, warp 1 MMA issuer, warps 2-5 / 6-9 epilogues of tile A / B
+constexpr uint32_t kSmemMax = 227u * 1024u;
+
+// Byte offset of element (row, k) of a weight matrix with K columns in the packed (UMMA K-major,
+// un-swizzled, LBO = 128, SBO = K*16) layout.
+__host__ __device__ __forceinline__ uint32_t canon_off(int row, int k, int K) {
+    return static_cast<uint32_t>((row >> 3) * (K * 16) + (k >> 3) * 128 + (row & 7) * 16 + (k & 7) * 2);
+}
+
+struct SplitPlan {
+    int ek;                       // layer-0 K, padded to 16
+    uint32_t w0Bytes, whBytes, wlBytes, packedBytes;
+    uint32_t xBytes, hBytes;      // one encoded tile / one hidden tile in shared memory
+    uint32_t offW, offX, offH, offBar, mlpSmem;
+    uint32_t encSmem;             // table bytes staged by an encoder CTA (largest level that fits)
+    int slices;                   // encoder CTAs per level
+};
+
+SplitPlan make_plan(const NetDev& net) {
+    SplitPlan p{};
+    const uint32_t W = net.width;
+    p.ek = (net.encDims + 15) & ~15;
+    p.w0Bytes = W * p.ek * 2;
+    p.whBytes = (net.nHidden - 1) * W * W * 2;
+    p.wlBytes = 16 * W * 2;
+    p.packedBytes = p.w0Bytes + p.whBytes + p.wlBytes;
+    p.xBytes = kTileM * p.ek * 2;
+    p.hBytes = kTileM * W * 2;
+    uint32_t o = 0;
+    p.offW = o; o += p.packedBytes;
+    p.offX = o; o += p.xBytes;
+    p.offH = o; o += 2 * p.hBytes;
+    p.offBar = o; o += 128;
+    p.mlpSmem = o;
+    uint32_t best = 0;
+    for (int l = 0; l < net.nLevels; ++l) {
+        const uint64_t bytes = static_cast<uint64_t>(net.levelSize[l]) * net.nFeatures * 2;
+        if (bytes <= 200u * 1024u && bytes > best) best = static_cast<uint32_t>(bytes);
+    }
+    p.encSmem = best;
+    p.slices = net.nLevels > 0 ? (148 / net.nLevels > 0 ? 148 / net.nLevels : 1) : 1;
+    return p;
+}
+
+// ---- weight pre-pack -----------------------------------------------------------------------------
+// tiny-cuda-nn parameter layout (row-major [out][in], W0 | W1.. | Wlast) -> the shared-memory image of
+// k_query_mlp.  One thread per (matrix row, 8-column chunk).
+__global__ void k_pack_weights(const __grid_constant__ NetDev net, unsigned char* dst, int ek) {
+    const int W = net.width, E = net.encDims, H = net.nHidden;
+    const int P = net.nPoints, L = net.nLevels, F = net.nFeatures, PLF = P * L * F;
+    const int c0 = W * (ek >> 3), ch = (H - 1) * W * (W >> 3), cl = 16 * (W >> 3);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < c0 + ch + cl; i += gridDim.x * blockDim.x) {
+        __half v[8];
+        uint32_t off;
+        if (i < c0) {
+            const int r = i / (ek >> 3), k8 = (i - r * (ek >> 3)) << 3;
+            for (int j = 0; j < 8; ++j) {
+                const int kp = k8 + j;  // our K index -> tiny-cuda-nn column
+                int c = kp;
+                if (kp < PLF) {
+                    const int level = kp / (P * F), rem = kp - level * (P * F), p = rem / F, f = rem - p * F;
+                    c = (p * L + level) * F + f;
+                }
+                v[j] = kp < E ? net.mlp[static_cast<size_t>(r) * E + c] : __float2half_rn(0.0f);
+            }
+            off = canon_off(r, k8, ek);
+        } else if (i < c0 + ch) {
+            const int t = i - c0, per = W * (W >> 3), l = t / per, u = t - l * per;
+            const int r = u / (W >> 3), k8 = (u - r * (W >> 3)) << 3;
+            const __half* src = net.mlp + static_cast<size_t>(W) * E + static_cast<size_t>(l) * W * W;
+            for (int j = 0; j < 8; ++j) v[j] = src[static_cast<size_t>(r) * W + k8 + j];
+            off = static_cast<uint32_t>(W * ek * 2 + l * W * W * 2) + canon_off(r, k8, W);
+        } else {
+            const int u = i - c0 - ch, r = u / (W >> 3), k8 = (u - r * (W >> 3)) << 3;
+            const __half* src = net.mlp + static_cast<size_t>(W) * E + static_cast<size_t>(H - 1) * W * W;
+            for (int j = 0; j < 8; ++j) v[j] = src[static_cast<size_t>(r) * W + k8 + j];
+            off = static_cast<uint32_t>(W * ek * 2 + (H - 1) * W * W * 2) + canon_off(r, k8, W);
+        }
+        *reinterpret_cast<uint4*>(dst + off) = *reinterpret_cast<const uint4*>(v);
+    }
+}
+
+// ---- encoder -------------------------------------------------------------------------------------
+template <int F, bool SMEM>
+__device__ __forceinline__ void load_entry(const unsigned char* gtable, uint32_t stable, uint32_t byteOff, uint32_t (&raw)[F / 2]) {
+    if (SMEM) {
+        if (F == 4) {
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(raw[0]), "=r"(raw[F / 2 - 1]) : "r"(stable + byteOff));
+        } else {
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(raw[0]) : "r"(stable + byteOff));
+        }
+    } else {
+        if (F == 4) {
+            const uint2 v = __ldg(reinterpret_cast<const uint2*>(gtable + byteOff));
+            raw[0] = v.x;
+            raw[F / 2 - 1] = v.y;
+        } else {
+            raw[0] = __ldg(reinterpret_cast<const uint32_t*>(gtable + byteOff));
+        }
+    }
+}
+
+struct LevelInfo {
+    float scale;
+    uint32_t res, size, mask;  // mask = (size - 1) * entryBytes when size is a power of two
+    bool dense, pow2;
+};
+
+// One (query, point) of this CTA's level: 8 corners, tiny-cuda-nn's arithmetic (see nrb_encode.cuh
+// encode_item, to which this is bit-identical; only the address generation is arranged differently).
+template <int F, bool SMEM>
+__device__ __forceinline__ void encode_point(const LevelInfo& lv, const unsigned char* gtable, uint32_t stable, float x0,
+                                             float x1, float x2, uint32_t (&acc)[F / 2]) {
+    constexpr uint32_t kShift = F == 4 ? 3 : 2;  // log2(entry bytes)
+    float w[3];
+    uint32_t g[3];
+    const float xs[3] = {x0, x1, x2};
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        const float p = fmaf(lv.scale, xs[d], 0.5f);
+        const float fl = floorf(p);
+        g[d] = static_cast<uint32_t>(static_cast<int>(fl));
+        w[d] = p - fl;
+    }
+    uint32_t off[8];
+    if (!lv.dense && lv.pow2) {
+        // (x ^ y*P1 ^ z*P2) & (size-1), scaled to bytes: mask and scale the three terms once, then one
+        // three-input XOR per corner.
+        const uint32_t ax0 = (g[0] << kShift) & lv.mask, ax1 = ((g[0] + 1u) << kShift) & lv.mask;
+        const uint32_t hy = g[1] * 2654435761u, hz = g[2] * 805459861u;
+        const uint32_t ay0 = (hy << kShift) & lv.mask, ay1 = ((hy + 2654435761u) << kShift) & lv.mask;
+        const uint32_t az0 = (hz << kShift) & lv.mask, az1 = ((hz + 805459861u) << kShift) & lv.mask;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) off[c] = ((c & 1) ? ax1 : ax0) ^ ((c & 2) ? ay1 : ay0) ^ ((c & 4) ? az1 : az0);
+    } else {
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+            off[c] = level_index(lv.dense, lv.pow2, lv.size, lv.res, g[0] + (c & 1), g[1] + ((c >> 1) & 1), g[2] + ((c >> 2) & 1))
+                     << kShift;
+    }
+    uint32_t raw[8][F / 2];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) load_entry<F, SMEM>(gtable, stable, off[c], raw[c]);
+    __half2 a[F / 2];
+#pragma unroll
+    for (int k = 0; k < F / 2; ++k) a[k] = __float2half2_rn(0.0f);
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        float wt = 1.0f;
+#pragma unroll
+        for (int d = 0; d < 3; ++d) wt *= (c & (1 << d)) ? w[d] : 1.0f - w[d];
+        const __half2 wh = __half2half2(__float2half_rn(wt));
+#pragma unroll
+        for (int k = 0; k < F / 2; ++k) a[k] = __hfma2(wh, *reinterpret_cast<const __half2*>(&raw[c][k]), a[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < F / 2; ++k) acc[k] = *reinterpret_cast<const uint32_t*>(&a[k]);
+}
+
+template <int F, bool SMEM>
+__device__ __forceinline__ void encode_tasks(const NetDev& net, const LevelInfo& lv, int level, const unsigned char* gtable,
+                                             uint32_t stable, const float* __restrict__ in, int rowBase, int rowEnd,
+                                             int tiles, int slice, int slices, unsigned char* __restrict__ xt, int ek) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nWarps = blockDim.x >> 5;
+    const int P = net.nPoints, D = net.inputDims, L = net.nLevels;
+    const int tasksPerTile = 4 * P + 1;
+    const int myTiles = (tiles - slice + slices - 1) / slices;
+    const int PLF = P * L * F, shN = net.shDegree * net.shDegree, E = net.encDims;
+    const uint32_t tileBytes = static_cast<uint32_t>(ek) * kTileM * 2;
+    for (int task = warp; task < myTiles * tasksPerTile; task += nWarps) {
+        const int tl = task / tasksPerTile, j = task - tl * tasksPerTile;
+        const int tile = slice + tl * slices;
+        unsigned char* tbase = xt + static_cast<size_t>(tile) * tileBytes;
+        if (j < 4 * P) {
+            const int p = j >> 2, r = ((j & 3) << 5) + lane;
+            const int row = rowBase + tile * kTileM + r;
+            if (row < rowEnd) {
+                const float* x = in + static_cast<size_t>(row) * D + 3 * p;
+                uint32_t acc[F / 2];
+                encode_point<F, SMEM>(lv, gtable, stable, __ldg(x), __ldg(x + 1), __ldg(x + 2), acc);
+                const int kp = level * (P * F) + p * F;
+                unsigned char* dst = tbase + ((kp >> 3) * kTileM + r) * 16 + (kp & 7) * 2;
+                if (F == 4) *reinterpret_cast<uint2*>(dst) = make_uint2(acc[0], acc[F / 2 - 1]);
+                else *reinterpret_cast<uint32_t*>(dst) = acc[0];
+            }
+        } else {
+            // spherical harmonics + K padding for the rows this level owns (row % L == level)
+            for (int r = level + lane * L; r < kTileM; r += 32 * L) {
+                const int row = rowBase + tile * kTileM + r;
+                if (row >= rowEnd) continue;
+                __half tail[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) tail[i] = __float2half_rn(0.0f);
+                if (shN > 0) {
+                    const float* dsrc = in + static_cast<size_t>(row) * D + 3 * P;
+                    const float d3[3] = {__ldg(dsrc), __ldg(dsrc + 1), __ldg(dsrc + 2)};
+                    encode_sh(net.shDegree, d3, tail);
+                }
+                // columns [PLF, ek): shN harmonics then zeros; PLF % 8 == 0 is a support condition
+                for (int k = PLF; k < ek; k += 8)
+                    *reinterpret_cast<uint4*>(tbase + ((k >> 3) * kTileM + r) * 16) = *reinterpret_cast<const uint4*>(tail + (k - PLF));
+            }
+            (void)E;
+        }
+    }
+}
+
+template <int F>
+__global__ void __launch_bounds__(kEncThreads, 1)
+    k_query_encode(const __grid_constant__ NetDev net, const float* __restrict__ in, int n, const int* dCount, int rowBase,
+                   int chunkRows, unsigned char* __restrict__ xt, int ek, uint32_t smemBytes) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    if (dCount) {
+        const int dn = *dCount;
+        n = dn < n ? dn : n;
+    }
+    int rowEnd = rowBase + chunkRows;
+    if (n < rowEnd) rowEnd = n;
+    if (rowEnd <= rowBase) return;
+    const int tiles = (rowEnd - rowBase + kTileM - 1) / kTileM;
+    const int L = net.nLevels, slices = gridDim.x / L;
+    const int level = blockIdx.x % L, slice = blockIdx.x / L;
+    if (slice >= tiles || slice >= slices) return;
+
+    LevelInfo lv;
+    lv.scale = net.levelScale[level];
+    lv.res = net.levelRes[level];
+    lv.size = net.levelSize[level];
+    lv.dense = net.levelDense[level] != 0;
+    lv.pow2 = net.levelPow2[level] != 0;
+    lv.mask = (lv.size - 1u) * (F * 2u);
+    const unsigned char* gtable = reinterpret_cast<const unsigned char*>(net.grid + static_cast<size_t>(net.levelOffset[level]) * F);
+    const uint32_t tableBytes = lv.size * F * 2u;
+    const bool staged = tableBytes <= smemBytes && !(net.debug & 4);
+    if (staged) {
+        for (uint32_t i = threadIdx.x * 16u; i < tableBytes; i += blockDim.x * 16u)
+            *reinterpret_cast<uint4*>(smem + i) = __ldg(reinterpret_cast<const uint4*>(gtable + i));
+        __syncthreads();
+        encode_tasks<F, true>(net, lv, level, gtable, tc::s32(smem), in, rowBase, rowEnd, tiles, slice, slices, xt, ek);
+    } else {
+        encode_tasks<F, false>(net, lv, level, gtable, 0u, in, rowBase, rowEnd, tiles, slice, slices, xt, ek);
+    }
+}
+
+// ---- MLP -----------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t pack_leaky(uint32_t a, uint32_t b) { return leaky_pack2(__uint_as_float(a), __uint_as_float(b)); }
+__device__ __forceinline__ uint32_t pack_plain(uint32_t a, uint32_t b) {
+    const __half2 h = __floats2half2_rn(__uint_as_float(a), __uint_as_float(b));
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+// Barrier block at plan.offBar: [0] weights landed, [1] X full, [2] X empty, [3,4] MMA done (tile A, B),
+// [5,6] epilogue done (tile A, B), then the TMEM base address.
+template <int WIDTH>
+__global__ void __launch_bounds__(kMlpThreads, 1)
+    k_query_mlp(const __grid_constant__ NetDev net, int n, const int* dCount, int rowBase, int chunkRows,
+                const unsigned char* __restrict__ xt, __half* __restrict__ out, const __grid_constant__ SplitPlan plan) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (dCount) {
+        const int dn = *dCount;
+        n = dn < n ? dn : n;
+    }
+    int rowEnd = rowBase + chunkRows;
+    if (n < rowEnd) rowEnd = n;
+    if (rowEnd <= rowBase) return;
+    const int tiles = (rowEnd - rowBase + kTileM - 1) / kTileM;
+    if (static_cast<int>(blockIdx.x) >= tiles) return;
+    const int nMine = (tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+
+    const int EK = plan.ek, H = net.nHidden, LAYERS = H + 1;
+    unsigned char* wsm = smem + plan.offW;
+    unsigned char* X = smem + plan.offX;
+    unsigned char* Hb = smem + plan.offH;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + plan.offBar);
+    uint64_t* barW = bars + 0;
+    uint64_t* barXFull = bars + 1;
+    uint64_t* barXEmpty = bars + 2;
+    uint64_t* barMma = bars + 3;   // [2]
+    uint64_t* barEpi = bars + 5;   // [2]
+    uint32_t* tmemSlot = reinterpret_cast<uint32_t*>(bars + 7);
+
+    if (tid == 0) {
+        tc::mbar_init(barW, 1);
+        tc::mbar_init(barXFull, 1);
+        tc::mbar_init(barXEmpty, 1);
+        tc::mbar_init(barMma + 0, 1);
+        tc::mbar_init(barMma + 1, 1);
+        tc::mbar_init(barEpi + 0, 4);
+        tc::mbar_init(barEpi + 1, 4);
+        tc::mbar_init_fence();
+    }
+    if (warp == 0) tc::tmem_alloc(tmemSlot, 2 * WIDTH);
+    tc::fence_before();
+    __syncthreads();
+    tc::fence_after();
+    const uint32_t tmem = *tmemSlot;
+
+    if (warp == 0) {
+        // ===================== producer: weights once, then one encoded tile per X-slot turn ==========
+        if (lane == 0) {
+            tc::mbar_expect_tx(barW, plan.packedBytes);
+            for (uint32_t o = 0; o < plan.packedBytes; o += 32768u) {
+                const uint32_t b = plan.packedBytes - o < 32768u ? plan.packedBytes - o : 32768u;
+                tc::bulk_g2s(wsm + o, static_cast<const unsigned char*>(net.packedW) + o, b, barW);
+            }
+            for (int k = 0; k < nMine; ++k) {
+                const int tile = blockIdx.x + k * gridDim.x;
+                tc::mbar_wait(barXEmpty, (k & 1) ^ 1);
+                tc::mbar_expect_tx(barXFull, plan.xBytes);
+                tc::bulk_g2s(X, xt + static_cast<size_t>(tile) * plan.xBytes, plan.xBytes, barXFull);
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer: two tiles in flight, offset by half a tile =================
+        if (lane == 0) {
+            tc::mbar_wait(barW, 0);
+            tc::fence_after();
+            const int nT[2] = {(nMine + 1) >> 1, nMine >> 1};
+            const int delay = LAYERS >> 1;
+            const int total = 2 * (nT[0] * LAYERS > nT[1] * LAYERS + delay ? nT[0] * LAYERS : nT[1] * LAYERS + delay);
+            uint32_t epiPhase[2] = {0u, 0u};
+            uint32_t xUse = 0;
+            const uint32_t wBase = tc::s32(wsm);
+            for (int s = 0; s < total; ++s) {
+                const int c = s & 1;
+                const int idx = (s >> 1) - (c ? delay : 0);
+                if (idx < 0) continue;
+                const int tk = idx / LAYERS, layer = idx - tk * LAYERS;
+                if (tk >= nT[c]) continue;
+                const uint32_t acc = tmem + static_cast<uint32_t>(c * WIDTH);
+                if (layer == 0) {
+                    if (tk > 0) {  // the previous tile's output epilogue has drained the accumulator
+                        tc::mbar_wait(barEpi + c, epiPhase[c]);
+                        epiPhase[c] ^= 1u;
+                    }
+                    tc::mbar_wait(barXFull, xUse & 1u);
+                    ++xUse;
+                    tc::fence_after();
+                    const uint32_t idesc = tc::instr_desc(kTileM, WIDTH);
+                    const uint64_t a0 = tc::smem_desc(tc::s32(X), 2048u, 128u);
+                    const uint64_t b0 = tc::smem_desc(wBase, 128u, static_cast<uint32_t>(EK) * 16u);
+                    for (int k = 0; k < EK / 16; ++k)
+                        tc::mma_f16(acc, a0 + static_cast<uint64_t>(256u * k), b0 + static_cast<uint64_t>(16u * k), idesc, k > 0);
+                    tc::commit(barXEmpty);
+                    tc::commit(barMma + c);
+                } else {
+                    tc::mbar_wait(barEpi + c, epiPhase[c]);
+                    epiPhase[c] ^= 1u;
+                    tc::fence_after();
+                    const bool last = layer == H;
+                    const uint32_t idesc = tc::instr_desc(kTileM, last ? 16 : WIDTH);
+                    const uint32_t wOff = plan.w0Bytes + static_cast<uint32_t>(layer - 1) * WIDTH * WIDTH * 2u;
+                    const uint64_t a0 = tc::smem_desc(tc::s32(Hb + c * plan.hBytes), 2048u, 128u);
+                    const uint64_t b0 = tc::smem_desc(wBase + wOff, 128u, static_cast<uint32_t>(WIDTH) * 16u);
+                    for (int k = 0; k < WIDTH / 16; ++k)
+                        tc::mma_f16(acc, a0 + static_cast<uint64_t>(256u * k), b0 + static_cast<uint64_t>(16u * k), idesc, k > 0);
+                    tc::commit(barMma + c);
+                }
+            }
+        }
+    } else {
+        // ===================== epilogue warps: TMEM -> LeakyReLU -> fp16 -> next layer's A operand ====
+        const int c = (warp - 2) >> 2;              // tile context
+        const int quarter = warp & 3;               // the TMEM lane quarter this warp may read
+        const int row = quarter * 32 + lane;
+        const uint32_t acc = tmem + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(c * WIDTH);
+        unsigned char* Hc = Hb + c * plan.hBytes;
+        const int nT = c == 0 ? (nMine + 1) >> 1 : nMine >> 1;
+        uint32_t phase = 0;
+        for (int tk = 0; tk < nT; ++tk) {
+            const int tile = blockIdx.x + (2 * tk + c) * gridDim.x;
+            const int q = rowBase + tile * kTileM + row;
+            for (int layer = 0; layer < H; ++layer) {
+                tc::mbar_wait(barMma + c, phase);
+                phase ^= 1u;
+                tc::fence_after();
+#pragma unroll 1
+                for (int c0 = 0; c0 < WIDTH; c0 += 32) {
+                    uint32_t v[32];
+                    tc::ld32(acc + c0, v);
+                    tc::wait_ld();
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        uint4 o;
+                        o.x = pack_leaky(v[8 * j + 0], v[8 * j + 1]);
+                        o.y = pack_leaky(v[8 * j + 2], v[8 * j + 3]);
+                        o.z = pack_leaky(v[8 * j + 4], v[8 * j + 5]);
+                        o.w = pack_leaky(v[8 * j + 6], v[8 * j + 7]);
+                        *reinterpret_cast<uint4*>(Hc + (((c0 >> 3) + j) * kTileM + row) * 16) = o;
+                    }
+                }
+                tc::proxy_fence();
+                tc::fence_before();
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive(barEpi + c);
+            }
+            tc::mbar_wait(barMma + c, phase);
+            phase ^= 1u;
+            tc::fence_after();
+            {
+                uint32_t v[16];
+                tc::ld16(acc, v);
+                tc::wait_ld();
+                if (q < rowEnd) {
+                    uint4 lo, hi;
+                    lo.x = pack_plain(v[0], v[1]); lo.y = pack_plain(v[2], v[3]);
+                    lo.z = pack_plain(v[4], v[5]); lo.w = pack_plain(v[6], v[7]);
+                    hi.x = pack_plain(v[8], v[9]); hi.y = pack_plain(v[10], v[11]);
+                    hi.z = pack_plain(v[12], v[13]); hi.w = pack_plain(v[14], v[15]);
+                    uint4* dst = reinterpret_cast<uint4*>(out + static_cast<size_t>(q) * 16);
+                    dst[0] = lo;
+                    dst[1] = hi;
+                }
+            }
+            tc::fence_before();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(barEpi + c);
+        }
+    }
+    tc::fence_before();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(tmem, 2 * WIDTH);
+}
+
+}  // namespace
+
+// ---- host side -----------------------------------------------------------------------------------
+bool split_query_supported(const NetDev& net) {
+    if (net.width != 64 && net.width != 128) return false;
+    if (net.nFeatures != 2 && net.nFeatures != 4) return false;
+    if (net.nHidden < 1 || net.shDegree > 4 || net.nLevels < 1 || net.nLevels > 148) return false;
+    if (((net.nPoints * net.nLevels * net.nFeatures) & 7) != 0) return false;
+    const SplitPlan p = make_plan(net);
+    return p.mlpSmem <= kSmemMax && p.encSmem <= kSmemMax;
+}
+
+size_t split_packed_bytes(const NetDev& net) { return make_plan(net).packedBytes; }
+
+size_t split_xt_bytes(const NetDev& net, size_t rows) {
+    const size_t tiles = (rows + kTileM - 1) / kTileM;
+    return tiles * make_plan(net).xBytes;
+}
+
+int split_prepack(const NetDev& net, void* packedW, cudaStream_t s) {
+    const SplitPlan p = make_plan(net);
+    k_pack_weights<<<64, 256, 0, s>>>(net, static_cast<unsigned char*>(packedW), p.ek);
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+int launch_split_query(const NetDev& net, const float* in, size_t n, const int* dCount, __half* out, cudaStream_t s) {
+    if (n == 0) return 0;
+    if (!net.packedW || !net.xt || net.xtRows < kTileM) return -1;
+    const SplitPlan p = make_plan(net);
+    static bool attr = false;
+    if (!attr) {
+        cudaFuncSetAttribute(k_query_encode<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax));
+        cudaFuncSetAttribute(k_query_encode<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax));
+        cudaFuncSetAttribute(k_query_mlp<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax));
+        cudaFuncSetAttribute(k_query_mlp<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax));
+        attr = true;
+    }
+    int chunkRows = static_cast<int>(net.xtRows / kTileM * kTileM);
+    if ((net.debug & 8) && chunkRows > 1024) chunkRows = 1024;  // tests: exercise the chunk walk on small batches
+    int launches = 0;
+    for (size_t base = 0; base < n; base += chunkRows) {
+        const size_t rows = n - base < static_cast<size_t>(chunkRows) ? n - base : chunkRows;
+        const int tiles = static_cast<int>((rows + kTileM - 1) / kTileM);
+        int slices = p.slices < tiles ? p.slices : tiles;
+        const int egrid = net.nLevels * slices;
+        unsigned char* xt = static_cast<unsigned char*>(net.xt);
+        if (net.nFeatures == 4)
+            k_query_encode<4><<<egrid, kEncThreads, p.encSmem, s>>>(net, in, static_cast<int>(n), dCount, static_cast<int>(base),
+                                                                    chunkRows, xt, p.ek, p.encSmem);
+        else
+            k_query_encode<2><<<egrid, kEncThreads, p.encSmem, s>>>(net, in, static_cast<int>(n), dCount, static_cast<int>(base),
+                                                                    chunkRows, xt, p.ek, p.encSmem);
+        NRB_LAUNCHED("k_query_encode", s);
+        const int mgrid = tiles < 148 ? tiles : 148;
+        if (net.width == 128)
+            k_query_mlp<128><<<mgrid, kMlpThreads, p.mlpSmem, s>>>(net, static_cast<int>(n), dCount, static_cast<int>(base), chunkRows,
+                                                                  xt, out, p);
+        else
+            k_query_mlp<64><<<mgrid, kMlpThreads, p.mlpSmem, s>>>(net, static_cast<int>(n), dCount, static_cast<int>(base), chunkRows,
+                                                                 xt, out, p);
+        NRB_LAUNCHED("k_query_mlp", s);
+        launches += 2;
+    }
+    return launches;
+}
+
+}  // namespace nrb

@@ -58,7 +58,7 @@ def _weights(**net):
     return nrb.scenes.make_weights(seed=42, **net)
 
 
-@pytest.mark.parametrize("kernel", [1, 2], ids=["mma_sync", "tcgen05"])
+@pytest.mark.parametrize("kernel", [1, 2, 3, 3 | (8 << 8)], ids=["mma_sync", "tcgen05_fused", "split", "split_chunked"])
 def test_neural_query_matches_oracle(oracle_lib, kernel):
     scene = nrb.scenes.make_scene("ico", 1, env=False)
     w = _weights()
@@ -76,7 +76,7 @@ def test_neural_query_matches_oracle(oracle_lib, kernel):
     prod.set_query_kernel(0)
 
 
-@pytest.mark.parametrize("kernel", [1, 2], ids=["mma_sync", "tcgen05"])
+@pytest.mark.parametrize("kernel", [1, 2, 3, 3 | (8 << 8)], ids=["mma_sync", "tcgen05_fused", "split", "split_chunked"])
 def test_neural_query_other_shape(oracle_lib, kernel):
     """BASELINE config 5 shape: 1 x HashGrid(16 levels, 2 features, T=2^15, scale 1.5) -> 32 -> 64 x 2 -> 16."""
     cfg = nrb.NNConfig(log2_hashmap_size=15, base_resolution=16, n_points=1, n_levels=16, n_features_per_level=2,
