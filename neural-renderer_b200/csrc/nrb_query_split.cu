@@ -27,6 +27,8 @@
 // permuted identically at pre-pack time, so the products summed per neuron are the same set.
 #include <cuda_runtime.h>
 
+#include <type_traits>
+
 #include "nrb_encode.cuh"
 #include "nrb_frame.cuh"
 #include "nrb_tc.cuh"
@@ -37,7 +39,8 @@ namespace {
 
 constexpr int kTileM = 128;
 constexpr int kEncThreads = 1024;
-constexpr int kMlpThreads = 320;  // warp 0 producer, warp 1 MMA issuer, warps 2-5 / 6-9 epilogues of tile A / B
+constexpr int kEpiWarps = 8;      // per tile in flight: two warps per TMEM lane quarter, half the columns each
+constexpr int kMlpThreads = 64 + 2 * kEpiWarps * 32;  // warp 0 producer, warp 1 MMA issuer, then the epilogues of tile A, B
 constexpr uint32_t kSmemMax = 227u * 1024u;
 
 // Byte offset of element (row, k) of a weight matrix with K columns in the packed (UMMA K-major,
@@ -196,50 +199,79 @@ __device__ __forceinline__ void encode_point(const LevelInfo& lv, const unsigned
     for (int k = 0; k < F / 2; ++k) acc[k] = *reinterpret_cast<const uint32_t*>(&a[k]);
 }
 
+// Warp task = (tile, 32-row group): lane = one query.  The lane fetches its whole input row once
+// (vector loads), encodes this CTA's level for all P points, and writes the level's P*F columns as
+// 16-byte / 8-byte pieces of the tile's k-chunks.  One task in L (warp-uniform) also produces the
+// spherical harmonics and the K padding of its rows.
 template <int F, bool SMEM>
 __device__ __forceinline__ void encode_tasks(const NetDev& net, const LevelInfo& lv, int level, const unsigned char* gtable,
                                              uint32_t stable, const float* __restrict__ in, int rowBase, int rowEnd,
                                              int tiles, int slice, int slices, unsigned char* __restrict__ xt, int ek) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nWarps = blockDim.x >> 5;
     const int P = net.nPoints, D = net.inputDims, L = net.nLevels;
-    const int tasksPerTile = 4 * P + 1;
     const int myTiles = (tiles - slice + slices - 1) / slices;
-    const int PLF = P * L * F, shN = net.shDegree * net.shDegree, E = net.encDims;
+    const int PF = P * F, PLF = PF * L, shN = net.shDegree * net.shDegree;
     const uint32_t tileBytes = static_cast<uint32_t>(ek) * kTileM * 2;
-    for (int task = warp; task < myTiles * tasksPerTile; task += nWarps) {
-        const int tl = task / tasksPerTile, j = task - tl * tasksPerTile;
+    const int k0 = level * PF;  // first column of this level
+    for (int task = warp; task < myTiles * 4; task += nWarps) {
+        const int tl = task >> 2, g = task & 3;
         const int tile = slice + tl * slices;
-        unsigned char* tbase = xt + static_cast<size_t>(tile) * tileBytes;
-        if (j < 4 * P) {
-            const int p = j >> 2, r = ((j & 3) << 5) + lane;
-            const int row = rowBase + tile * kTileM + r;
-            if (row < rowEnd) {
-                const float* x = in + static_cast<size_t>(row) * D + 3 * p;
-                uint32_t acc[F / 2];
-                encode_point<F, SMEM>(lv, gtable, stable, __ldg(x), __ldg(x + 1), __ldg(x + 2), acc);
-                const int kp = level * (P * F) + p * F;
-                unsigned char* dst = tbase + ((kp >> 3) * kTileM + r) * 16 + (kp & 7) * 2;
-                if (F == 4) *reinterpret_cast<uint2*>(dst) = make_uint2(acc[0], acc[F / 2 - 1]);
-                else *reinterpret_cast<uint32_t*>(dst) = acc[0];
+        const int r = (g << 5) + lane;
+        const int row = rowBase + tile * kTileM + r;
+        if (row >= rowEnd) continue;
+        unsigned char* tbase = xt + static_cast<size_t>(tile) * tileBytes + r * 16;
+        float x[16];
+        const float* src = in + static_cast<size_t>(row) * D;
+        if ((D & 3) == 0) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (4 * i < D) {
+                    const float4 v = __ldg(reinterpret_cast<const float4*>(src) + i);
+                    x[4 * i] = v.x; x[4 * i + 1] = v.y; x[4 * i + 2] = v.z; x[4 * i + 3] = v.w;
+                }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+                if (i < D) x[i] = __ldg(src + i);
+        }
+        uint32_t w[4][F / 2];
+#pragma unroll
+        for (int p = 0; p < 4; ++p)
+            if (p < P) encode_point<F, SMEM>(lv, gtable, stable, x[3 * p], x[3 * p + 1], x[3 * p + 2], w[p]);
+        if (F == 4 && P == 3 && (k0 & 3) == 0) {
+            // 24 bytes per row: one full 16-byte chunk and half of a neighbouring one
+            unsigned char* c0 = tbase + (k0 >> 3) * (kTileM * 16);
+            if ((k0 & 7) == 0) {
+                *reinterpret_cast<uint4*>(c0) = make_uint4(w[0][0], w[0][F / 2 - 1], w[1][0], w[1][F / 2 - 1]);
+                *reinterpret_cast<uint2*>(c0 + kTileM * 16) = make_uint2(w[2][0], w[2][F / 2 - 1]);
+            } else {
+                *reinterpret_cast<uint2*>(c0 + 8) = make_uint2(w[0][0], w[0][F / 2 - 1]);
+                *reinterpret_cast<uint4*>(c0 + kTileM * 16) = make_uint4(w[1][0], w[1][F / 2 - 1], w[2][0], w[2][F / 2 - 1]);
             }
         } else {
-            // spherical harmonics + K padding for the rows this level owns (row % L == level)
-            for (int r = level + lane * L; r < kTileM; r += 32 * L) {
-                const int row = rowBase + tile * kTileM + r;
-                if (row >= rowEnd) continue;
-                __half tail[32];
 #pragma unroll
-                for (int i = 0; i < 32; ++i) tail[i] = __float2half_rn(0.0f);
-                if (shN > 0) {
-                    const float* dsrc = in + static_cast<size_t>(row) * D + 3 * P;
-                    const float d3[3] = {__ldg(dsrc), __ldg(dsrc + 1), __ldg(dsrc + 2)};
-                    encode_sh(net.shDegree, d3, tail);
+            for (int p = 0; p < 4; ++p)
+                if (p < P) {
+                    const int kp = k0 + p * F;
+                    unsigned char* dst = tbase + (kp >> 3) * (kTileM * 16) + (kp & 7) * 2;
+                    if (F == 4) *reinterpret_cast<uint2*>(dst) = make_uint2(w[p][0], w[p][F / 2 - 1]);
+                    else *reinterpret_cast<uint32_t*>(dst) = w[p][0];
                 }
-                // columns [PLF, ek): shN harmonics then zeros; PLF % 8 == 0 is a support condition
-                for (int k = PLF; k < ek; k += 8)
-                    *reinterpret_cast<uint4*>(tbase + ((k >> 3) * kTileM + r) * 16) = *reinterpret_cast<const uint4*>(tail + (k - PLF));
+        }
+        if ((tile * 4 + g) % L == level && PLF < ek) {
+            // spherical harmonics + K padding: columns [PLF, ek), PLF % 8 == 0 is a support condition
+            __half tail[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) tail[i] = __float2half_rn(0.0f);
+            if (shN > 0) {
+                float d3[3] = {0.0f, 0.0f, 0.0f};
+#pragma unroll
+                for (int i = 0; i < 16; ++i)
+                    if (i >= 3 * P && i < 3 * P + 3) d3[i - 3 * P] = x[i];
+                encode_sh(net.shDegree, d3, tail);
             }
-            (void)E;
+            for (int k = PLF; k < ek; k += 8)
+                *reinterpret_cast<uint4*>(tbase + (k >> 3) * (kTileM * 16)) = *reinterpret_cast<const uint4*>(tail + (k - PLF));
         }
     }
 }
@@ -288,6 +320,15 @@ __device__ __forceinline__ uint32_t pack_plain(uint32_t a, uint32_t b) {
     return *reinterpret_cast<const uint32_t*>(&h);
 }
 
+// Experiments (net.debug bit 4): CTA 0 stamps clock64 at protocol points into the rows after the
+// last output row (the caller allocates 4096 extra rows): slot layout [who][event][4].
+__device__ __forceinline__ void trace(bool on, __half* out, int n, int who, int ev, int field) {
+    if (!on || ev >= 64) return;
+    long long t;
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(t));
+    reinterpret_cast<long long*>(out + static_cast<size_t>(n) * 16)[(who * 64 + ev) * 4 + field] = t;
+}
+
 // Barrier block at plan.offBar: [0] weights landed, [1] X full, [2] X empty, [3,4] MMA done (tile A, B),
 // [5,6] epilogue done (tile A, B), then the TMEM base address.
 template <int WIDTH>
@@ -305,6 +346,7 @@ __global__ void __launch_bounds__(kMlpThreads, 1)
     if (rowEnd <= rowBase) return;
     const int tiles = (rowEnd - rowBase + kTileM - 1) / kTileM;
     if (static_cast<int>(blockIdx.x) >= tiles) return;
+    const bool tr = (net.debug & 16) && blockIdx.x == 0;
     const int nMine = (tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
 
     const int EK = plan.ek, H = net.nHidden, LAYERS = H + 1;
@@ -325,8 +367,8 @@ __global__ void __launch_bounds__(kMlpThreads, 1)
         tc::mbar_init(barXEmpty, 1);
         tc::mbar_init(barMma + 0, 1);
         tc::mbar_init(barMma + 1, 1);
-        tc::mbar_init(barEpi + 0, 4);
-        tc::mbar_init(barEpi + 1, 4);
+        tc::mbar_init(barEpi + 0, kEpiWarps);
+        tc::mbar_init(barEpi + 1, kEpiWarps);
         tc::mbar_init_fence();
     }
     if (warp == 0) tc::tmem_alloc(tmemSlot, 2 * WIDTH);
@@ -352,104 +394,129 @@ __global__ void __launch_bounds__(kMlpThreads, 1)
         }
     } else if (warp == 1) {
         // ===================== MMA issuer: two tiles in flight, offset by half a tile =================
-        if (lane == 0) {
-            tc::mbar_wait(barW, 0);
-            tc::fence_after();
-            const int nT[2] = {(nMine + 1) >> 1, nMine >> 1};
-            const int delay = LAYERS >> 1;
-            const int total = 2 * (nT[0] * LAYERS > nT[1] * LAYERS + delay ? nT[0] * LAYERS : nT[1] * LAYERS + delay);
-            uint32_t epiPhase[2] = {0u, 0u};
-            uint32_t xUse = 0;
-            const uint32_t wBase = tc::s32(wsm);
-            for (int s = 0; s < total; ++s) {
-                const int c = s & 1;
-                const int idx = (s >> 1) - (c ? delay : 0);
-                if (idx < 0) continue;
-                const int tk = idx / LAYERS, layer = idx - tk * LAYERS;
-                if (tk >= nT[c]) continue;
-                const uint32_t acc = tmem + static_cast<uint32_t>(c * WIDTH);
-                if (layer == 0) {
-                    if (tk > 0) {  // the previous tile's output epilogue has drained the accumulator
-                        tc::mbar_wait(barEpi + c, epiPhase[c]);
-                        epiPhase[c] ^= 1u;
-                    }
-                    tc::mbar_wait(barXFull, xUse & 1u);
-                    ++xUse;
-                    tc::fence_after();
-                    const uint32_t idesc = tc::instr_desc(kTileM, WIDTH);
-                    const uint64_t a0 = tc::smem_desc(tc::s32(X), 2048u, 128u);
-                    const uint64_t b0 = tc::smem_desc(wBase, 128u, static_cast<uint32_t>(EK) * 16u);
-                    for (int k = 0; k < EK / 16; ++k)
-                        tc::mma_f16(acc, a0 + static_cast<uint64_t>(256u * k), b0 + static_cast<uint64_t>(16u * k), idesc, k > 0);
-                    tc::commit(barXEmpty);
-                    tc::commit(barMma + c);
-                } else {
-                    tc::mbar_wait(barEpi + c, epiPhase[c]);
-                    epiPhase[c] ^= 1u;
-                    tc::fence_after();
-                    const bool last = layer == H;
-                    const uint32_t idesc = tc::instr_desc(kTileM, last ? 16 : WIDTH);
-                    const uint32_t wOff = plan.w0Bytes + static_cast<uint32_t>(layer - 1) * WIDTH * WIDTH * 2u;
-                    const uint64_t a0 = tc::smem_desc(tc::s32(Hb + c * plan.hBytes), 2048u, 128u);
-                    const uint64_t b0 = tc::smem_desc(wBase + wOff, 128u, static_cast<uint32_t>(WIDTH) * 16u);
-                    for (int k = 0; k < WIDTH / 16; ++k)
-                        tc::mma_f16(acc, a0 + static_cast<uint64_t>(256u * k), b0 + static_cast<uint64_t>(16u * k), idesc, k > 0);
-                    tc::commit(barMma + c);
+        // The whole warp runs this loop convergently (uniform operands -> uniform registers); one
+        // elected lane issues.  Tile context A runs layer ops at even turns, B at odd turns starting
+        // half a tile later, so one context's epilogue runs under the other's MMAs.
+        tc::mbar_wait(barW, 0);
+        tc::fence_after();
+        const uint32_t elected = tc::elect_one();
+        const int nTA = (nMine + 1) >> 1, nTB = nMine >> 1;
+        const int delay = LAYERS >> 1;
+        const uint32_t wBase = tc::s32(wsm);
+        const uint32_t idescW = tc::instr_desc(kTileM, WIDTH), idescL = tc::instr_desc(kTileM, 16);
+        const uint64_t dX = tc::smem_desc(tc::s32(X), 2048u, 128u);
+        const uint64_t dW0 = tc::smem_desc(wBase, 128u, static_cast<uint32_t>(EK) * 16u);
+        const uint64_t dWh = tc::smem_desc(wBase + plan.w0Bytes, 128u, static_cast<uint32_t>(WIDTH) * 16u);
+        const uint64_t dHA = tc::smem_desc(tc::s32(Hb), 2048u, 128u);
+        const uint64_t dHB = tc::smem_desc(tc::s32(Hb + plan.hBytes), 2048u, 128u);
+        const int ksteps0 = EK / 16;
+        uint32_t xUse = 0;
+        // one layer op of context c (compile-time), returns after the MMAs are queued and committed
+        auto op = [&](auto cTag, int tk, int layer, uint32_t& epiPhase, int step) {
+            constexpr int c = decltype(cTag)::value;
+            const uint32_t acc = tmem + static_cast<uint32_t>(c * WIDTH);
+            trace(tr && lane == 0, out, n, 0, step, 0);
+            if (layer == 0) {
+                if (tk > 0) {  // the previous tile's output epilogue has drained the accumulator
+                    tc::mbar_wait(barEpi + c, epiPhase);
+                    epiPhase ^= 1u;
                 }
+                tc::mbar_wait(barXFull, xUse & 1u);
+                ++xUse;
+                tc::fence_after();
+                trace(tr && lane == 0, out, n, 0, step, 1);
+                for (int k = 0; k < ksteps0; ++k)
+                    tc::mma_f16_elect(elected, acc, dX + static_cast<uint64_t>(256u * k), dW0 + static_cast<uint64_t>(16u * k), idescW, k > 0);
+                tc::commit_elect(elected, barXEmpty);
+                tc::commit_elect(elected, barMma + c);
+            } else {
+                tc::mbar_wait(barEpi + c, epiPhase);
+                epiPhase ^= 1u;
+                tc::fence_after();
+                trace(tr && lane == 0, out, n, 0, step, 1);
+                const uint64_t a0 = c == 0 ? dHA : dHB;
+                const uint64_t b0 = dWh + static_cast<uint64_t>(static_cast<uint32_t>(layer - 1) * (WIDTH * WIDTH * 2u / 16u));
+                if (layer == H) {
+#pragma unroll
+                    for (int k = 0; k < WIDTH / 16; ++k)
+                        tc::mma_f16_elect(elected, acc, a0 + static_cast<uint64_t>(256u * k), b0 + static_cast<uint64_t>(16u * k), idescL, k > 0);
+                } else {
+#pragma unroll
+                    for (int k = 0; k < WIDTH / 16; ++k)
+                        tc::mma_f16_elect(elected, acc, a0 + static_cast<uint64_t>(256u * k), b0 + static_cast<uint64_t>(16u * k), idescW, k > 0);
+                }
+                tc::commit_elect(elected, barMma + c);
+            }
+            trace(tr && lane == 0, out, n, 0, step, 2);
+        };
+        uint32_t phA = 0, phB = 0;
+        int tkA = 0, layA = 0, tkB = 0, layB = 0;
+        for (int turn = 0; tkA < nTA || tkB < nTB; ++turn) {
+            if (tkA < nTA) {
+                op(std::integral_constant<int, 0>{}, tkA, layA, phA, 2 * turn);
+                if (++layA == LAYERS) { layA = 0; ++tkA; }
+            }
+            if (tkB < nTB && turn >= delay) {
+                op(std::integral_constant<int, 1>{}, tkB, layB, phB, 2 * turn + 1);
+                if (++layB == LAYERS) { layB = 0; ++tkB; }
             }
         }
     } else {
         // ===================== epilogue warps: TMEM -> LeakyReLU -> fp16 -> next layer's A operand ====
-        const int c = (warp - 2) >> 2;              // tile context
+        const int c = (warp - 2) / kEpiWarps;       // tile context
+        const int half = ((warp - 2) % kEpiWarps) >> 2;  // which half of the columns
         const int quarter = warp & 3;               // the TMEM lane quarter this warp may read
         const int row = quarter * 32 + lane;
         const uint32_t acc = tmem + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(c * WIDTH);
         unsigned char* Hc = Hb + c * plan.hBytes;
         const int nT = c == 0 ? (nMine + 1) >> 1 : nMine >> 1;
+        constexpr int kCols = WIDTH / 2;            // columns per thread per hidden layer
         uint32_t phase = 0;
         for (int tk = 0; tk < nT; ++tk) {
             const int tile = blockIdx.x + (2 * tk + c) * gridDim.x;
             const int q = rowBase + tile * kTileM + row;
             for (int layer = 0; layer < H; ++layer) {
+                const bool trE = tr && lane == 0 && ((warp - 2) % kEpiWarps) == 0;
+                const int ev = tk * (H + 1) + layer;
+                trace(trE, out, n, 1 + c, ev, 0);
                 tc::mbar_wait(barMma + c, phase);
                 phase ^= 1u;
                 tc::fence_after();
-#pragma unroll 1
-                for (int c0 = 0; c0 < WIDTH; c0 += 32) {
-                    uint32_t v[32];
-                    tc::ld32(acc + c0, v);
-                    tc::wait_ld();
+                trace(trE, out, n, 1 + c, ev, 1);
+                uint32_t v[kCols / 32][32];
+#pragma unroll
+                for (int b = 0; b < kCols / 32; ++b) tc::ld32(acc + half * kCols + b * 32, v[b]);
+                tc::wait_ld();
+                trace(trE, out, n, 1 + c, ev, 2);
+#pragma unroll
+                for (int b = 0; b < kCols / 32; ++b)
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         uint4 o;
-                        o.x = pack_leaky(v[8 * j + 0], v[8 * j + 1]);
-                        o.y = pack_leaky(v[8 * j + 2], v[8 * j + 3]);
-                        o.z = pack_leaky(v[8 * j + 4], v[8 * j + 5]);
-                        o.w = pack_leaky(v[8 * j + 6], v[8 * j + 7]);
-                        *reinterpret_cast<uint4*>(Hc + (((c0 >> 3) + j) * kTileM + row) * 16) = o;
+                        o.x = pack_leaky(v[b][8 * j + 0], v[b][8 * j + 1]);
+                        o.y = pack_leaky(v[b][8 * j + 2], v[b][8 * j + 3]);
+                        o.z = pack_leaky(v[b][8 * j + 4], v[b][8 * j + 5]);
+                        o.w = pack_leaky(v[b][8 * j + 6], v[b][8 * j + 7]);
+                        *reinterpret_cast<uint4*>(Hc + ((((half * kCols) >> 3) + b * 4 + j) * kTileM + row) * 16) = o;
                     }
-                }
                 tc::proxy_fence();
                 tc::fence_before();
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(barEpi + c);
+                trace(trE, out, n, 1 + c, ev, 3);
             }
             tc::mbar_wait(barMma + c, phase);
             phase ^= 1u;
             tc::fence_after();
             {
-                uint32_t v[16];
-                tc::ld16(acc, v);
+                uint32_t v[8];
+                tc::ld8(acc + half * 8, v);
                 tc::wait_ld();
                 if (q < rowEnd) {
-                    uint4 lo, hi;
-                    lo.x = pack_plain(v[0], v[1]); lo.y = pack_plain(v[2], v[3]);
-                    lo.z = pack_plain(v[4], v[5]); lo.w = pack_plain(v[6], v[7]);
-                    hi.x = pack_plain(v[8], v[9]); hi.y = pack_plain(v[10], v[11]);
-                    hi.z = pack_plain(v[12], v[13]); hi.w = pack_plain(v[14], v[15]);
-                    uint4* dst = reinterpret_cast<uint4*>(out + static_cast<size_t>(q) * 16);
-                    dst[0] = lo;
-                    dst[1] = hi;
+                    uint4 o;
+                    o.x = pack_plain(v[0], v[1]); o.y = pack_plain(v[2], v[3]);
+                    o.z = pack_plain(v[4], v[5]); o.w = pack_plain(v[6], v[7]);
+                    reinterpret_cast<uint4*>(out + static_cast<size_t>(q) * 16)[half] = o;
                 }
             }
             tc::fence_before();
