@@ -201,7 +201,9 @@ typedef enum nrb_option {
     NRB_OPT_CAPTURE = 8,              /* (new) keep per-element debug buffers for nrb_read_buffer */
     NRB_OPT_USE_HARDWARE_RT = 9,      /* setUseHardwareRT: accepted, ignored (no OptiX path) */
     NRB_OPT_PROFILE = 10,             /* (new) record a CUDA event after every kernel launch: nrb_get_stage */
-    NRB_OPT_QUERY_KERNEL = 11         /* (new, process-wide) neural query kernel: 0 auto, 1 mma.sync, 2 tcgen05 */
+    NRB_OPT_QUERY_KERNEL = 11,        /* (new, process-wide) neural query kernel: 0 auto, 1 mma.sync, 2 fused tcgen05, 3 split */
+    NRB_OPT_TAIL_GRAPH = 12           /* (new) 1 (default): segment-loop iterations 1..9 run as a device-driven CUDA
+                                         conditional WHILE graph; 0: nine fixed launches per pass */
 } nrb_option;
 int nrb_set_option(nrb_renderer* r, int option, int value);
 int nrb_get_option(const nrb_renderer* r, int option);

@@ -150,6 +150,7 @@ __global__ void __launch_bounds__(128) k_trace_rays(const __grid_constant__ Mesh
 
 static thread_local StageProfiler* g_profiler = nullptr;
 void set_stage_profiler(StageProfiler* p) { g_profiler = p; }
+StageProfiler* get_stage_profiler() { return g_profiler; }
 
 void debug_check(const char* what, cudaStream_t s) {
     static const bool on = getenv("NRB_DEBUG") != nullptr;

@@ -29,6 +29,7 @@ struct StageProfiler {
     bool ready = false;
 };
 void set_stage_profiler(StageProfiler* p);
+StageProfiler* get_stage_profiler();
 void debug_check(const char* what, cudaStream_t s);
 #define NRB_LAUNCHED(what, s) ::nrb::debug_check(what, s)
 
@@ -37,7 +38,22 @@ struct NetDev;
 void launch_trace_rays(const MeshDev& m, int mode, const float* o, const float* d, size_t n, Hit* out,
                        unsigned long long* stats, cudaStream_t s);
 int launch_gt_frame(const Frame& f, bool lambert, cudaStream_t s);       // returns kernels launched
-int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStream_t s);
+// Host-side state of the device-driven segment-loop tail (nrb_segments.cu): one instantiated
+// conditional-WHILE graph per hit-record target, the device copy of the frame block its kernels
+// read, and the key the graphs were built for.  Owned by the renderer; null = fixed ten iterations.
+struct SegTail {
+    cudaGraph_t graph[2] = {nullptr, nullptr};
+    cudaGraphExec_t exec[2] = {nullptr, nullptr};
+    cudaStream_t capture = nullptr;
+    void* dFrame = nullptr;       // Frame
+    void* dCtl = nullptr;         // SegCtl[2]
+    unsigned char key[512] = {};  // bytes the graphs depend on (NetDev, state pointers, sizes)
+    size_t keyBytes = 0;
+    bool failed = false;          // conditional graphs unavailable: stay on the fixed loop
+    void release();
+    ~SegTail() { release(); }
+};
+int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStream_t s, SegTail* tail);
 int launch_finalize(const Frame& f, cudaStream_t s);
 int launch_lambert(const Frame& f, cudaStream_t s);
 

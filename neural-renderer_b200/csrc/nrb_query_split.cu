@@ -54,7 +54,8 @@ struct SplitPlan {
     uint32_t w0Bytes, whBytes, wlBytes, packedBytes;
     uint32_t xBytes, hBytes;      // one encoded tile / one hidden tile in shared memory
     uint32_t offW, offX, offH, offBar, mlpSmem;
-    uint32_t encSmem;             // table bytes staged by an encoder CTA (largest level that fits)
+    uint32_t encSmem;             // table bytes staged by an encoder CTA (largest level that fits), 128-aligned
+    uint32_t encRing;             // per-warp two-stage input rings
     int slices;                   // encoder CTAs per level
 };
 
@@ -74,10 +75,11 @@ SplitPlan make_plan(const NetDev& net) {
     p.offH = o; o += 2 * p.hBytes;
     p.offBar = o; o += 128;
     p.mlpSmem = o;
+    p.encRing = (kEncThreads / 32) * 2u * 32u * net.inputDims * 4u;
     uint32_t best = 0;
     for (int l = 0; l < net.nLevels; ++l) {
-        const uint64_t bytes = static_cast<uint64_t>(net.levelSize[l]) * net.nFeatures * 2;
-        if (bytes <= 200u * 1024u && bytes > best) best = static_cast<uint32_t>(bytes);
+        const uint64_t bytes = (static_cast<uint64_t>(net.levelSize[l]) * net.nFeatures * 2 + 127u) / 128u * 128u;
+        if (bytes + p.encRing <= kSmemMax && bytes > best) best = static_cast<uint32_t>(bytes);
     }
     p.encSmem = best;
     p.slices = net.nLevels > 0 ? (148 / net.nLevels > 0 ? 148 / net.nLevels : 1) : 1;
@@ -206,34 +208,68 @@ __device__ __forceinline__ void encode_point(const LevelInfo& lv, const unsigned
 template <int F, bool SMEM>
 __device__ __forceinline__ void encode_tasks(const NetDev& net, const LevelInfo& lv, int level, const unsigned char* gtable,
                                              uint32_t stable, const float* __restrict__ in, int rowBase, int rowEnd,
-                                             int tiles, int slice, int slices, unsigned char* __restrict__ xt, int ek) {
+                                             int tiles, int slice, int slices, unsigned char* __restrict__ xt, int ek,
+                                             float* stageBase) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nWarps = blockDim.x >> 5;
     const int P = net.nPoints, D = net.inputDims, L = net.nLevels;
     const int myTiles = (tiles - slice + slices - 1) / slices;
     const int PF = P * F, PLF = PF * L, shN = net.shDegree * net.shDegree;
     const uint32_t tileBytes = static_cast<uint32_t>(ek) * kTileM * 2;
     const int k0 = level * PF;  // first column of this level
-    for (int task = warp; task < myTiles * 4; task += nWarps) {
+    // Input rows reach the lanes through a per-warp two-stage cp.async ring: the 32 rows of a task are
+    // one contiguous, 16-byte-aligned block of 128*D bytes, fetched while the previous task computes.
+    const int stageFloats = 32 * D;
+    float* stage = stageBase + warp * 2 * stageFloats;
+    const size_t inBytes = static_cast<size_t>(rowEnd) * D * 4;
+    auto fetch = [&](int task, int slot) {
+        const int tile = slice + (task >> 2) * slices;
+        const size_t off = static_cast<size_t>(rowBase + tile * kTileM + ((task & 3) << 5)) * D * 4;
+        const unsigned char* src = reinterpret_cast<const unsigned char*>(in) + off;
+        const uint32_t dst = tc::s32(stage + slot * stageFloats);
+        for (int i = lane; i < 8 * D; i += 32) {
+            const size_t o = off + 16u * i;
+            if (o + 16 <= inBytes) {
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * i), "l"(src + 16u * i) : "memory");
+            } else {
+                for (int j = 0; j < 4; ++j)
+                    stage[slot * stageFloats + 4 * i + j] = o + 4u * j + 4 <= inBytes ? __ldg(in + (o >> 2) + j) : 0.0f;
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    const int nTasks = myTiles * 4;
+    int it = 0;
+    if (warp < nTasks) fetch(warp, 0);
+    for (int task = warp; task < nTasks; task += nWarps, ++it) {
         const int tl = task >> 2, g = task & 3;
         const int tile = slice + tl * slices;
         const int r = (g << 5) + lane;
         const int row = rowBase + tile * kTileM + r;
-        if (row >= rowEnd) continue;
+        const int slot = it & 1;
+        if (task + nWarps < nTasks) {
+            fetch(task + nWarps, slot ^ 1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncwarp();  // this task's rows have landed in the slot
         unsigned char* tbase = xt + static_cast<size_t>(tile) * tileBytes + r * 16;
         float x[16];
-        const float* src = in + static_cast<size_t>(row) * D;
+        const float* xs = stage + slot * stageFloats + lane * D;
         if ((D & 3) == 0) {
 #pragma unroll
             for (int i = 0; i < 4; ++i)
                 if (4 * i < D) {
-                    const float4 v = __ldg(reinterpret_cast<const float4*>(src) + i);
+                    const float4 v = *reinterpret_cast<const float4*>(xs + 4 * i);
                     x[4 * i] = v.x; x[4 * i + 1] = v.y; x[4 * i + 2] = v.z; x[4 * i + 3] = v.w;
                 }
         } else {
 #pragma unroll
             for (int i = 0; i < 16; ++i)
-                if (i < D) x[i] = __ldg(src + i);
+                if (i < D) x[i] = xs[i];
         }
+        __syncwarp();  // every lane holds its row: the slot may be refilled by the next fetch
+        if (row >= rowEnd) continue;
         uint32_t w[4][F / 2];
 #pragma unroll
         for (int p = 0; p < 4; ++p)
@@ -307,9 +343,11 @@ __global__ void __launch_bounds__(kEncThreads, 1)
         for (uint32_t i = threadIdx.x * 16u; i < tableBytes; i += blockDim.x * 16u)
             *reinterpret_cast<uint4*>(smem + i) = __ldg(reinterpret_cast<const uint4*>(gtable + i));
         __syncthreads();
-        encode_tasks<F, true>(net, lv, level, gtable, tc::s32(smem), in, rowBase, rowEnd, tiles, slice, slices, xt, ek);
+        encode_tasks<F, true>(net, lv, level, gtable, tc::s32(smem), in, rowBase, rowEnd, tiles, slice, slices, xt, ek,
+                              reinterpret_cast<float*>(smem + smemBytes));
     } else {
-        encode_tasks<F, false>(net, lv, level, gtable, 0u, in, rowBase, rowEnd, tiles, slice, slices, xt, ek);
+        encode_tasks<F, false>(net, lv, level, gtable, 0u, in, rowBase, rowEnd, tiles, slice, slices, xt, ek,
+                               reinterpret_cast<float*>(smem + smemBytes));
     }
 }
 
@@ -538,7 +576,7 @@ bool split_query_supported(const NetDev& net) {
     if (net.nHidden < 1 || net.shDegree > 4 || net.nLevels < 1 || net.nLevels > 148) return false;
     if (((net.nPoints * net.nLevels * net.nFeatures) & 7) != 0) return false;
     const SplitPlan p = make_plan(net);
-    return p.mlpSmem <= kSmemMax && p.encSmem <= kSmemMax;
+    return p.mlpSmem <= kSmemMax && p.encSmem + p.encRing <= kSmemMax;
 }
 
 size_t split_packed_bytes(const NetDev& net) { return make_plan(net).packedBytes; }
@@ -576,10 +614,10 @@ int launch_split_query(const NetDev& net, const float* in, size_t n, const int* 
         const int egrid = net.nLevels * slices;
         unsigned char* xt = static_cast<unsigned char*>(net.xt);
         if (net.nFeatures == 4)
-            k_query_encode<4><<<egrid, kEncThreads, p.encSmem, s>>>(net, in, static_cast<int>(n), dCount, static_cast<int>(base),
+            k_query_encode<4><<<egrid, kEncThreads, p.encSmem + p.encRing, s>>>(net, in, static_cast<int>(n), dCount, static_cast<int>(base),
                                                                     chunkRows, xt, p.ek, p.encSmem);
         else
-            k_query_encode<2><<<egrid, kEncThreads, p.encSmem, s>>>(net, in, static_cast<int>(n), dCount, static_cast<int>(base),
+            k_query_encode<2><<<egrid, kEncThreads, p.encSmem + p.encRing, s>>>(net, in, static_cast<int>(n), dCount, static_cast<int>(base),
                                                                     chunkRows, xt, p.ek, p.encSmem);
         NRB_LAUNCHED("k_query_encode", s);
         const int mgrid = tiles < 148 ? tiles : 148;

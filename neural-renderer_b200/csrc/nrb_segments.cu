@@ -16,6 +16,9 @@
 // The host loop of traceNeuralSegmentsForRays (:1810-2083) reads the active count back to the
 // host after every compaction; here the counts never leave the device: every stage is launched
 // with a fixed persistent grid and loops over the count it finds in device memory.
+#include <cstdio>
+#include <cstring>
+
 #include "nrb_frame_dev.cuh"
 #include "nrb_neural.cuh"
 
@@ -57,7 +60,7 @@ __global__ void __launch_bounds__(kTileThreads) k_entry_camera(const __grid_cons
 }
 
 // One iteration, first half: exits + network inputs for every ray in the segment queue.
-__global__ void __launch_bounds__(kQueueThreads) k_seg_exits(const __grid_constant__ Frame f, int qin) {
+__device__ __forceinline__ void seg_exits_body(const Frame& f, int qin) {
     const FrameParams& fp = f.fp;
     const int n = f.st.counts[qin];
     const int D = fp.inputDims;
@@ -95,11 +98,11 @@ __global__ void __launch_bounds__(kQueueThreads) k_seg_exits(const __grid_consta
         atomicAdd(f.st.stats + 1, static_cast<unsigned long long>(n));
     }
 }
+__global__ void __launch_bounds__(kQueueThreads) k_seg_exits(const __grid_constant__ Frame f, int qin) { seg_exits_body(f, qin); }
 
 // One iteration, second half: decode the network output, record hits, re-enter the shell for the
 // rays that go on, and compact them into the next queue.
-__global__ void __launch_bounds__(kQueueThreads) k_seg_apply(const __grid_constant__ Frame f, int qin, int qout,
-                                                             int recIdx) {
+__device__ __forceinline__ void seg_apply_body(const Frame& f, int qin, int qout, int recIdx) {
     const FrameParams& fp = f.fp;
     const int n = f.st.counts[qin];
     const int nWarpRounded = (n + 31) & ~31;
@@ -149,6 +152,41 @@ __global__ void __launch_bounds__(kQueueThreads) k_seg_apply(const __grid_consta
         queue_push(f.st.queue[qout], f.st.counts + qout, again, e);
     }
     stat_flush(f.st.stats + 0, nTrace);
+}
+__global__ void __launch_bounds__(kQueueThreads) k_seg_apply(const __grid_constant__ Frame f, int qin, int qout,
+                                                             int recIdx) {
+    seg_apply_body(f, qin, qout, recIdx);
+}
+
+// ---- the tail of the segment loop as a device-driven WHILE graph ----------------------------------
+// Iterations 1..9 of traceNeuralSegmentsForRays (:2003-2081) only see rays that left a shell segment
+// without a hit and re-entered the shell: usually none.  The reference decides on the host (a
+// blocking count read-back per iteration); launching all nine iterations blindly costs ~36 empty
+// launches per pass.  Here a CUDA conditional WHILE node repeats {exits, query, apply, control}
+// while the device-resident count is non-zero.  The tail kernels read the frame block from device
+// memory (it is re-uploaded per frame) so that the instantiated graph outlives the frame.
+struct SegCtl {
+    int qin, qout, it, curCount, recIdx;
+};
+__global__ void k_seg_tail_begin(SegCtl* ctl, int* counts, cudaGraphConditionalHandle h, int recIdx) {
+    // after iteration 0: queue 2 -> queue 3
+    const int c = counts[3];
+    ctl->qin = 3; ctl->qout = 2; ctl->it = 1; ctl->curCount = c; ctl->recIdx = recIdx;
+    counts[2] = 0;
+    cudaGraphSetConditional(h, (c > 0 && 1 < kMaxSegIters) ? 1u : 0u);
+}
+__global__ void k_seg_tail_next(SegCtl* ctl, int* counts, cudaGraphConditionalHandle h) {
+    const int qin = ctl->qout, qout = ctl->qin, it = ctl->it + 1;
+    const int c = counts[qin];
+    ctl->qin = qin; ctl->qout = qout; ctl->it = it; ctl->curCount = c;
+    counts[qout] = 0;
+    cudaGraphSetConditional(h, (c > 0 && it < kMaxSegIters) ? 1u : 0u);
+}
+__global__ void __launch_bounds__(kQueueThreads) k_seg_exits_tail(const Frame* __restrict__ f, const SegCtl* __restrict__ ctl) {
+    seg_exits_body(*f, ctl->qin);
+}
+__global__ void __launch_bounds__(kQueueThreads) k_seg_apply_tail(const Frame* __restrict__ f, const SegCtl* __restrict__ ctl) {
+    seg_apply_body(*f, ctl->qin, ctl->qout, ctl->recIdx);
 }
 
 __device__ __forceinline__ void select_closer(const SurfRec& rec, int e, bool addHit, V3 origin, V3 pos, V3 nrm, V3 alb,
@@ -310,38 +348,154 @@ __global__ void __launch_bounds__(kQueueThreads) k_bounce_finish(const __grid_co
 
 // ---------------------------------------------------------------------------------------------
 
-// The segment loop of traceNeuralSegmentsForRays: fixed kMaxSegIters iterations, device counts.
-static int run_segments(const Frame& f, const NetDev& net, int recIdx, cudaStream_t s) {
-    int launches = 0;
-    int qin = 2;
-    for (int it = 0; it < kMaxSegIters; ++it) {
-        // Iterations past the first see only rays that left a shell segment without a hit and
-        // re-entered it: usually none, rarely many.  They get a one-wave grid (grid-stride loops make
-        // any count correct) so that an empty iteration costs a minimal launch.
-        const int grid = it == 0 ? queue_grid(f.fp.nElems) : 148;
-        const int qout = qin == 2 ? 3 : 2;
-        cudaMemsetAsync(f.st.counts + qout, 0, sizeof(int), s);
-        k_seg_exits<<<grid, kQueueThreads, 0, s>>>(f, qin);
-        NRB_LAUNCHED("k_seg_exits", s);
-        launches += 1 + launch_neural_query(net, f.st.netIn, static_cast<size_t>(f.fp.nElems), f.st.counts + qin,
-                                            f.st.netOut, s);
-        k_seg_apply<<<grid, kQueueThreads, 0, s>>>(f, qin, qout, recIdx);
-        NRB_LAUNCHED("k_seg_apply", s);
-        ++launches;
-        qin = qout;
+// The segment loop of traceNeuralSegmentsForRays.  Iteration 0 is launched directly (full grids,
+// frame block in the constant bank).  The remaining iterations run either as the WHILE graph above
+// (tail != nullptr) or, for the per-launch profiler and as the fallback, as nine fixed one-wave
+// launches whose grid-stride loops make any count correct.
+static int seg_iteration(const Frame& f, const NetDev& net, int recIdx, int qin, int grid, cudaStream_t s) {
+    const int qout = qin == 2 ? 3 : 2;
+    cudaMemsetAsync(f.st.counts + qout, 0, sizeof(int), s);
+    k_seg_exits<<<grid, kQueueThreads, 0, s>>>(f, qin);
+    NRB_LAUNCHED("k_seg_exits", s);
+    int launches = 1 + launch_neural_query(net, f.st.netIn, static_cast<size_t>(f.fp.nElems), f.st.counts + qin, f.st.netOut, s);
+    k_seg_apply<<<grid, kQueueThreads, 0, s>>>(f, qin, qout, recIdx);
+    NRB_LAUNCHED("k_seg_apply", s);
+    return launches + 1;
+}
+
+void SegTail::release() {
+    for (int i = 0; i < 2; ++i) {
+        if (exec[i]) cudaGraphExecDestroy(exec[i]);
+        if (graph[i]) cudaGraphDestroy(graph[i]);
+        exec[i] = nullptr;
+        graph[i] = nullptr;
+    }
+    if (capture) cudaStreamDestroy(capture);
+    capture = nullptr;
+    if (dFrame) cudaFree(dFrame);
+    if (dCtl) cudaFree(dCtl);
+    dFrame = dCtl = nullptr;
+    keyBytes = 0;
+}
+
+// Build graph[recIdx]: k_seg_tail_begin -> WHILE { exits, query, apply, k_seg_tail_next }.
+static bool build_tail(SegTail& t, const Frame& f, const NetDev& net, int recIdx) {
+    cudaGraph_t g = nullptr;
+    if (cudaGraphCreate(&g, 0) != cudaSuccess) return false;
+    t.graph[recIdx] = g;
+    cudaGraphConditionalHandle h;
+    if (cudaGraphConditionalHandleCreate(&h, g, 0, cudaGraphCondAssignDefault) != cudaSuccess) return false;
+    SegCtl* ctl = static_cast<SegCtl*>(t.dCtl) + recIdx;
+    int* counts = f.st.counts;
+    cudaGraphNode_t begin = nullptr;
+    {
+        void* args[] = {&ctl, &counts, &h, &recIdx};
+        cudaKernelNodeParams kp{};
+        kp.func = reinterpret_cast<void*>(k_seg_tail_begin);
+        kp.gridDim = dim3(1);
+        kp.blockDim = dim3(1);
+        kp.kernelParams = args;
+        if (cudaGraphAddKernelNode(&begin, g, nullptr, 0, &kp) != cudaSuccess) return false;
+    }
+    cudaGraphNodeParams cp{};
+    cp.type = cudaGraphNodeTypeConditional;
+    cp.conditional.handle = h;
+    cp.conditional.type = cudaGraphCondTypeWhile;
+    cp.conditional.size = 1;
+    cudaGraphNode_t loop = nullptr;
+    if (cudaGraphAddNode(&loop, g, &begin, 1, &cp) != cudaSuccess) return false;
+    cudaGraph_t body = cp.conditional.phGraph_out[0];
+    if (cudaStreamBeginCaptureToGraph(t.capture, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed) != cudaSuccess) return false;
+    const Frame* df = static_cast<const Frame*>(t.dFrame);
+    k_seg_exits_tail<<<148, kQueueThreads, 0, t.capture>>>(df, ctl);
+    const int q = launch_neural_query(net, f.st.netIn, static_cast<size_t>(f.fp.nElems), &ctl->curCount, f.st.netOut, t.capture);
+    k_seg_apply_tail<<<148, kQueueThreads, 0, t.capture>>>(df, ctl);
+    k_seg_tail_next<<<1, 1, 0, t.capture>>>(ctl, counts, h);
+    cudaGraph_t done = nullptr;
+    if (cudaStreamEndCapture(t.capture, &done) != cudaSuccess || q < 0) return false;
+    if (cudaGraphInstantiate(&t.exec[recIdx], g, 0) != cudaSuccess) return false;
+    return true;
+}
+
+// Make sure the graphs match this frame's buffers and network; (re)build them if not.
+static bool prepare_tail(SegTail& t, const Frame& f, const NetDev& net, cudaStream_t s) {
+    if (t.failed) return false;
+    unsigned char key[512] = {};
+    size_t n = 0;
+    auto put = [&](const void* p, size_t bytes) {
+        if (n + bytes <= sizeof(key)) std::memcpy(key + n, p, bytes);
+        n += bytes;
+    };
+    put(&net, sizeof(NetDev));
+    put(&f.st.netIn, sizeof(void*));
+    put(&f.st.netOut, sizeof(void*));
+    put(&f.st.counts, sizeof(void*));
+    put(&f.fp.nElems, sizeof(int));
+    int kernelChoice = query_kernel();
+    put(&kernelChoice, sizeof(int));
+    if (n > sizeof(key)) { t.failed = true; return false; }
+    if (t.exec[0] && t.exec[1] && n == t.keyBytes && std::memcmp(key, t.key, n) == 0) return true;
+    StageProfiler* prof = get_stage_profiler();  // no per-launch events inside a capture
+    set_stage_profiler(nullptr);
+    struct Restore {
+        StageProfiler* p;
+        ~Restore() { set_stage_profiler(p); }
+    } restore{prof};
+    cudaStreamSynchronize(s);  // graphs of the previous key may still be running
+    for (int i = 0; i < 2; ++i) {
+        if (t.exec[i]) cudaGraphExecDestroy(t.exec[i]);
+        if (t.graph[i]) cudaGraphDestroy(t.graph[i]);
+        t.exec[i] = nullptr;
+        t.graph[i] = nullptr;
+    }
+    bool ok = true;
+    if (!t.capture) ok = cudaStreamCreateWithFlags(&t.capture, cudaStreamNonBlocking) == cudaSuccess;
+    if (ok && !t.dFrame) ok = cudaMalloc(&t.dFrame, sizeof(Frame)) == cudaSuccess;
+    if (ok && !t.dCtl) ok = cudaMalloc(&t.dCtl, 2 * sizeof(SegCtl)) == cudaSuccess;
+    if (ok) {
+        // one empty query outside capture: the launchers set their function attributes on first use
+        cudaMemsetAsync(t.dCtl, 0, 2 * sizeof(SegCtl), s);
+        launch_neural_query(net, f.st.netIn, static_cast<size_t>(f.fp.nElems), &static_cast<SegCtl*>(t.dCtl)->curCount, f.st.netOut, s);
+        cudaStreamSynchronize(s);
+    }
+    ok = ok && build_tail(t, f, net, 0) && build_tail(t, f, net, 1);
+    if (!ok) {
+        cudaGetLastError();
+        t.failed = true;
+        fprintf(stderr, "[nrb] conditional-graph segment tail unavailable; using the fixed iteration loop\n");
+        return false;
+    }
+    std::memcpy(t.key, key, n);
+    t.keyBytes = n;
+    return true;
+}
+
+static int run_segments(const Frame& f, const NetDev& net, int recIdx, cudaStream_t s, SegTail* tail) {
+    int launches = seg_iteration(f, net, recIdx, 2, queue_grid(f.fp.nElems), s);
+    if (tail) {
+        cudaGraphLaunch(tail->exec[recIdx], s);
+        NRB_LAUNCHED("segment_tail_graph", s);
+        return launches + 1;
+    }
+    int qin = 3;
+    for (int it = 1; it < kMaxSegIters; ++it) {
+        launches += seg_iteration(f, net, recIdx, qin, 148, s);
+        qin = qin == 2 ? 3 : 2;
     }
     return launches;
 }
 
-int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStream_t s) {
+int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStream_t s, SegTail* tail) {
     const FrameParams& fp = f.fp;
     int launches = 0;
+    if (tail && !prepare_tail(*tail, f, net, s)) tail = nullptr;
+    if (tail) cudaMemcpyAsync(tail->dFrame, &f, sizeof(Frame), cudaMemcpyHostToDevice, s);
     cudaMemsetAsync(f.st.counts, 0, 16 * sizeof(int), s);
     const dim3 tiles((fp.width + 31) / 32, (fp.localHeight + 3) / 4, fp.spp);
     k_entry_camera<<<tiles, kTileThreads, 0, s>>>(f);
     NRB_LAUNCHED("k_entry_camera", s);
     ++launches;
-    launches += run_segments(f, net, 0, s);
+    launches += run_segments(f, net, 0, s, tail);
     k_primary_finish<<<tiles, kTileThreads, 0, s>>>(f);
     NRB_LAUNCHED("k_primary_finish", s);
     ++launches;
@@ -353,7 +507,7 @@ int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStr
         k_bounce_begin<<<grid, kQueueThreads, 0, s>>>(f, b, 0, 1);
         NRB_LAUNCHED("k_bounce_begin", s);
         ++launches;
-        launches += run_segments(f, net, 1, s);
+        launches += run_segments(f, net, 1, s, tail);
         cudaMemsetAsync(f.st.counts + 0, 0, sizeof(int), s);
         k_bounce_finish<<<grid, kQueueThreads, 0, s>>>(f, b, 1, 0);
         NRB_LAUNCHED("k_bounce_finish", s);

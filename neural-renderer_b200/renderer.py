@@ -289,8 +289,14 @@ class RendererNeural:
         self._opt(K.OPT_PROFILE, v)
 
     def set_query_kernel(self, which: int):
-        """0 = automatic, 1 = mma.sync kernel, 2 = tcgen05/TMEM kernel (process-wide)."""
+        """0 = automatic, 1 = mma.sync kernel, 2 = fused tcgen05 kernel, 3 = split encode + tcgen05 MLP
+        (process-wide)."""
         self._opt(K.OPT_QUERY_KERNEL, which)
+
+    def set_tail_graph(self, v: bool):
+        """Segment-loop iterations 1..9 as a device-driven conditional WHILE graph (default) or as
+        nine fixed launches per pass."""
+        self._opt(K.OPT_TAIL_GRAPH, 1 if v else 0)
 
     def stages(self):
         """-> {kernel name: (total ms, launches)} accumulated since reset_stages()."""

@@ -195,6 +195,18 @@ def make_scene(kind: str = "ico", subdivisions: int = 4, shells: bool = True, en
         n = vertex_normals(v, idx)
         uv = np.stack([np.arctan2(v0[:, 0], v0[:, 2]) / (2 * np.pi) + 0.5, np.arccos(np.clip(v0[:, 1], -1, 1)) / np.pi],
                       -1).astype(np.float32)
+    blobs = kind == "blobs"
+    if blobs:
+        # two separate objects in two separate shell components, lined up with the default camera (a small near one in front of a larger far one): rays
+        # that leave the first component without a hit re-enter the shell at the second one, so the
+        # segment loop needs more than one iteration
+        d = np.array([2.0, 1.2, 2.0], np.float32)
+        d /= np.linalg.norm(d)
+        nv = len(v)
+        v = np.concatenate([v * np.float32(0.3) + d * np.float32(0.9), v * np.float32(0.6) - d * np.float32(0.6)]).astype(np.float32)
+        n = np.concatenate([n, n]).astype(np.float32)
+        uv = np.concatenate([uv, uv]).astype(np.float32)
+        idx = np.concatenate([idx, idx + np.uint32(nv)]).astype(np.uint32)
     extra = {}
     if textured:
         m = K.Material.from_config(base_color=(0.8, 0.8, 0.8), roughness=roughness, metallic=metallic, specular=specular)
@@ -205,8 +217,14 @@ def make_scene(kind: str = "ico", subdivisions: int = 4, shells: bool = True, en
     scene = Scene(original_mesh=mesh_from(v, idx, normals=n, texcoords=uv, **extra))
     if shells:
         hv, hidx = icosphere(3)
-        scene.inner_shell = mesh_from((hv * np.float32(1.0 - shell_delta)).astype(np.float32), hidx)
-        scene.outer_shell = mesh_from((hv * np.float32(1.0 + shell_delta)).astype(np.float32), hidx)
+        if blobs:
+            two = lambda r: np.concatenate([hv * np.float32(0.3 * r) + d * np.float32(0.9), hv * np.float32(0.6 * r) - d * np.float32(0.6)]).astype(np.float32)
+            hidx2 = np.concatenate([hidx, hidx + np.uint32(len(hv))]).astype(np.uint32)
+            scene.inner_shell = mesh_from(two(1.0 - shell_delta), hidx2)
+            scene.outer_shell = mesh_from(two(1.0 + shell_delta), hidx2)
+        else:
+            scene.inner_shell = mesh_from((hv * np.float32(1.0 - shell_delta)).astype(np.float32), hidx)
+            scene.outer_shell = mesh_from((hv * np.float32(1.0 + shell_delta)).astype(np.float32), hidx)
     if additional:
         gv, gidx = ground_quad()
         scene.additional_mesh = mesh_from(gv, gidx)

@@ -145,6 +145,28 @@ def test_neural_frame_parity(oracle_lib, spp, bounces, additional):
     assert abs(ca["neural_queries"] - cb["neural_queries"]) <= 0.01 * cb["neural_queries"] + 2
 
 
+def test_segment_tail_graph_matches_fixed_loop(oracle_lib):
+    """Two shell components in line with the camera: rays that pass the first one re-enter the shell, so
+    iterations >= 1 of the segment loop carry rays.  The device-driven WHILE graph must give the
+    same frame, bit for bit, as the nine fixed launches, and both must match the oracle's host loop."""
+    scene = nrb.scenes.make_scene("blobs", 3, additional=True, shell_delta=0.3)
+    prod, orc, eye = make_pair(scene, oracle_lib, 160, 96, spp=1, bounces=2, neural=True, weights=_weights())
+    frames, queries = [], []
+    for graph in (True, False, True):
+        prod.set_tail_graph(graph)
+        prod.reset_samples()
+        prod.render(eye)
+        frames.append(prod.read_pixels().copy())
+        queries.append(prod.counters()["neural_queries"])
+    assert np.array_equal(frames[0], frames[1]) and np.array_equal(frames[0], frames[2])
+    assert queries[0] == queries[1] == queries[2]
+    orc.render(eye)
+    oq = orc.counters()["neural_queries"]
+    print("tail test: queries", queries[0], "oracle", oq)
+    assert abs(queries[0] - oq) <= 0.02 * oq + 2
+    assert psnr8(frames[0], orc.read_pixels()) > 28.0, psnr8(frames[0], orc.read_pixels())
+
+
 def test_tiles_reassemble_full_frame(oracle_lib):
     """Multi-GPU partition (row bands, global RNG streams): the union of ranks' rows is the 1-GPU image bit for bit."""
     scene = nrb.scenes.make_scene("ico", 3)
