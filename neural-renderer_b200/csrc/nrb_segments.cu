@@ -232,80 +232,158 @@ __global__ void __launch_bounds__(kTileThreads) k_primary_finish(const __grid_co
 // Bounce, first half: sample the BRDF at every live vertex, early-terminate paths whose bounce ray
 // reaches the inner shell before the outer one, find the shell entry of the survivors.
 // qin -> qray (all surviving rays) and -> segment queue 2 (those that enter the shell).
-__global__ void __launch_bounds__(kQueueThreads) k_bounce_begin(const __grid_constant__ Frame f, int bounce, int qin,
-                                                                int qray) {
+//
+// checkBounceEarlyTerminationKernel + traceOuterShellEntryFromRaysKernel need up to five closest-hit
+// queries per vertex: ANY / FORWARD / BACKWARD on the outer shell (one fused pass, MultiTrace), ANY on
+// the inner shell, FORWARD on the outer shell again from beyond the exit.  Bounce rays are incoherent
+// and their traversal lengths are heavy-tailed: with one vertex per lane for the whole kernel, ncu
+// showed 7.5 of 32 lanes active in the traversal loops (profiles/r1_v5_*).  This kernel is therefore a
+// PERSISTENT warp scheduler: every lane runs a small state machine (fetch vertex -> sample -> trace
+// -> trace -> ... -> write), the warp alternates between a convergent traversal phase and a
+// convergent transition phase, and lanes whose work is done fetch the next vertex from a global
+// cursor as soon as fewer than kRefillBelow lanes are still tracing.
+constexpr int kRefillBelow = 22;
+
+// sampleBounceDirectionsKernel (:357-499) on the live-path queue: fully convergent apart from the
+// three-way lobe choice.  A path the reference deactivates here is marked by pdf = -1.
+__global__ void __launch_bounds__(kQueueThreads) k_bounce_sample(const __grid_constant__ Frame f, int bounce, int qin) {
     const FrameParams& fp = f.fp;
     const int n = f.st.counts[qin];
-    const int nWarpRounded = (n + 31) & ~31;
     const SurfRec& cur = f.st.rec[bounce == 1 ? 0 : 1];
-    const TraceTarget tOuter = target_of(f.mesh[NRB_SLOT_OUTER]), tInner = target_of(f.mesh[NRB_SLOT_INNER]);
-    unsigned int nTrace = 0, nVert = 0;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nWarpRounded; i += gridDim.x * blockDim.x) {
-        bool alive = false, enters = false;
-        int e = 0, stage = 5;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int e = f.st.queue[qin][i];
+        const ElemId id = queue_elem(fp, e);
+        const float4 P = cur.P[e], N = cur.N[e], C = cur.C[e];
+        const float2 M = cur.M[e];
+        const V3 prev = bounce == 1 ? v3s(0.0f) : f4v(f.st.prevD[e]);
         V3 org = v3s(0.0f), wi = v3(0.0f, 0.0f, 1.0f), weight = v3s(0.0f);
-        float pdf = 0.0f, carried = 0.0f;
-        if (i < n) {
-            e = f.st.queue[qin][i];
-            const ElemId id = queue_elem(fp, e);
-            const float4 P = cur.P[e], N = cur.N[e], C = cur.C[e];
-            const float2 M = cur.M[e];
-            const V3 prev = bounce == 1 ? v3s(0.0f) : f4v(f.st.prevD[e]);
-            ++nVert;
-            alive = sample_vertex(f, id, f4v(P), f4v(N), f4v(C), v3(C.w, M.x, M.y), bounce == 1, prev, org, wi, weight,
-                                  pdf);
-            carried = N.w;
-        }
-        // checkBounceEarlyTerminationKernel + traceOuterShellEntryFromRaysKernel.  The three outer-shell
-        // queries of a bounce ray (ANY for early termination, FORWARD entry, BACKWARD exit when the
-        // origin is inside the shell) are ONE fused depth-first pass (trace_multi, exact per mode); the
-        // inner-shell ANY trace and the re-entry trace then run in a convergent loop over the
-        // out-of-line traversal so lanes at different steps still execute the same instructions.
-        float tAny = 1e30f, tFwd = 1e30f, tBwd = 1e30f;
-        if (alive) {
-            trace_multi(tOuter, (carried > 0.0f ? 1 : 0) | 2 | 4, org, wi, tAny, tFwd, tBwd);
-            nTrace += (carried > 0.0f ? 1u : 0u) + 1u + (tFwd >= 1e30f ? 1u : 0u);
-        }
-        const int afterTermination = tFwd < 1e30f ? 5 : (tBwd < 1e30f ? 4 : 5);  // 4 = re-entry trace needed
-        if (alive) stage = carried > 0.0f ? 1 : afterTermination;
-        Hit hEntry{tFwd, 0.0f, 0.0f, 0u};
-        float baseOffset = 0.0f;
-        V3 entryOrigin = org;
-        while (__any_sync(0xffffffffu, stage < 5)) {
-            if (stage < 5) {
-                if (stage == 4) {
+        float pdf = 0.0f;
+        const bool ok = sample_vertex(f, id, f4v(P), f4v(N), f4v(C), v3(C.w, M.x, M.y), bounce == 1, prev, org, wi, weight, pdf);
+        f.st.rayO[e] = make_float4(org.x, org.y, org.z, ok ? pdf : -1.0f);
+        f.st.rayD[e] = make_float4(wi.x, wi.y, wi.z, N.w);
+        f.st.rayW[e] = make_float4(weight.x, weight.y, weight.z, 0.0f);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(f.st.stats + 2, static_cast<unsigned long long>(n));
+}
+
+__global__ void __launch_bounds__(kQueueThreads) k_bounce_begin(const __grid_constant__ Frame f, int bounce, int qin,
+                                                                int qray) {
+    const int n = f.st.counts[qin];
+    int* cursor = f.st.counts + 8;
+    const TraceTarget tOuter = target_of(f.mesh[NRB_SLOT_OUTER]), tInner = target_of(f.mesh[NRB_SLOT_INNER]);
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    unsigned int nTrace = 0;
+
+    // lane state: stage 0 = no vertex; 1 = fused outer trace; 2 = inner ANY; 3 = re-entry FORWARD
+    int stage = 0, e = 0;
+    V3 org = v3s(0.0f), wi = v3(0.0f, 0.0f, 1.0f), entryOrigin = v3s(0.0f);
+    float carried = 0.0f, tAny = 1e30f, tFwd = 1e30f, tBwd = 1e30f, baseOffset = 0.0f;
+    MultiTrace tr;
+    tr.ref = kTraceDone;
+    bool more = true;  // warp-uniform: the cursor has not run past the queue
+
+    for (;;) {
+        // ================= transition phase (convergent) =================
+        for (;;) {
+            bool finish = false, alive = false;
+            float entryT = 1e30f;
+            if (stage != 0 && tr.done()) {
+                int next;  // 2 = inner ANY, 3 = re-entry, 5 = write
+                if (stage == 1) {
+                    tAny = tr.best0; tFwd = tr.best1; tBwd = tr.best2;
+                    nTrace += (carried > 0.0f ? 1u : 0u) + 1u + (tFwd >= 1e30f ? 1u : 0u);
+                    const int after = tFwd < 1e30f ? 5 : (tBwd < 1e30f ? 3 : 5);
+                    next = carried > 0.0f ? 2 : after;
+                    entryT = tFwd;
+                    alive = true;
+                } else if (stage == 2) {
+                    const float ht = tr.best0;
+                    const int after = tFwd < 1e30f ? 5 : (tBwd < 1e30f ? 3 : 5);
+                    if (ht < 1e30f && tAny < 1e30f && ht < tAny) { next = 5; alive = false; }
+                    else { next = after; alive = true; entryT = tFwd; }
+                } else {
+                    next = 5;
+                    alive = true;
+                    entryT = tr.best1;
+                }
+                if (next == 2) {
+                    tr.begin(tInner, 1, org, wi);
+                    ++nTrace;
+                    stage = 2;
+                } else if (next == 3) {
                     baseOffset = tBwd + kSegEps;
                     entryOrigin = org + wi * baseOffset;
-                }
-                const TraceTarget tgt = pick_target(stage == 1, tInner, tOuter);
-                const Hit h = trace_dyn(tgt, stage == 1 ? TRACE_ANY : TRACE_FORWARD, stage == 4 ? entryOrigin : org, wi);
-                ++nTrace;
-                if (stage == 1) {
-                    if (h.t < 1e30f && tAny < 1e30f && h.t < tAny) { alive = false; stage = 5; }
-                    else stage = afterTermination;
+                    tr.begin(tOuter, 2, entryOrigin, wi);
+                    ++nTrace;
+                    stage = 3;
                 } else {
-                    hEntry = h;
-                    stage = 5;
+                    finish = true;
+                    stage = 0;
                 }
             }
+            bool enters = false;
+            if (finish && alive) {
+                rec_clear(f.st.rec[1], e);
+                if (entryT < 1e30f) {
+                    const V3 p = entryOrigin + wi * entryT;
+                    f.st.segE[e] = make_float4(p.x, p.y, p.z, baseOffset + entryT);
+                    f.st.segD[e] = make_float4(wi.x, wi.y, wi.z, 0.0f);
+                    enters = true;
+                }
+            }
+            queue_push(f.st.queue[qray], f.st.counts + qray, finish && alive, e);
+            queue_push(f.st.queue[2], f.st.counts + 2, enters, e);
+
+            // idle lanes fetch the next vertex
+            const unsigned idle = __ballot_sync(full, stage == 0);
+            if (more && idle) {
+                int base = 0;
+                const int leader = __ffs(idle) - 1;
+                if (lane == leader) base = atomicAdd(cursor, __popc(idle));
+                base = __shfl_sync(full, base, leader);
+                more = base + __popc(idle) < n;
+                const int i = base + __popc(idle & ((1u << lane) - 1));
+                if (stage == 0 && i < n) {
+                    e = f.st.queue[qin][i];
+                    const float4 O = f.st.rayO[e], D = f.st.rayD[e];  // written by k_bounce_sample
+                    org = f4v(O);
+                    wi = f4v(D);
+                    carried = D.w;
+                    if (O.w > 0.0f) {
+                        baseOffset = 0.0f;
+                        entryOrigin = org;
+                        tr.begin(tOuter, (carried > 0.0f ? 1 : 0) | 2 | 4, org, wi);
+                        stage = 1;
+                    }
+                }
+            }
+            // again while a lane still has a finished trace to act on, or is idle with work left
+            const bool pending = (stage != 0 && tr.done()) || (stage == 0 && more);
+            if (!__any_sync(full, pending)) break;
         }
-        if (alive) {
-            f.st.rayO[e] = make_float4(org.x, org.y, org.z, pdf);
-            f.st.rayD[e] = make_float4(wi.x, wi.y, wi.z, carried);
-            f.st.rayW[e] = make_float4(weight.x, weight.y, weight.z, 0.0f);
-            rec_clear(f.st.rec[1], e);
-            if (hEntry.t < 1e30f) {
-                const V3 p = entryOrigin + wi * hEntry.t;
-                f.st.segE[e] = make_float4(p.x, p.y, p.z, baseOffset + hEntry.t);
-                f.st.segD[e] = make_float4(wi.x, wi.y, wi.z, 0.0f);
-                enters = true;
+        if (!__any_sync(full, stage != 0)) break;  // nothing in flight and nothing left to fetch
+
+        // ================= traversal phase (convergent) =================
+        // Every iteration the warp votes: the unit kind wanted by most lanes runs, the others wait (and
+        // pile up until they are the majority), so each executed instruction carries a large lane group
+        // instead of node steps, triangle tests and pops serialising at a few lanes each.
+        for (;;) {
+            const int k = tr.kind();
+            const unsigned bN = __ballot_sync(full, k == 0), bT = __ballot_sync(full, k == 1), bP = __ballot_sync(full, k == 2);
+            const int busy = __popc(bN | bT | bP);
+            if (busy == 0 || (more && busy < kRefillBelow)) break;
+            const int nN = __popc(bN), nT = __popc(bT), nP = __popc(bP);
+            if (nP >= 8 || (nP >= nN && nP >= nT)) {
+                if (k == 2) tr.step_pop();
+            } else if (nN >= nT) {
+                if (k == 0) tr.step_node();
+            } else {
+                if (k == 1) tr.step_tri();
             }
         }
-        queue_push(f.st.queue[qray], f.st.counts + qray, alive, e);
-        queue_push(f.st.queue[2], f.st.counts + 2, enters, e);
     }
     stat_flush(f.st.stats + 0, nTrace);
-    stat_flush(f.st.stats + 2, nVert);
 }
 
 // Bounce, second half: hybrid mesh + merge, throughput/radiance update, Russian roulette.
@@ -504,9 +582,12 @@ int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStr
     for (int b = 1; b <= fp.maxBounces; ++b) {
         // path queue 0 -> ray queue 1 (+ segment queue 2) -> path queue 0
         cudaMemsetAsync(f.st.counts + 1, 0, 3 * sizeof(int), s);
+        cudaMemsetAsync(f.st.counts + 8, 0, sizeof(int), s);  // k_bounce_begin's work cursor
+        k_bounce_sample<<<grid, kQueueThreads, 0, s>>>(f, b, 0);
+        NRB_LAUNCHED("k_bounce_sample", s);
         k_bounce_begin<<<grid, kQueueThreads, 0, s>>>(f, b, 0, 1);
         NRB_LAUNCHED("k_bounce_begin", s);
-        ++launches;
+        launches += 2;
         launches += run_segments(f, net, 1, s, tail);
         cudaMemsetAsync(f.st.counts + 0, 0, sizeof(int), s);
         k_bounce_finish<<<grid, kQueueThreads, 0, s>>>(f, b, 1, 0);

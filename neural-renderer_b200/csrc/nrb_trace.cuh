@@ -144,6 +144,15 @@ __device__ __forceinline__ TraceTarget pick_target(bool first, const TraceTarget
     return t;
 }
 
+// Control flow: "while-while" (Aila & Laine 2009).  Each lane descends inner nodes until it holds a
+// leaf (or is done); the warp reconverges behind that loop, tests the leaves' triangles together,
+// pops, and repeats.  Structured loops without `continue` give the compiler one reconvergence point
+// per phase; the first version's single loop with early `continue`s left incoherent bounce rays at
+// 7.5 of 32 active lanes (ncu, profiles/r1_v2_ncu_k_bounce_begin.txt).  Per-lane results and visit
+// order are unchanged.
+constexpr int kTraceDone = static_cast<int>(0x80000000u);  // not a leaf ref: first < 2^26 (checked at upload)
+constexpr int kTracePop = static_cast<int>(0x80000001u);   // MultiTrace: the lane must pop its stack next
+
 static __device__ __noinline__ Hit trace_dyn(TraceTarget m, int mode, V3 o, V3 d) {
     Hit best{1e30f, 0.0f, 0.0f, 0u};
     if (m.numTriangles <= 0) return best;
@@ -155,57 +164,59 @@ static __device__ __noinline__ Hit trace_dyn(TraceTarget m, int mode, V3 o, V3 d
     int ref = m.rootRef;
     const NodePair* __restrict__ nodes = m.nodes;
     const TriBlock* __restrict__ tris = m.tris;
-    for (;;) {
-        if (ref >= 0) {
+    // pop: skip entries whose box entry distance is now beyond the best hit
+    auto pop = [&]() {
+        int next = kTraceDone;
+        while (sp > 0) {
+            const int2 e = stack[--sp];
+            if (!(__int_as_float(e.y) > best.t)) { next = e.x; break; }
+        }
+        return next;
+    };
+    while (ref != kTraceDone) {
+        while (ref >= 0) {
             const float4 a = __ldg(&nodes[ref].a), b = __ldg(&nodes[ref].b), c = __ldg(&nodes[ref].c);
             const int4 k = __ldg(&nodes[ref].d);
             float ln, rn;
             const bool hl = slab(o, inv, a.x, a.y, a.z, a.w, b.x, b.y, best.t, ln);
             const bool hr = slab(o, inv, b.z, b.w, c.x, c.y, c.z, c.w, best.t, rn);
             if (hl && hr) {
-                int nearRef = k.x, farRef = k.y;
-                float farT = rn;
-                if (rn < ln) { nearRef = k.y; farRef = k.x; farT = ln; }
-                if (sp < kTraceStack) stack[sp++] = make_int2(farRef, __float_as_int(farT));
-                ref = nearRef;
-                continue;
+                const bool rightFirst = rn < ln;
+                if (sp < kTraceStack) stack[sp++] = make_int2(rightFirst ? k.x : k.y, __float_as_int(rightFirst ? ln : rn));
+                ref = rightFirst ? k.y : k.x;
+            } else if (hl) {
+                ref = k.x;
+            } else if (hr) {
+                ref = k.y;
+            } else {
+                ref = pop();
             }
-            if (hl) { ref = k.x; continue; }
-            if (hr) { ref = k.y; continue; }
-        } else {
+        }
+        if (ref != kTraceDone) {
             const int packed = ~ref;
             const int first = packed >> kLeafCountBits;
             const int end = first + (packed & ((1 << kLeafCountBits) - 1)) + 1;
             for (int i = first; i < end; ++i) {
                 const float4 p = __ldg(&tris[i].p), q = __ldg(&tris[i].q), r = __ldg(&tris[i].r);
                 const float facing = dot(v3(p.w, q.w, r.w), d);
-                if (mode == TRACE_FORWARD && facing >= 0.0f) continue;
-                if (mode == TRACE_BACKWARD && facing <= 0.0f) continue;
+                bool ok = !((mode == TRACE_FORWARD && facing >= 0.0f) || (mode == TRACE_BACKWARD && facing <= 0.0f));
                 const V3 e1 = v3(q.x, q.y, q.z), e2 = v3(r.x, r.y, r.z);
                 const V3 pv = cross(d, e2);
                 const float det = dot(e1, pv);
-                if (fabsf(det) < 1e-8f) continue;
+                ok = ok && !(fabsf(det) < 1e-8f);
                 const float invDet = 1.0f / det;
                 const V3 tv = o - v3(p.x, p.y, p.z);
                 const float u = dot(tv, pv) * invDet;
-                if (u < 0.0f || u > 1.0f) continue;
+                ok = ok && !(u < 0.0f || u > 1.0f);
                 const V3 qv = cross(tv, e1);
                 const float v = dot(d, qv) * invDet;
-                if (v < 0.0f || u + v > 1.0f) continue;
+                ok = ok && !(v < 0.0f || u + v > 1.0f);
                 const float t = dot(e2, qv) * invDet;
-                if (t <= 1e-8f) continue;
-                if (t > 1e-6f && t < best.t) best = Hit{t, u, v, static_cast<uint32_t>(i)};
+                ok = ok && !(t <= 1e-8f) && t > 1e-6f && t < best.t;
+                if (ok) best = Hit{t, u, v, static_cast<uint32_t>(i)};
             }
+            ref = pop();
         }
-        bool found = false;
-        while (sp > 0) {
-            const int2 e = stack[--sp];
-            if (__int_as_float(e.y) > best.t) continue;
-            ref = e.x;
-            found = true;
-            break;
-        }
-        if (!found) break;
     }
     return best;
 }
@@ -252,8 +263,17 @@ __device__ __noinline__ static void trace_multi(TraceTarget m, int want, V3 o, V
         if ((set & 4) && !(tNear > best2)) out |= 4;
         return out;
     };
-    for (;;) {
-        if (ref >= 0) {
+    auto pop = [&]() {
+        int next = kTraceDone;
+        while (sp > 0) {
+            --sp;
+            const int again = live(smask[sp], __int_as_float(stack[sp].y));
+            if (again) { next = stack[sp].x; mask = again; break; }
+        }
+        return next;
+    };
+    while (ref != kTraceDone) {  // while-while, see trace_dyn
+        while (ref >= 0) {
             const float4 a = __ldg(&nodes[ref].a), b = __ldg(&nodes[ref].b), c = __ldg(&nodes[ref].c);
             const int4 k = __ldg(&nodes[ref].d);
             float ln, rn;
@@ -268,11 +288,17 @@ __device__ __noinline__ static void trace_multi(TraceTarget m, int want, V3 o, V
                 }
                 ref = rightFirst ? k.y : k.x;
                 mask = rightFirst ? mr : ml;
-                continue;
+            } else if (ml) {
+                ref = k.x;
+                mask = ml;
+            } else if (mr) {
+                ref = k.y;
+                mask = mr;
+            } else {
+                ref = pop();
             }
-            if (ml) { ref = k.x; mask = ml; continue; }
-            if (mr) { ref = k.y; mask = mr; continue; }
-        } else {
+        }
+        if (ref != kTraceDone) {
             const int packed = ~ref;
             const int first = packed >> kLeafCountBits;
             const int end = first + (packed & ((1 << kLeafCountBits) - 1)) + 1;
@@ -282,41 +308,153 @@ __device__ __noinline__ static void trace_multi(TraceTarget m, int want, V3 o, V
                 int acc = mask & 1;
                 if ((mask & 2) && !(facing >= 0.0f)) acc |= 2;
                 if ((mask & 4) && !(facing <= 0.0f)) acc |= 4;
-                if (!acc) continue;
                 const V3 e1 = v3(q.x, q.y, q.z), e2 = v3(r.x, r.y, r.z);
                 const V3 pv = cross(d, e2);
                 const float det = dot(e1, pv);
-                if (fabsf(det) < 1e-8f) continue;
+                bool ok = acc != 0 && !(fabsf(det) < 1e-8f);
                 const float invDet = 1.0f / det;
                 const V3 tv = o - v3(p.x, p.y, p.z);
                 const float u = dot(tv, pv) * invDet;
-                if (u < 0.0f || u > 1.0f) continue;
+                ok = ok && !(u < 0.0f || u > 1.0f);
                 const V3 qv = cross(tv, e1);
                 const float v = dot(d, qv) * invDet;
-                if (v < 0.0f || u + v > 1.0f) continue;
+                ok = ok && !(v < 0.0f || u + v > 1.0f);
                 const float t = dot(e2, qv) * invDet;
-                if (t <= 1e-8f || !(t > 1e-6f)) continue;
-                if ((acc & 1) && t < best0) best0 = t;
-                if ((acc & 2) && t < best1) best1 = t;
-                if ((acc & 4) && t < best2) best2 = t;
+                ok = ok && !(t <= 1e-8f || !(t > 1e-6f));
+                if (ok) {
+                    if ((acc & 1) && t < best0) best0 = t;
+                    if ((acc & 2) && t < best1) best1 = t;
+                    if ((acc & 4) && t < best2) best2 = t;
+                }
             }
+            ref = pop();
         }
-        bool found = false;
-        while (sp > 0) {
-            --sp;
-            const int again = live(smask[sp], __int_as_float(stack[sp].y));
-            if (!again) continue;
-            ref = stack[sp].x;
-            mask = again;
-            found = true;
-            break;
-        }
-        if (!found) break;
     }
     tAny = best0;
     tFwd = best1;
     tBwd = best2;
 }
+
+// The same fused traversal as a resumable per-lane engine: the warp-level scheduler of a persistent
+// kernel (k_bounce_begin) runs `round()` for the lanes that hold a live trace and refills finished
+// lanes with new work instead of letting them idle until the warp's longest ray ends.
+struct MultiTrace {
+    const NodePair* nodes;
+    const TriBlock* tris;
+    V3 o, d, inv;
+    float best0, best1, best2;
+    int ref, sp, mask, cur;  // cur: next triangle of the current leaf, -1 = leaf not started
+    int2 stack[kTraceStack];
+    unsigned char smask[kTraceStack];
+
+    __device__ __forceinline__ bool done() const { return ref == kTraceDone; }
+    __device__ __forceinline__ int live(int set, float tNear) const {
+        int out = 0;
+        if ((set & 1) && !(tNear > best0)) out |= 1;
+        if ((set & 2) && !(tNear > best1)) out |= 2;
+        if ((set & 4) && !(tNear > best2)) out |= 4;
+        return out;
+    }
+    __device__ __forceinline__ void begin(const TraceTarget& m, int want, V3 org, V3 dir) {
+        best0 = best1 = best2 = 1e30f;
+        ref = kTraceDone;
+        sp = 0;
+        cur = -1;
+        if (m.numTriangles <= 0 || want == 0) return;
+        o = org;
+        d = dir;
+        inv = v3(1.0f / dir.x, 1.0f / dir.y, 1.0f / dir.z);
+        float tn;
+        if (!slab_base(o, inv, m.bmin.x, m.bmin.y, m.bmin.z, m.bmax.x, m.bmax.y, m.bmax.z, tn) || tn > 1e30f) return;
+        nodes = m.nodes;
+        tris = m.tris;
+        mask = want;
+        ref = m.rootRef;
+    }
+    __device__ __forceinline__ int pop() {
+        int next = kTraceDone;
+        while (sp > 0) {
+            --sp;
+            const int again = live(smask[sp], __int_as_float(stack[sp].y));
+            if (again) { next = stack[sp].x; mask = again; break; }
+        }
+        return next;
+    }
+    // Units of work for a warp-level scheduler that votes on what to run next: a node-pair step, one
+    // triangle of the current leaf, or one stack entry of a pop.  kind(): 0 node, 1 triangle, 2 pop,
+    // 3 finished.
+    __device__ __forceinline__ int kind() const { return ref >= 0 ? 0 : (ref == kTraceDone ? 3 : (ref == kTracePop ? 2 : 1)); }
+    __device__ __forceinline__ void step_node() {
+        const float4 a = __ldg(&nodes[ref].a), b = __ldg(&nodes[ref].b), c = __ldg(&nodes[ref].c);
+        const int4 k = __ldg(&nodes[ref].d);
+        float ln, rn;
+        const bool bl = slab_base(o, inv, a.x, a.y, a.z, a.w, b.x, b.y, ln);
+        const bool br = slab_base(o, inv, b.z, b.w, c.x, c.y, c.z, c.w, rn);
+        const int ml = bl ? live(mask, ln) : 0, mr = br ? live(mask, rn) : 0;
+        if (ml && mr) {
+            const bool rightFirst = rn < ln;
+            if (sp < kTraceStack) {
+                stack[sp] = make_int2(rightFirst ? k.x : k.y, __float_as_int(rightFirst ? ln : rn));
+                smask[sp++] = static_cast<unsigned char>(rightFirst ? ml : mr);
+            }
+            ref = rightFirst ? k.y : k.x;
+            mask = rightFirst ? mr : ml;
+        } else if (ml) {
+            ref = k.x;
+            mask = ml;
+        } else if (mr) {
+            ref = k.y;
+            mask = mr;
+        } else {
+            ref = kTracePop;
+        }
+        cur = -1;
+    }
+    __device__ __forceinline__ void step_tri() {
+        const int packed = ~ref;
+        const int first = packed >> kLeafCountBits;
+        const int end = first + (packed & ((1 << kLeafCountBits) - 1)) + 1;
+        const int i = cur < 0 ? first : cur;
+        const float4 p = __ldg(&tris[i].p), q = __ldg(&tris[i].q), r = __ldg(&tris[i].r);
+        const float facing = dot(v3(p.w, q.w, r.w), d);
+        int acc = mask & 1;
+        if ((mask & 2) && !(facing >= 0.0f)) acc |= 2;
+        if ((mask & 4) && !(facing <= 0.0f)) acc |= 4;
+        const V3 e1 = v3(q.x, q.y, q.z), e2 = v3(r.x, r.y, r.z);
+        const V3 pv = cross(d, e2);
+        const float det = dot(e1, pv);
+        bool ok = acc != 0 && !(fabsf(det) < 1e-8f);
+        const float invDet = 1.0f / det;
+        const V3 tv = o - v3(p.x, p.y, p.z);
+        const float u = dot(tv, pv) * invDet;
+        ok = ok && !(u < 0.0f || u > 1.0f);
+        const V3 qv = cross(tv, e1);
+        const float v = dot(d, qv) * invDet;
+        ok = ok && !(v < 0.0f || u + v > 1.0f);
+        const float t = dot(e2, qv) * invDet;
+        ok = ok && !(t <= 1e-8f || !(t > 1e-6f));
+        if (ok) {
+            if ((acc & 1) && t < best0) best0 = t;
+            if ((acc & 2) && t < best1) best1 = t;
+            if ((acc & 4) && t < best2) best2 = t;
+        }
+        cur = i + 1;
+        if (cur >= end) ref = kTracePop;
+    }
+    __device__ __forceinline__ void step_pop() {
+        if (sp == 0) {
+            ref = kTraceDone;
+        } else {
+            --sp;
+            const int again = live(smask[sp], __int_as_float(stack[sp].y));
+            if (again) {
+                ref = stack[sp].x;
+                mask = again;
+                cur = -1;
+            }
+        }
+    }
+};
 
 template <bool STATS = false>
 __device__ __forceinline__ Hit trace_mode(const MeshDev& m, int mode, V3 o, V3 d, TraceStats* st = nullptr) {

@@ -8,7 +8,7 @@ fname = "?"; H = None
 agg = collections.OrderedDict()
 for r in rows:
     if not r: continue
-    if r[0] == "File Name": fname = os.path.basename(r[1]) or "?"; continue
+    if r[0] in ("File Name", "File Path"): fname = os.path.basename(r[1]) or "?"; continue
     if r[0] == "Line No": H = r; continue
     if H is None or len(r) < len(H): continue
     try: ie = float(r[H.index("Instructions Executed")] or 0); te = float(r[H.index("Thread Instructions Executed")] or 0); sm = float(r[H.index("# Samples")] or 0)
