@@ -305,16 +305,43 @@ def main():
     top = max(stages.items(), key=lambda kv: kv[1][0])
     per_kernel = {k: {"ms_per_step": v[0] / a.steps, "launches_per_step": v[1] / a.steps, "share": v[0] / total_stage_ms}
                   for k, v in sorted(stages.items(), key=lambda kv: -kv[1][0])}
+    # Roofline of the dominant DENSE kernel of the path: the MLP stage is the only contraction
+    # (131072 FLOP per query); achieved = FLOPs of the queries counted on the device /
+    # the kernel's CUDA-event time summed over its launches of one step, against the measured
+    # sustained bf16/fp16 tensor peak.  The other stages are listed beside it with the resource that
+    # bounds them (ncu: profiles/): the encoder gathers from shared memory, traversal is issue/L1 bound.
     roof = None
+    stage_ms = lambda name: stages[name][0] / a.steps if name in stages else None
+    traffic_db = {}
+    tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(tpath):
+        traffic_db = json.load(open(tpath))
     qkeys = [k for k in stages if k.startswith("k_neural_query") or k.startswith("k_query_")]
     if qkeys and a.mode == "neural":
+        mlp_key = "k_query_mlp" if "k_query_mlp" in stages else qkeys[0]
+        m_ms = stage_ms(mlp_key)
         q_ms = sum(stages[k][0] for k in qkeys) / a.steps
-        tf = neural_q * FLOPS_PER_QUERY / (q_ms * 1e-3) / 1e12
-        roof = {"kernel": "+".join(sorted(qkeys)), "bound": "tensor", "achieved": tf, "peak": pk["tf_sustained"], "unit": "TFLOP/s",
-                "frac": tf / pk["tf_sustained"], "traffic": None, "peak_source": pk["src"] + " sustained bf16 (fp16 same pipe rate)",
-                "queries_per_step": neural_q, "flops_per_query": FLOPS_PER_QUERY, "ms_per_step": q_ms,
-                "hbm_gbs": neural_q * HBM_BYTES_PER_QUERY / (q_ms * 1e-3) / 1e9,
-                "l2_gather_gbs": neural_q * 1536 / (q_ms * 1e-3) / 1e9, "top_kernel_by_time": top[0]}
+        tf = neural_q * FLOPS_PER_QUERY / (m_ms * 1e-3) / 1e12
+        tr = traffic_db.get(mlp_key)
+        roof = {"kernel": mlp_key, "bound": "tensor", "achieved": tf, "peak": pk["tf_sustained"], "unit": "TFLOP/s",
+                "frac": tf / pk["tf_sustained"],
+                "traffic": (tr["dram_bytes_per_query"] * neural_q / max(1.0, stages[mlp_key][1] / a.steps)) if tr else None,
+                "traffic_note": "DRAM bytes per launch (ncu --set full, profiles/), scaled per query" if tr else None,
+                "peak_source": pk["src"] + " sustained bf16 (fp16 same pipe rate)",
+                "queries_per_step": neural_q, "flops_per_query": FLOPS_PER_QUERY, "ms_per_step": m_ms,
+                "launches_per_step": stages[mlp_key][1] / a.steps,
+                "whole_query": {"kernels": sorted(qkeys), "ms_per_step": q_ms,
+                                "Gqueries_per_s": neural_q / (q_ms * 1e-3) / 1e9,
+                                "tensor_TFLOPs": neural_q * FLOPS_PER_QUERY / (q_ms * 1e-3) / 1e12,
+                                "hbm_gbs": neural_q * HBM_BYTES_PER_QUERY / (q_ms * 1e-3) / 1e9},
+                "top_kernel_by_time": top[0]}
+        e_ms = stage_ms("k_query_encode")
+        if e_ms:
+            smem_peak = 148 * 128 * (clocks["sm_mhz"] or 1965.0) * 1e6 / 1e9 if clocks else 148 * 128 * 1.965e9 / 1e9
+            roof["encode"] = {"kernel": "k_query_encode", "bound": "shared-memory gathers", "ms_per_step": e_ms,
+                              "achieved": neural_q * 1536 / (e_ms * 1e-3) / 1e9, "unit": "GB/s gathered",
+                              "peak": smem_peak, "peak_source": "148 SMs x 128 B/clk x SM clock (conflict-free)",
+                              "frac": neural_q * 1536 / (e_ms * 1e-3) / 1e9 / smem_peak}
     else:
         k, v = top
         roof = {"kernel": k, "bound": "hbm", "achieved": None, "peak": pk["hbm"], "unit": "GB/s", "frac": None, "traffic": None,

@@ -176,6 +176,15 @@ __device__ __forceinline__ void encode_point(const LevelInfo& lv, const unsigned
         const uint32_t az0 = (hz << kShift) & lv.mask, az1 = ((hz + 805459861u) << kShift) & lv.mask;
 #pragma unroll
         for (int c = 0; c < 8; ++c) off[c] = ((c & 1) ? ax1 : ax0) ^ ((c & 2) ? ay1 : ay0) ^ ((c & 4) ? az1 : az0);
+    } else if (lv.dense && lv.pow2) {
+        // (x + y*res + z*res^2) & (size-1), scaled to bytes: shift the three terms once, then an add3 and
+        // a mask per corner (level CTAs of a dense level would otherwise be the kernel's stragglers)
+        const uint32_t sy = lv.res << kShift, sz = (lv.res * lv.res) << kShift;
+        const uint32_t ax0 = g[0] << kShift, ax1 = ax0 + (1u << kShift);
+        const uint32_t ay0 = g[1] * sy, ay1 = ay0 + sy;
+        const uint32_t az0 = g[2] * sz, az1 = az0 + sz;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) off[c] = (((c & 1) ? ax1 : ax0) + ((c & 2) ? ay1 : ay0) + ((c & 4) ? az1 : az0)) & lv.mask;
     } else {
 #pragma unroll
         for (int c = 0; c < 8; ++c)
@@ -216,6 +225,8 @@ __device__ __forceinline__ void encode_tasks(const NetDev& net, const LevelInfo&
     const int PF = P * F, PLF = PF * L, shN = net.shDegree * net.shDegree;
     const uint32_t tileBytes = static_cast<uint32_t>(ek) * kTileM * 2;
     const int k0 = level * PF;  // first column of this level
+    const bool lPow2 = (L & (L - 1)) == 0;
+    auto shOwner = [&](int group) { return (lPow2 ? (group & (L - 1)) : (group % L)) == level; };
     // Input rows reach the lanes through a per-warp two-stage cp.async ring: the 32 rows of a task are
     // one contiguous, 16-byte-aligned block of 128*D bytes, fetched while the previous task computes.
     const int stageFloats = 32 * D;
@@ -226,11 +237,12 @@ __device__ __forceinline__ void encode_tasks(const NetDev& net, const LevelInfo&
         const size_t off = static_cast<size_t>(rowBase + tile * kTileM + ((task & 3) << 5)) * D * 4;
         const unsigned char* src = reinterpret_cast<const unsigned char*>(in) + off;
         const uint32_t dst = tc::s32(stage + slot * stageFloats);
-        for (int i = lane; i < 8 * D; i += 32) {
-            const size_t o = off + 16u * i;
-            if (o + 16 <= inBytes) {
+        if (off + 128u * D <= inBytes) {  // the whole 32-row block is inside the batch (all but the last task)
+            for (int i = lane; i < 8 * D; i += 32)
                 asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * i), "l"(src + 16u * i) : "memory");
-            } else {
+        } else {
+            for (int i = lane; i < 8 * D; i += 32) {
+                const size_t o = off + 16u * i;
                 for (int j = 0; j < 4; ++j)
                     stage[slot * stageFloats + 4 * i + j] = o + 4u * j + 4 <= inBytes ? __ldg(in + (o >> 2) + j) : 0.0f;
             }
@@ -294,7 +306,7 @@ __device__ __forceinline__ void encode_tasks(const NetDev& net, const LevelInfo&
                     else *reinterpret_cast<uint32_t*>(dst) = w[p][0];
                 }
         }
-        if ((tile * 4 + g) % L == level && PLF < ek) {
+        if (shOwner(tile * 4 + g) && PLF < ek) {
             // spherical harmonics + K padding: columns [PLF, ek), PLF % 8 == 0 is a support condition
             __half tail[32];
 #pragma unroll
