@@ -48,6 +48,7 @@ def parse():
     ap.add_argument("--subdiv", type=int, default=7)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-tail-graph", action="store_true", help="fixed nine-iteration segment tail (profiling aid)")
     return ap.parse_args()
 
 
@@ -80,6 +81,8 @@ def setup(nrb, a, scene, lib=None):
     if a.mode == "neural":
         r.load_weights(nrb.scenes.make_weights())
         r.set_use_neural_query(True)
+        if getattr(a, "no_tail_graph", False) and lib is None:
+            r.set_tail_graph(False)
     return r, eye, basis
 
 
