@@ -201,6 +201,13 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    # Multi-GPU runs are WEAK-scaled: the 1080p frame is sharded by row bands and the samples per pixel
+    # grow with the GPU count, so every GPU keeps the element count of the 1-GPU frame (SURVEY.md §8e:
+    # the path shards by pixels with no data-path collective; the one exchange is the frame gather).
+    n_scale = max(world, a.gpus if a.impl == "reference" else 1)
+    a.base_spp = a.spp
+    if n_scale > 1:
+        a.spp = a.spp * n_scale
     if a.impl == "reference":
         run_reference(a, rank)
         return
@@ -352,9 +359,9 @@ def main():
 
     line = {
         "metric": "neural-render Mrays/s at 1080p", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": a.steps,
-        "warmup": max(3, a.warmup), "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "strong",
+        "warmup": max(3, a.warmup), "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32 geometry + f16 network (f32 accumulate)", "data": "synthetic",
-        "config": {"workload": workload_name(a), "mode": a.mode, "partition": f"{band}-row bands round-robin, scene+weights replicated",
+        "config": {"workload": workload_name(a), "mode": a.mode, "partition": f"{band}-row bands round-robin, scene+weights replicated; spp = {a.base_spp} x n_gpus (weak scaling)",
                    "l2": "per-frame wavefront state (~0.4 KB/path) exceeds L2; BVH and hash tables are L2-resident by design; "
                          "every step draws new samples (progressive accumulation)"},
         "clocks": clocks,
