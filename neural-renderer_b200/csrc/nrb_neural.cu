@@ -215,7 +215,10 @@ int launch_neural_query(const NetDev& net, const float* in, size_t n, const int*
                         cudaStream_t s) {
     if (n == 0) return 0;
     const int which = g_queryKernel & 0xff;
-    if ((which == 0 || which == 3) && net.xtRows > 0 && net.packedW && split_query_supported(net)) {
+    // automatic choice: the split pays when a lane's encoder task carries enough gathers to amortise its
+    // fixed cost (measured: 3 points x F4 -> 2.7x the fused kernel; 1 point x F2 -> 0.5x)
+    const bool splitPays = net.nPoints * net.nFeatures >= 8;
+    if ((which == 3 || (which == 0 && splitPays)) && net.xtRows > 0 && net.packedW && split_query_supported(net)) {
         NetDev tmp = net;
         tmp.debug = g_queryKernel >> 8;
         return launch_split_query(tmp, in, n, dCount, out, s);
