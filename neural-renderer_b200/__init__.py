@@ -8,7 +8,7 @@ from ._capi import (BVH_NODE_DTYPE, HIT_DTYPE, Lib, Material, MeshDesc, NNConfig
                     SLOT_ADDITIONAL, SLOT_INNER, SLOT_ORIGINAL, SLOT_OUTER, TRACE_ANY, TRACE_BACKWARD_ONLY,
                     TRACE_FORWARD_ONLY, product_lib)
 from .renderer import MeshData, RenderBasis, RendererNeural, Scene, compute_camera_basis, look_at_basis
-from . import scenes, tiles
+from . import evaluate, metrics, scenes, tiles
 
-__all__ = ["RendererNeural", "Scene", "MeshData", "RenderBasis", "Material", "NNConfig", "scenes", "tiles",
+__all__ = ["RendererNeural", "Scene", "MeshData", "RenderBasis", "Material", "NNConfig", "scenes", "tiles", "evaluate", "metrics",
            "compute_camera_basis", "look_at_basis", "product_lib", "Lib", "NrbError"]
