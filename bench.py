@@ -245,6 +245,7 @@ def main():
         if gathered is None:
             gathered = torch.empty_like(t)
         gathered.copy_(t)  # non-owned rows are zero on every rank, so a sum over ranks is the gather
+        stream.wait_stream(torch.cuda.current_stream())  # the next frame's finalize must not overtake this read
         dist.reduce(gathered, dst=0, op=dist.ReduceOp.SUM)
 
     def barrier():
@@ -272,15 +273,23 @@ def main():
         r.render(eye)
         gather()
 
-    host_frame = torch.empty(a.width * a.height * 4, dtype=torch.uint8).pin_memory()
+    host_frames = [torch.empty(a.width * a.height * 4, dtype=torch.uint8).pin_memory() for _ in range(2)]
+    e2e_step = [0]
 
     def step_e2e():
+        """One frame through the public API with host buffers on both sides: camera in, RGBA frame out.
+        The device->host read of frame k is enqueued right behind it (nrb_read_pixels_async: second
+        stream, double-buffered pinned destination) and so travels under the kernels of frame k+1; the
+        closing barrier of the timed region waits for every transfer."""
         r.set_camera_basis(basis)          # host inputs of the step (camera), uploaded with the launches
         r.render(eye)
         gather()
-        if rank == 0:
-            src = gathered if world > 1 else frame_tensor()
-            host_frame.copy_(src, non_blocking=False)   # device->host read of the step's result
+        dst = host_frames[e2e_step[0] & 1]
+        e2e_step[0] += 1
+        if world == 1:
+            r.read_pixels_async(dst.data_ptr(), dst.numel())
+        elif rank == 0:
+            dst.copy_(gathered, non_blocking=True)
 
     for _ in range(max(3, a.warmup)):
         step_device()

@@ -230,6 +230,12 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]);
 void* nrb_device_pixels(const nrb_renderer* r);
 /* Convenience for host callers: blocking copy of devicePixels into rgba (4*width*height B). */
 int nrb_read_pixels(nrb_renderer* r, void* rgba, size_t bytes);
+/* (new) Non-blocking variant for callers that stream frames: returns once the copy is enqueued on
+ * a second stream, so the transfer of this frame overlaps the kernels of the next nrb_render.
+ * rgba should be pinned; it is valid after nrb_sync() (or once the legacy default stream, which
+ * the copy is joined to like nrb_render, has drained).  One transfer in flight per renderer: a
+ * second call waits on the device for the first. */
+int nrb_read_pixels_async(nrb_renderer* r, void* rgba, size_t bytes);
 int nrb_width(const nrb_renderer* r);
 int nrb_height(const nrb_renderer* r);
 uint32_t nrb_accum_sample_count(const nrb_renderer* r);

@@ -136,7 +136,7 @@ class Lib:
             "get_option": ([vp, i], i), "set_envmap_rotation": ([vp, f], i),
             "set_constant_neural_color": ([vp, P(f)], i), "set_direct_env_color": ([vp, P(f)], i),
             "reset_samples": ([vp], i), "set_tile": ([vp, i, i, i], i), "render": ([vp, P(f)], i),
-            "device_pixels": ([vp], vp), "read_pixels": ([vp, vp, sz], i), "width": ([vp], i), "height": ([vp], i),
+            "device_pixels": ([vp], vp), "read_pixels": ([vp, vp, sz], i), "read_pixels_async": ([vp, vp, sz], i), "width": ([vp], i), "height": ([vp], i),
             "accum_sample_count": ([vp], C.c_uint32), "get_timings": ([vp, P(C.c_double), P(i), P(C.c_uint64)], i),
             "get_counters": ([vp, P(C.c_uint64)], i), "read_buffer": ([vp, C.c_char_p, vp, sz], i),
             "trace_rays": ([vp, i, i, vp, vp, sz, vp], i), "trace_rays_host": ([vp, i, i, vp, vp, sz, vp], i),

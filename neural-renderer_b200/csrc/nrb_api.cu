@@ -98,6 +98,10 @@ struct nrb_renderer {
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t evStart = nullptr, evStop = nullptr, evJoin = nullptr;
+    // nrb_read_pixels_async: frame -> staging copy on `stream`, staging -> host on `copyStream`
+    cudaStream_t copyStream = nullptr;
+    cudaEvent_t evStaged = nullptr, evCopied = nullptr;
+    bool copyPending = false;
 
     // scene
     MeshSlot mesh[4];
@@ -133,7 +137,7 @@ struct nrb_renderer {
     // wavefront state
     std::vector<DevBuf> pool;
     State st{};
-    DevBuf accum, pixels;
+    DevBuf accum, pixels, pixelsStaged;
     size_t stateElems = 0, accumPixels = 0, pixelCount = 0;
     int localHeight = 0;
 
@@ -358,6 +362,9 @@ void nrb_destroy(nrb_renderer* r) {
     if (r->evStart) cudaEventDestroy(r->evStart);
     if (r->evStop) cudaEventDestroy(r->evStop);
     if (r->evJoin) cudaEventDestroy(r->evJoin);
+    if (r->copyStream) { cudaStreamSynchronize(r->copyStream); cudaStreamDestroy(r->copyStream); }
+    if (r->evStaged) cudaEventDestroy(r->evStaged);
+    if (r->evCopied) cudaEventDestroy(r->evCopied);
     if (r->prof.ready)
         for (int i = 0; i <= StageProfiler::kMaxMarks; ++i) cudaEventDestroy(r->prof.ev[i]);
     if (r->stream) cudaStreamDestroy(r->stream);
@@ -573,6 +580,8 @@ int nrb_output_dims(const nrb_renderer*) { return 16; }
 int nrb_sync(nrb_renderer* r) {
     NRB_CUDA(cudaSetDevice(r->device));
     NRB_CUDA(cudaStreamSynchronize(r->stream));
+    if (r->copyStream) NRB_CUDA(cudaStreamSynchronize(r->copyStream));
+    r->copyPending = false;
     return NRB_OK;
 }
 
@@ -811,6 +820,36 @@ int nrb_read_pixels(nrb_renderer* r, void* rgba, size_t bytes) {
     NRB_CUDA(cudaSetDevice(r->device));
     NRB_CUDA(cudaMemcpyAsync(rgba, r->pixels.p, bytes, cudaMemcpyDeviceToHost, r->stream));
     NRB_CUDA(cudaStreamSynchronize(r->stream));
+    return NRB_OK;
+}
+
+// Overlapped read-back for callers that stream frames (viewer, bench e2e): the frame is copied to a
+// staging buffer on the render stream (8 MB device-to-device, microseconds) and from there to the
+// host on a second stream, so the PCIe transfer of frame k runs under the kernels of frame k+1.
+// The staging buffer is reused only after the previous transfer has completed (event wait).
+int nrb_read_pixels_async(nrb_renderer* r, void* rgba, size_t bytes) {
+    if (!r || !rgba) return fail(NRB_ERR_INVALID, "null argument");
+    if (bytes != r->pixelCount * 4 || !r->pixels.p) return fail(NRB_ERR_SIZE, "pixel buffer size mismatch");
+    NRB_CUDA(cudaSetDevice(r->device));
+    if (!r->copyStream) {
+        NRB_CUDA(cudaStreamCreateWithFlags(&r->copyStream, cudaStreamNonBlocking));
+        NRB_CUDA(cudaEventCreateWithFlags(&r->evStaged, cudaEventDisableTiming));
+        NRB_CUDA(cudaEventCreateWithFlags(&r->evCopied, cudaEventDisableTiming));
+    }
+    if (r->pixelsStaged.bytes != bytes) {
+        NRB_CUDA(cudaStreamSynchronize(r->copyStream));
+        NRB_CUDA(cudaStreamSynchronize(r->stream));
+        NRB_CUDA(r->pixelsStaged.alloc(bytes));
+        r->copyPending = false;
+    }
+    if (r->copyPending) NRB_CUDA(cudaStreamWaitEvent(r->stream, r->evCopied, 0));
+    NRB_CUDA(cudaMemcpyAsync(r->pixelsStaged.p, r->pixels.p, bytes, cudaMemcpyDeviceToDevice, r->stream));
+    NRB_CUDA(cudaEventRecord(r->evStaged, r->stream));
+    NRB_CUDA(cudaStreamWaitEvent(r->copyStream, r->evStaged, 0));
+    NRB_CUDA(cudaMemcpyAsync(rgba, r->pixelsStaged.p, bytes, cudaMemcpyDeviceToHost, r->copyStream));
+    NRB_CUDA(cudaEventRecord(r->evCopied, r->copyStream));
+    NRB_CUDA(cudaStreamWaitEvent(cudaStreamLegacy, r->evCopied, 0));  // same join rule as nrb_render
+    r->copyPending = true;
     return NRB_OK;
 }
 

@@ -324,6 +324,10 @@ class RendererNeural:
         self.lib.check(self.lib.fn("read_pixels")(self._h, out.ctypes.data, out.nbytes), "read_pixels")
         return out
 
+    def read_pixels_async(self, host_ptr: int, nbytes: int):
+        """Enqueue the frame's copy into (pinned) host memory on the copy stream; valid after sync()."""
+        self.lib.check(self.lib.fn("read_pixels_async")(self._h, host_ptr, nbytes), "read_pixels_async")
+
     def read_buffer(self, name: str) -> np.ndarray:
         n = self.width() * self.height() * max(1, self._spp)
         shape, dt = {"hit_positions": ((n, 3), np.float32), "hit_normals": ((n, 3), np.float32),

@@ -224,3 +224,34 @@ def test_fused_three_mode_traversal_is_exact(oracle_lib):
         for mode, key in ((nrb.TRACE_ANY, "t"), (nrb.TRACE_FORWARD_ONLY, "u"), (nrb.TRACE_BACKWARD_ONLY, "v")):
             ref = orc.trace_rays(slot, mode, o, d)
             assert np.array_equal(fused[key], ref["t"]), (slot, mode)
+
+
+def test_async_read_back_is_the_frame():
+    """nrb_read_pixels_async (second stream, staged copy): frames streamed back while the next one renders are
+    the frames a blocking read returns."""
+    import torch
+    scene = nrb.scenes.make_scene("ico", 3)
+    eye, basis = nrb.scenes.default_camera()
+
+    def renderer():
+        r = nrb.RendererNeural(scene)
+        r.resize(320, 200)
+        r.set_camera_basis(basis)
+        r.set_bounce_count(1)
+        return r
+
+    a, b = renderer(), renderer()
+    n = 320 * 200 * 4
+    host = [torch.empty(n, dtype=torch.uint8).pin_memory() for _ in range(4)]
+    want = []
+    for k in range(4):
+        a.render(eye)
+        a.read_pixels_async(host[k].data_ptr(), n)  # no wait: the next render is enqueued behind it
+        b.render(eye)
+        want.append(b.read_pixels().reshape(-1))
+    a.sync()
+    for k in range(4):
+        assert np.array_equal(host[k].numpy(), want[k]), k
+    assert not np.array_equal(want[0], want[3])  # accumulation moved on between the frames
+    with pytest.raises(nrb.NrbError):
+        a.read_pixels_async(host[0].data_ptr(), n - 4)
