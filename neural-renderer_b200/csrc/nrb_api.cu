@@ -116,6 +116,7 @@ struct nrb_renderer {
     DevBuf grid, mlp, packedW, xt;
     SegTail segTail;
     bool useTailGraph = true;
+    bool denoise = false;
     size_t gridParams = 0, mlpParams = 0;
     bool weightsLoaded = false;
 
@@ -529,6 +530,7 @@ int nrb_set_option(nrb_renderer* r, int option, int value) {
         case NRB_OPT_PROFILE: r->profile = value; break;
         case NRB_OPT_QUERY_KERNEL: set_query_kernel(value); break;
         case NRB_OPT_TAIL_GRAPH: r->useTailGraph = value != 0; break;
+        case NRB_OPT_DENOISE: r->denoise = value != 0; break;
         case NRB_OPT_USE_HARDWARE_RT: break;  // accepted, ignored: there is no OptiX path
         default: return fail(NRB_ERR_INVALID, "unknown option");
     }
@@ -549,6 +551,7 @@ int nrb_get_option(const nrb_renderer* r, int option) {
         case NRB_OPT_PROFILE: return r->profile;
         case NRB_OPT_QUERY_KERNEL: return query_kernel();
         case NRB_OPT_TAIL_GRAPH: return r->useTailGraph ? 1 : 0;
+        case NRB_OPT_DENOISE: return r->denoise ? 1 : 0;
         default: return 0;
     }
 }
@@ -711,6 +714,7 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     if (r->classicMeshIndex == 1 && r->mesh[NRB_MESH_INNER_SHELL].view.numTriangles > 0) classicSlot = NRB_MESH_INNER_SHELL;
     else if (r->classicMeshIndex == 2 && r->mesh[NRB_MESH_OUTER_SHELL].view.numTriangles > 0) classicSlot = NRB_MESH_OUTER_SHELL;
 
+    if (r->denoise && r->world > 1) return fail(NRB_ERR_INVALID, "NRB_OPT_DENOISE needs the whole frame on one GPU (nrb_set_tile world 1)");
     const size_t framePixels = static_cast<size_t>(r->width) * r->height;
     r->localHeight = local_rows(r);
     const size_t localPixels = static_cast<size_t>(r->width) * r->localHeight;
@@ -799,6 +803,7 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     int launches;
     if (neural) launches = launch_neural_frame(f, r->net, r->lambertView, s, (r->useTailGraph && getenv("NRB_DEBUG") == nullptr) ? &r->segTail : nullptr);
     else launches = launch_gt_frame(f, r->lambertView, s);
+    if (r->denoise && !r->lambertView) launches += launch_denoise(f, s);
     set_stage_profiler(nullptr);
     r->profPending = r->profile != 0;
     NRB_CUDA(cudaEventRecord(r->evStop, s));

@@ -56,5 +56,6 @@ struct SegTail {
 int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStream_t s, SegTail* tail);
 int launch_finalize(const Frame& f, cudaStream_t s);
 int launch_lambert(const Frame& f, cudaStream_t s);
+int launch_denoise(const Frame& f, cudaStream_t s);  // world == 1 only: reads accum/rec[0] of the whole frame
 
 }  // namespace nrb

@@ -298,6 +298,10 @@ class RendererNeural:
         nine fixed launches per pass."""
         self._opt(K.OPT_TAIL_GRAPH, 1 if v else 0)
 
+    def set_denoise(self, v: bool):
+        """Joint bilateral filter of the accumulated frame (reference src/denoiser.cuh) on the way to devicePixels()."""
+        self._opt(K.OPT_DENOISE, int(v))
+
     def stages(self):
         """-> {kernel name: (total ms, launches)} accumulated since reset_stages()."""
         out, i = {}, 0

@@ -247,7 +247,7 @@ struct orc_renderer {
     // RendererNeural state (cuda_renderer_neural.h:216-277)
     RenderBasis basis{};
     int width = 0, height = 0;
-    bool lambertView = false, useNeuralQuery = false;
+    bool lambertView = false, useNeuralQuery = false, denoise = false;
     int samplesPerPixel = 1, bounceCount = 0, classicMeshIndex = 0;
     float envmapRotation = 0.0f;
     bool useConstantNeuralColor = false;
@@ -847,6 +847,52 @@ void orc_renderer::render(Vec3 camPos) {
         });
     };
 
+    // bilateralDenoiseKernel, src/denoiser.cuh:47-113 (shipped by the reference, never launched there):
+    // guides = sample-0 primary-hit normals / albedo, accumCount = samples accumulated so far.
+    auto denoisePass = [&]() {
+        const int kRadius = 5;                                     // denoiser.cuh:31
+        const float kSigmaSpatial = 3.0f, kNormalAlpha = 64.0f, kSigmaAlbedo = 0.1f;  // :32-34
+        const int width = params.width, height = params.height;
+        const int accumCount = static_cast<int>(params.sampleOffset) + params.samplesPerPixel;
+        const float* guideNormals = hitNormals.data();
+        const float* guideAlbedo = hitColors.data();
+        forPixels(params, [&](int cx, int cy) {
+            int centerIdx = cy * width + cx;
+            float invAccum = 1.0f / fmaxf(1.0f, static_cast<float>(accumCount));
+            Vec3 centerColor = accum[centerIdx] * invAccum;
+            float cnx = guideNormals[centerIdx * 3 + 0], cny = guideNormals[centerIdx * 3 + 1], cnz = guideNormals[centerIdx * 3 + 2];
+            float cax = guideAlbedo[centerIdx * 3 + 0], cay = guideAlbedo[centerIdx * 3 + 1], caz = guideAlbedo[centerIdx * 3 + 2];
+            const float invSigmaSpatial2 = 1.0f / (2.0f * kSigmaSpatial * kSigmaSpatial);
+            const float invSigmaAlbedo2 = 1.0f / (2.0f * kSigmaAlbedo * kSigmaAlbedo);
+            Vec3 weightedSum(0.0f, 0.0f, 0.0f);
+            float totalWeight = 0.0f;
+            for (int dy = -kRadius; dy <= kRadius; ++dy) {
+                int ny = cy + dy;
+                if (ny < 0 || ny >= height) continue;
+                for (int dx = -kRadius; dx <= kRadius; ++dx) {
+                    int nx = cx + dx;
+                    if (nx < 0 || nx >= width) continue;
+                    int nIdx = ny * width + nx;
+                    Vec3 neighborColor = accum[nIdx] * invAccum;
+                    float dist2 = static_cast<float>(dx * dx + dy * dy);
+                    float wSpatial = expf(-dist2 * invSigmaSpatial2);
+                    float nnx = guideNormals[nIdx * 3 + 0], nny = guideNormals[nIdx * 3 + 1], nnz = guideNormals[nIdx * 3 + 2];
+                    float normalDot = fmaxf(0.0f, fminf(1.0f, cnx * nnx + cny * nny + cnz * nnz));
+                    float wNormal = powf(normalDot, kNormalAlpha);
+                    float dax = guideAlbedo[nIdx * 3 + 0] - cax, day = guideAlbedo[nIdx * 3 + 1] - cay, daz = guideAlbedo[nIdx * 3 + 2] - caz;
+                    float wAlbedo = expf(-(dax * dax + day * day + daz * daz) * invSigmaAlbedo2);
+                    float w = wSpatial * wNormal * wAlbedo;
+                    weightedSum += neighborColor * w;
+                    totalWeight += w;
+                }
+            }
+            Vec3 color = (totalWeight > 0.0f) ? (weightedSum * (1.0f / totalWeight)) : centerColor;
+            color = encodeSrgb(color);
+            pixels[centerIdx] = Px4{static_cast<unsigned char>(color.x * 255.0f), static_cast<unsigned char>(color.y * 255.0f),
+                                    static_cast<unsigned char>(color.z * 255.0f), 255};
+        });
+    };
+
     auto lambert = [&]() {  // lambertKernel :1547-1607
         forPixels(params, [&](int x, int y) {
             int pixelIdx = y * params.width + x;
@@ -1022,6 +1068,7 @@ void orc_renderer::render(Vec3 camPos) {
                 curDist = bounceDistances.data();
             }
             finalize();
+            if (denoise) denoisePass();
             accumSampleCount += static_cast<uint32_t>(spp);
         } else {
             lambert();
@@ -1080,6 +1127,7 @@ void orc_renderer::render(Vec3 camPos) {
                 curFlags = bounceHitFlags.data();
             }
             finalize();
+            if (denoise) denoisePass();
             accumSampleCount += static_cast<uint32_t>(spp);
         }
     }
@@ -1225,6 +1273,7 @@ int orc_set_option(orc_renderer* r, int opt, int v) {
         case NRB_OPT_USE_ADDITIONAL_MESH: r->useAdditionalMesh = v != 0; break;
         case NRB_OPT_USE_CONSTANT_NEURAL_COLOR: r->useConstantNeuralColor = v != 0; break;
         case NRB_OPT_USE_DIRECT_ENV_COLOR: r->useDirectEnvColor = v != 0; break;
+        case NRB_OPT_DENOISE: r->denoise = v != 0; break;
         case NRB_OPT_CAPTURE: case NRB_OPT_USE_HARDWARE_RT: break;
         default: return fail(NRB_ERR_INVALID, "unknown option");
     }

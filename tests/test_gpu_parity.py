@@ -255,3 +255,32 @@ def test_async_read_back_is_the_frame():
     assert not np.array_equal(want[0], want[3])  # accumulation moved on between the frames
     with pytest.raises(nrb.NrbError):
         a.read_pixels_async(host[0].data_ptr(), n - 4)
+
+
+def test_denoiser_matches_oracle(oracle_lib):
+    """NRB_OPT_DENOISE: bilateralDenoiseKernel of the reference (src/denoiser.cuh:47-113) behind finalize, GPU vs
+    the oracle's restatement on the same noisy 2-spp frame (8-bit output; device expf/powf may move a value
+    by one step), and the property it exists for: closer to a converged render than the unfiltered frame."""
+    scene = nrb.scenes.make_scene("ico", 3)
+    prod, orc, eye = make_pair(scene, oracle_lib, 160, 96, spp=2, bounces=2)
+    for r in (prod, orc):
+        r.set_denoise(True)
+        r.render(eye)
+    a, b = prod.read_pixels(), orc.read_pixels()
+    d = np.abs(a.astype(int) - b.astype(int))
+    assert d.max() <= 1 and (d > 0).mean() < 0.01, (d.max(), (d > 0).mean())
+    prod.set_denoise(False)
+    prod.reset_samples()
+    prod.render(eye)
+    noisy = prod.read_pixels()
+    assert not np.array_equal(noisy, a)
+    prod.set_samples_per_pixel(64)
+    for _ in range(4):
+        prod.render(eye)
+    converged = prod.read_pixels()
+    assert psnr8(a, converged) > psnr8(noisy, converged) + 1.0
+    # accumulation is untouched by the filter: turning it off later shows the plain running mean
+    prod.set_tile(16, 0, 2)
+    prod.set_denoise(True)
+    with pytest.raises(nrb.NrbError):
+        prod.render(eye)
