@@ -10,5 +10,7 @@ from ._capi import (BVH_NODE_DTYPE, HIT_DTYPE, Lib, Material, MeshDesc, NNConfig
 from .renderer import MeshData, RenderBasis, RendererNeural, Scene, compute_camera_basis, look_at_basis
 from . import evaluate, metrics, scenes, tiles
 
+# torch_net (the PyTorch twin of the network + weight-file exporter) is imported on demand:
+#   importlib.import_module("neural-renderer_b200.torch_net")
 __all__ = ["RendererNeural", "Scene", "MeshData", "RenderBasis", "Material", "NNConfig", "scenes", "tiles", "evaluate", "metrics",
            "compute_camera_basis", "look_at_basis", "product_lib", "Lib", "NrbError"]
