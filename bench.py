@@ -185,7 +185,7 @@ def run_reference(a, rank):
     rays = (y1 - y0) * a.width * a.spp
     v = rays / dt / 1e6
     sample = f"rows {y0}..{y1} of {a.height} per step ({rays} paths), all host threads"
-    print(json.dumps({
+    emit(({
         "impl": "reference", "metric": "neural-render Mrays/s at 1080p", "value": v, "unit": "Mrays/s", "n_gpus": a.gpus,
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": dt * 1e3 * (a.height / (y1 - y0)), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32+f16", "data": "synthetic",
@@ -196,7 +196,21 @@ def run_reference(a, rank):
     }))
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The ONE JSON line of the contract, on the process's real stdout."""
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, (json.dumps(line) + "\n").encode())
+
+
 def main():
+    # Libraries write to fd 1 behind Python's back (NCCL prints its version banner there): everything but
+    # the result line goes to stderr, so stdout carries exactly one JSON line.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     a = parse()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -385,7 +399,7 @@ def main():
     if world == 1 and not a.no_cpu_baseline:
         v, d = cpu_sample(nrb, a, scene, a.cpu_seconds)
         line["cpu_baseline"] = {"value": v, "unit": "Mrays/s", "cores": d["cores"], "kind": d["kind"], "sample": d["sample"]}
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
