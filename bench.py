@@ -375,6 +375,16 @@ def main():
                               "achieved": neural_q * 1536 / (e_ms * 1e-3) / 1e9, "unit": "GB/s gathered",
                               "peak": smem_peak, "peak_source": "148 SMs x 128 B/clk x SM clock (conflict-free)",
                               "frac": neural_q * 1536 / (e_ms * 1e-3) / 1e9 / smem_peak}
+        b_ms = stage_ms("k_bounce_begin")
+        if b_ms:
+            # 63 node pairs (64 B) + 16 triangle blocks (48 B) fetched per path vertex on this scene
+            # (counted with the instrumented traversal), + 32 B vertex read + 88 B results: gathers served by L1/L2.
+            bpv = 63 * 64 + 16 * 48 + 32 + 88
+            gbs = counters["path_vertices"] * bpv / (b_ms * 1e-3) / 1e9
+            roof["traversal"] = {"kernel": "k_bounce_begin", "bound": "instruction issue (ncu: 70 % issue-active, 16/32 lanes, L1 hit 91 %)",
+                                 "ms_per_step": b_ms, "bytes_per_vertex": bpv, "achieved": gbs, "unit": "GB/s gathered (L1/L2-resident BVH)",
+                                 "hbm_peak": pk["hbm"], "vs_hbm_peak": gbs / pk["hbm"],
+                                 "vertices_per_step": counters["path_vertices"]}
     else:
         k, v = top
         roof = {"kernel": k, "bound": "hbm", "achieved": None, "peak": pk["hbm"], "unit": "GB/s", "frac": None, "traffic": None,

@@ -299,6 +299,17 @@ void* nrb_stream(const nrb_renderer* r);
 int nrb_build_bvh(const float* vertices, int num_vertices, uint32_t* indices, int num_triangles,
                   nrb_bvh_node* nodes, int* num_nodes, uint32_t* prim_ids);
 
+/* (new) The same contract built on the GPU in milliseconds (LBVH: Morton sort + radix tree + bottom-up
+ * fit, subtrees of <= max_leaf (default 4, <= 32) triangles folded into one leaf): for large meshes and
+ * scenes that change per frame.  Host pointers in and out like nrb_build_bvh; nodes must hold
+ * 2*num_triangles entries, the root is node 0 and unreachable entries may remain.  device < 0 = current
+ * device; build_ms (optional) receives the device time of the build kernels.  The tree differs from the
+ * reference's SAH tree: map hit ids through prim_ids when comparing with a reference build.
+ * Replaces Mesh::buildBvh (src/mesh_bvh.cpp:27-162) for callers that can trade tree quality for build time. */
+int nrb_build_bvh_gpu(const float* vertices, int num_vertices, uint32_t* indices, int num_triangles,
+                      nrb_bvh_node* nodes, int* num_nodes, uint32_t* prim_ids, int device, int max_leaf, float* build_ms);
+const char* nrb_build_bvh_gpu_error(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -162,9 +162,26 @@ def build_bvh(vertices, indices):
     return nodes[: n.value].copy(), idx, prim
 
 
-def mesh_from(vertices, indices, normals=None, texcoords=None, **kw):
+def build_bvh_gpu(vertices, indices, max_leaf: int = 4, device: int = -1):
+    """nrb_build_bvh_gpu (LBVH on the device): -> (nodes, leaf-ordered indices, prim ids, build ms)."""
+    import ctypes as C
+    from . import _capi as K
+    lib = K.product_lib()
+    v = np.ascontiguousarray(vertices, np.float32)
+    idx = np.ascontiguousarray(indices, np.uint32).copy()
+    nodes = np.zeros(2 * len(idx), K.BVH_NODE_DTYPE)
+    prim = np.zeros(len(idx), np.uint32)
+    n, ms = C.c_int(0), C.c_float(0.0)
+    rc = lib.fn("build_bvh_gpu")(v.ctypes.data, len(v), idx.ctypes.data, len(idx), nodes.ctypes.data, C.byref(n),
+                                 prim.ctypes.data, device, max_leaf, C.byref(ms))
+    if rc != 0:
+        raise K.NrbError(f"nrb_build_bvh_gpu failed ({rc}): {lib.fn('build_bvh_gpu_error')().decode()}")
+    return nodes[: n.value].copy(), idx, prim, ms.value
+
+
+def mesh_from(vertices, indices, normals=None, texcoords=None, gpu_bvh: bool = False, **kw):
     from .renderer import MeshData
-    nodes, idx, _ = build_bvh(vertices, indices)
+    nodes, idx, _ = build_bvh_gpu(vertices, indices)[:3] if gpu_bvh else build_bvh(vertices, indices)
     return MeshData(vertices=vertices, indices=idx, nodes=nodes, normals=normals, texcoords=texcoords, **kw)
 
 

@@ -284,3 +284,76 @@ def test_denoiser_matches_oracle(oracle_lib):
     prod.set_denoise(True)
     with pytest.raises(nrb.NrbError):
         prod.render(eye)
+
+
+def _check_tree(nodes, idx, prim, v, src_idx, max_leaf):
+    """Structural validity of a reference-format BVH: every triangle in exactly one reachable leaf, children inside
+    their parent's box, triangles inside their leaf's box, leaf sizes bounded, index buffer = permuted source."""
+    nt = len(idx)
+    assert np.array_equal(np.sort(prim), np.arange(nt)) and np.array_equal(idx, src_idx[prim])
+    covered = np.zeros(nt, np.int32)
+    todo, depth_max = [(0, 1)], 1
+    while todo:
+        i, depth = todo.pop()
+        n = nodes[i]
+        depth_max = max(depth_max, depth)
+        if n["is_leaf"]:
+            first, count = int(n["first"]), int(n["count"])
+            assert 1 <= count <= max_leaf
+            covered[first:first + count] += 1
+            tri = v[idx[first:first + count].reshape(-1)]
+            assert np.all(tri >= n["bounds_min"] - 0) and np.all(tri <= n["bounds_max"] + 0)
+        else:
+            for c in (int(n["left"]), int(n["right"])):
+                assert 0 < c < len(nodes)
+                assert np.all(nodes[c]["bounds_min"] >= n["bounds_min"]) and np.all(nodes[c]["bounds_max"] <= n["bounds_max"])
+                todo.append((c, depth + 1))
+    assert np.all(covered == 1)
+    return depth_max
+
+
+@pytest.mark.parametrize("sub,max_leaf", [(0, 4), (3, 1), (5, 4)])
+def test_gpu_bvh_build(sub, max_leaf):
+    """nrb_build_bvh_gpu (LBVH on the device): a valid tree in the reference's node format, and rays traced through it
+    find the same source triangle at the bit-identical t as through the host SAH build."""
+    v0, f = nrb.scenes.icosphere(sub)
+    v = nrb.scenes.displace(v0, 0.1)
+    nodes, idx, prim, ms = nrb.scenes.build_bvh_gpu(v, f, max_leaf=max_leaf)
+    depth = _check_tree(nodes, idx, prim, v, np.ascontiguousarray(f, np.uint32), max_leaf)
+    assert depth <= 64
+    h_nodes, h_idx, h_prim = nrb.scenes.build_bvh(v, f)
+    o, d = random_rays(20000, seed=31 + sub)
+    hits = []
+    for nd, ix in ((nodes, idx), (h_nodes, h_idx)):
+        scene = nrb.Scene(original_mesh=nrb.MeshData(vertices=v, indices=ix, nodes=nd))
+        r = nrb.RendererNeural(scene)
+        hits.append([r.trace_rays(nrb.SLOT_ORIGINAL, mode, o, d) for mode in (0, 1, 2)])
+        r.close()
+    for a, b in zip(*hits):
+        assert np.array_equal(a["t"], b["t"])
+        hit = b["t"] < 1e30
+        assert hit.sum() > 100
+        same = prim[a["prim"][hit]] == h_prim[b["prim"][hit]]
+        assert same.mean() > 0.999  # equal-t ties (shared edges) may resolve to the neighbouring triangle
+    print(f"LBVH build of {len(f)} triangles: {ms:.3f} ms on the device, depth {depth}, {len(nodes)} nodes")
+
+
+def test_gpu_bvh_build_large_and_degenerate():
+    v0, f = nrb.scenes.icosphere(7)
+    v = nrb.scenes.displace(v0, 0.1)
+    import time
+    t0 = time.time()
+    nodes, idx, prim, ms = nrb.scenes.build_bvh_gpu(v, f)
+    wall = time.time() - t0
+    t0 = time.time()
+    nrb.scenes.build_bvh(v, f)
+    host = time.time() - t0
+    print(f"327680 triangles: device build {ms:.2f} ms ({wall * 1e3:.0f} ms with copies) vs host SAH build {host * 1e3:.0f} ms")
+    assert ms < 50.0
+    # all triangles identical (every Morton code equal): the index half of the key keeps the tree well formed
+    tri = np.tile(np.array([[0, 1, 2]], np.uint32), (1000, 1))
+    pts = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32)
+    nodes, idx, prim, _ = nrb.scenes.build_bvh_gpu(pts, tri, max_leaf=2)
+    assert _check_tree(nodes, idx, prim, pts, tri, 2) <= 64
+    with pytest.raises(nrb.NrbError):
+        nrb.scenes.build_bvh_gpu(pts, np.array([[0, 1, 7]], np.uint32))
