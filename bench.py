@@ -48,6 +48,8 @@ def parse():
     ap.add_argument("--subdiv", type=int, default=7)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
+                    help="multi-GPU frame gather: peer-memory stores fused into finalize (default) or an NCCL reduce")
     ap.add_argument("--no-tail-graph", action="store_true", help="fixed nine-iteration segment tail (profiling aid)")
     return ap.parse_args()
 
@@ -249,11 +251,21 @@ def main():
         return torch.as_tensor(Pixels(r.device_pixels(), a.width * a.height * 4), device=torch.device("cuda", local_rank))
 
     gathered = None
+    # The one exchange step of the path: every rank owns row bands and rank 0 ends up with the whole frame.
+    # Default: fused into the frame - each rank's finalize kernel stores its bands into rank 0's frame buffer
+    # over NVLink peer memory (nrb_gather_export / nrb_gather_attach) and rank 0's render ends with the wait
+    # for their signals.  --gather nccl keeps the collective (a sum-reduce of the zero-padded frames).
+    peer_gather = world > 1 and a.gather == "peer"
+    if peer_gather:
+        box = [r.gather_export(world - 1) if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        if rank != 0:
+            r.gather_attach(box[0])
+        dist.barrier()
 
     def gather():
-        """The one exchange step: every rank owns row bands; rank 0 ends up with the whole frame."""
         nonlocal gathered
-        if world == 1:
+        if world == 1 or peer_gather:
             return
         t = frame_tensor()
         if gathered is None:
@@ -300,7 +312,7 @@ def main():
         gather()
         dst = host_frames[e2e_step[0] & 1]
         e2e_step[0] += 1
-        if world == 1:
+        if world == 1 or (peer_gather and rank == 0):
             r.read_pixels_async(dst.data_ptr(), dst.numel())
         elif rank == 0:
             dst.copy_(gathered, non_blocking=True)
@@ -395,6 +407,7 @@ def main():
         "warmup": max(3, a.warmup), "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32 geometry + f16 network (f32 accumulate)", "data": "synthetic",
         "config": {"workload": workload_name(a), "mode": a.mode, "partition": f"{band}-row bands round-robin, scene+weights replicated; spp = {a.base_spp} x n_gpus (weak scaling)",
+                   "gather": ("none (1 GPU)" if world == 1 else ("finalize stores into rank 0's frame over NVLink peer memory" if peer_gather else "NCCL sum-reduce of zero-padded frames")),
                    "l2": "per-frame wavefront state (~0.4 KB/path) exceeds L2; BVH and hash tables are L2-resident by design; "
                          "every step draws new samples (progressive accumulation)"},
         "clocks": clocks,

@@ -241,6 +241,18 @@ int nrb_read_pixels(nrb_renderer* r, void* rgba, size_t bytes);
  * the copy is joined to like nrb_render, has drained).  One transfer in flight per renderer: a
  * second call waits on the device for the first. */
 int nrb_read_pixels_async(nrb_renderer* r, void* rgba, size_t bytes);
+/* (new) Multi-GPU frame gather fused into the frame, over peer memory instead of a collective: the root
+ * rank (one process per GPU) exports its frame buffer, the others attach and from then on their finalize
+ * kernel stores the row bands they own (nrb_set_tile) directly into the root's devicePixels() over NVLink
+ * and signals; the root's nrb_render ends with a device-side wait for `peers` signals, so the work it
+ * enqueues next sees the complete frame.  The handle (NRB_GATHER_HANDLE_BYTES) travels between the
+ * processes by any means (torch.distributed broadcast, a pipe).  All ranks must render the same number of
+ * frames; a rank that stops makes the others' waits give up after ~3 s and nrb_sync report it.  A peer's
+ * own devicePixels() is no longer written.  nrb_resize drops the association on either side. */
+#define NRB_GATHER_HANDLE_BYTES 144
+int nrb_gather_export(nrb_renderer* r, int peers, void* handle, size_t handle_bytes);
+int nrb_gather_attach(nrb_renderer* r, const void* handle, size_t handle_bytes);
+int nrb_gather_detach(nrb_renderer* r);
 int nrb_width(const nrb_renderer* r);
 int nrb_height(const nrb_renderer* r);
 uint32_t nrb_accum_sample_count(const nrb_renderer* r);

@@ -142,6 +142,7 @@ class Lib:
             "trace_rays": ([vp, i, i, vp, vp, sz, vp], i), "trace_rays_host": ([vp, i, i, vp, vp, sz, vp], i),
             "neural_query": ([vp, vp, sz, vp], i), "neural_query_host": ([vp, vp, sz, vp], i),
             "input_dims": ([vp], i), "output_dims": ([vp], i), "sync": ([vp], i), "stream": ([vp], vp),
+            "gather_export": ([vp, i, vp, sz], i), "gather_attach": ([vp, vp, sz], i), "gather_detach": ([vp], i),
             "build_bvh": ([vp, i, vp, i, vp, P(i), vp], i),
             "build_bvh_gpu": ([vp, i, vp, i, vp, P(i), vp, i, i, P(C.c_float)], i), "build_bvh_gpu_error": ([], C.c_char_p), "abi_version": ([], i),
             "get_stage": ([vp, i, P(C.c_char_p), P(C.c_double), P(C.c_uint64)], i), "reset_stages": ([vp], i),

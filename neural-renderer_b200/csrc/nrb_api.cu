@@ -102,6 +102,15 @@ struct nrb_renderer {
     cudaStream_t copyStream = nullptr;
     cudaEvent_t evStaged = nullptr, evCopied = nullptr;
     bool copyPending = false;
+    // peer-memory frame gather (nrb_gather_export / nrb_gather_attach)
+    struct Gather {
+        int role = 0;                 // 0 off, 1 root (owns the gathered frame), 2 peer (stores into the root's)
+        int peers = 0;                // root: ranks that signal per frame
+        unsigned frames = 0;          // frames rendered since the gather was set up
+        DevBuf sync;                  // root: {signals, released, -, -}; every rank: [4] = local error flag
+        void* remotePixels = nullptr; // peer: the root's frame buffer and sync block, opened over CUDA IPC
+        void* remoteSync = nullptr;
+    } gather;
 
     // scene
     MeshSlot mesh[4];
@@ -158,6 +167,15 @@ struct nrb_renderer {
 };
 
 namespace {
+
+void gather_reset(nrb_renderer* r) {
+    if (r->gather.remotePixels) cudaIpcCloseMemHandle(r->gather.remotePixels);
+    if (r->gather.remoteSync) cudaIpcCloseMemHandle(r->gather.remoteSync);
+    r->gather.remotePixels = r->gather.remoteSync = nullptr;
+    r->gather.role = 0;
+    r->gather.peers = 0;
+    r->gather.frames = 0;
+}
 
 int local_rows(const nrb_renderer* r) {
     if (r->world <= 1) return r->height;
@@ -363,6 +381,8 @@ void nrb_destroy(nrb_renderer* r) {
     if (r->evStart) cudaEventDestroy(r->evStart);
     if (r->evStop) cudaEventDestroy(r->evStop);
     if (r->evJoin) cudaEventDestroy(r->evJoin);
+    if (r->gather.remotePixels) cudaIpcCloseMemHandle(r->gather.remotePixels);
+    if (r->gather.remoteSync) cudaIpcCloseMemHandle(r->gather.remoteSync);
     if (r->copyStream) { cudaStreamSynchronize(r->copyStream); cudaStreamDestroy(r->copyStream); }
     if (r->evStaged) cudaEventDestroy(r->evStaged);
     if (r->evCopied) cudaEventDestroy(r->evCopied);
@@ -503,6 +523,7 @@ int nrb_resize(nrb_renderer* r, int width, int height) {
     r->pixels.release();
     r->stateElems = r->accumPixels = r->pixelCount = 0;
     r->accumSampleCount = 0;
+    gather_reset(r);  // the exported frame buffer is gone: export / attach again
     return NRB_OK;
 }
 
@@ -585,6 +606,11 @@ int nrb_sync(nrb_renderer* r) {
     NRB_CUDA(cudaStreamSynchronize(r->stream));
     if (r->copyStream) NRB_CUDA(cudaStreamSynchronize(r->copyStream));
     r->copyPending = false;
+    if (r->gather.role != 0) {
+        unsigned err = 0;
+        NRB_CUDA(cudaMemcpy(&err, r->gather.sync.as<unsigned>() + 4, sizeof(err), cudaMemcpyDeviceToHost));
+        if (err) return fail(NRB_ERR_CUDA, "frame gather timed out: a rank stopped rendering (frames are out of step)");
+    }
     return NRB_OK;
 }
 
@@ -638,7 +664,7 @@ int ensure_state(nrb_renderer* r, size_t nElems, size_t localPixels, size_t fram
         r->pixelCount = framePixels;
     }
     r->st.accum = r->accum.as<float>();
-    r->st.pixels = r->pixels.as<uchar4>();
+    r->st.pixels = r->gather.role == 2 ? static_cast<uchar4*>(r->gather.remotePixels) : r->pixels.as<uchar4>();
     return NRB_OK;
 }
 
@@ -794,6 +820,12 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     }
     NRB_CUDA(cudaMemsetAsync(r->st.stats, 0, 16 * sizeof(unsigned long long), s));
     NRB_CUDA(cudaEventRecord(r->evStart, s));
+    if (r->gather.role == 1) {
+        // everything the caller enqueued on this stream since the last frame has read it: peers may overwrite
+        launch_gather_release(r->gather.sync.as<unsigned>(), r->gather.frames, s);
+    } else if (r->gather.role == 2) {
+        launch_gather_wait(static_cast<unsigned*>(r->gather.remoteSync) + 1, r->gather.frames, r->gather.sync.as<unsigned>() + 4, s);
+    }
     if (r->profile) {
         r->prof.marks = 0;
         NRB_CUDA(cudaEventRecord(r->prof.ev[0], s));
@@ -804,6 +836,13 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     if (neural) launches = launch_neural_frame(f, r->net, r->lambertView, s, (r->useTailGraph && getenv("NRB_DEBUG") == nullptr) ? &r->segTail : nullptr);
     else launches = launch_gt_frame(f, r->lambertView, s);
     if (r->denoise && !r->lambertView) launches += launch_denoise(f, s);
+    if (r->gather.role != 0) {
+        ++r->gather.frames;
+        if (r->gather.role == 2) launch_gather_signal(static_cast<unsigned*>(r->gather.remoteSync), s);
+        else launch_gather_wait(r->gather.sync.as<unsigned>(), r->gather.frames * static_cast<unsigned>(r->gather.peers),
+                                r->gather.sync.as<unsigned>() + 4, s);
+        launches += 2;
+    }
     set_stage_profiler(nullptr);
     r->profPending = r->profile != 0;
     NRB_CUDA(cudaEventRecord(r->evStop, s));
@@ -855,6 +894,70 @@ int nrb_read_pixels_async(nrb_renderer* r, void* rgba, size_t bytes) {
     NRB_CUDA(cudaEventRecord(r->evCopied, r->copyStream));
     NRB_CUDA(cudaStreamWaitEvent(cudaStreamLegacy, r->evCopied, 0));  // same join rule as nrb_render
     r->copyPending = true;
+    return NRB_OK;
+}
+
+// ---- frame gather over peer memory ------------------------------------------------------------------
+// One process per GPU.  The root rank exports its frame buffer and a sync block as CUDA IPC handles; the
+// other ranks open them and from then on their k_finalize stores the row bands they own straight into the
+// root's buffer over NVLink, followed by one system-scope signal.  The root's nrb_render ends with a wait
+// for the signals of all peers, so when it returns (stream-ordered) nrb_device_pixels() on the root holds
+// the whole frame: the gather is fused into the last kernel of the frame, no collective call follows.
+int nrb_gather_export(nrb_renderer* r, int peers, void* handle, size_t handle_bytes) {
+    if (!r || !handle || peers < 0) return fail(NRB_ERR_INVALID, "bad argument");
+    if (handle_bytes < NRB_GATHER_HANDLE_BYTES) return fail(NRB_ERR_SIZE, "gather handle buffer too small");
+    if (r->width <= 0 || r->height <= 0) return fail(NRB_ERR_INVALID, "nrb_resize first");
+    NRB_CUDA(cudaSetDevice(r->device));
+    NRB_CUDA(cudaStreamSynchronize(r->stream));
+    gather_reset(r);
+    const size_t framePixels = static_cast<size_t>(r->width) * r->height;
+    if (framePixels != r->pixelCount) {
+        NRB_CUDA(r->pixels.alloc(framePixels * sizeof(uchar4)));
+        NRB_CUDA(cudaMemset(r->pixels.p, 0, r->pixels.bytes));
+        r->pixelCount = framePixels;
+    }
+    NRB_CUDA(r->gather.sync.alloc(64));
+    NRB_CUDA(cudaMemset(r->gather.sync.p, 0, 64));
+    cudaIpcMemHandle_t h[2];
+    NRB_CUDA(cudaIpcGetMemHandle(&h[0], r->pixels.p));
+    NRB_CUDA(cudaIpcGetMemHandle(&h[1], r->gather.sync.p));
+    std::memcpy(handle, h, sizeof(h));
+    const uint64_t dims[2] = {static_cast<uint64_t>(r->width), static_cast<uint64_t>(r->height)};
+    std::memcpy(static_cast<char*>(handle) + sizeof(h), dims, sizeof(dims));
+    r->gather.role = 1;
+    r->gather.peers = peers;
+    return NRB_OK;
+}
+
+int nrb_gather_attach(nrb_renderer* r, const void* handle, size_t handle_bytes) {
+    if (!r || !handle) return fail(NRB_ERR_INVALID, "bad argument");
+    if (handle_bytes < NRB_GATHER_HANDLE_BYTES) return fail(NRB_ERR_SIZE, "gather handle buffer too small");
+    NRB_CUDA(cudaSetDevice(r->device));
+    NRB_CUDA(cudaStreamSynchronize(r->stream));
+    gather_reset(r);
+    cudaIpcMemHandle_t h[2];
+    uint64_t dims[2];
+    std::memcpy(h, handle, sizeof(h));
+    std::memcpy(dims, static_cast<const char*>(handle) + sizeof(h), sizeof(dims));
+    if (dims[0] != static_cast<uint64_t>(r->width) || dims[1] != static_cast<uint64_t>(r->height))
+        return fail(NRB_ERR_SIZE, "root frame size differs from this renderer's");
+    NRB_CUDA(cudaIpcOpenMemHandle(&r->gather.remotePixels, h[0], cudaIpcMemLazyEnablePeerAccess));
+    cudaError_t e = cudaIpcOpenMemHandle(&r->gather.remoteSync, h[1], cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+        gather_reset(r);
+        return fail(NRB_ERR_CUDA, std::string("cudaIpcOpenMemHandle: ") + cudaGetErrorString(e));
+    }
+    NRB_CUDA(r->gather.sync.alloc(64));
+    NRB_CUDA(cudaMemset(r->gather.sync.p, 0, 64));
+    r->gather.role = 2;
+    return NRB_OK;
+}
+
+int nrb_gather_detach(nrb_renderer* r) {
+    if (!r) return fail(NRB_ERR_INVALID, "null renderer");
+    NRB_CUDA(cudaSetDevice(r->device));
+    NRB_CUDA(cudaStreamSynchronize(r->stream));
+    gather_reset(r);
     return NRB_OK;
 }
 

@@ -242,6 +242,47 @@ int launch_finalize(const Frame& f, cudaStream_t s) {
     return 1;
 }
 
+// ---- frame gather over peer memory (multi-GPU) -----------------------------------------------------
+// With nrb_gather_attach a non-root rank's k_finalize stores its row bands straight into the root GPU's
+// frame buffer (NVLink peer stores); these three single-thread kernels are the hand-shake around it.
+// sync[0] = bands-complete signals received (monotonic), sync[1] = frames the root has released for
+// overwriting, both in the root's memory; err = local flag set when a wait gives up.
+__device__ __forceinline__ unsigned ld_sys(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__global__ void k_gather_release(unsigned* sync, unsigned frames) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sync + 1), "r"(frames) : "memory");
+}
+__global__ void k_gather_wait(const unsigned* flag, unsigned want, unsigned* err) {
+    const long long t0 = clock64();
+    while (static_cast<int>(ld_sys(flag) - want) < 0) {
+        if (clock64() - t0 > 6000000000ll) {  // ~3 s: a peer stopped rendering; give up instead of hanging the GPU
+            *err = 1u;
+            break;
+        }
+        __nanosleep(500);
+    }
+    __threadfence_system();
+}
+__global__ void k_gather_signal(unsigned* remoteSync) {
+    __threadfence_system();  // the finalize kernel before this one wrote the bands; order them before the signal
+    atomicAdd_system(remoteSync, 1u);
+}
+void launch_gather_release(unsigned* sync, unsigned frames, cudaStream_t s) {
+    k_gather_release<<<1, 1, 0, s>>>(sync, frames);
+    NRB_LAUNCHED("k_gather_release", s);
+}
+void launch_gather_wait(const unsigned* flag, unsigned want, unsigned* err, cudaStream_t s) {
+    k_gather_wait<<<1, 1, 0, s>>>(flag, want, err);
+    NRB_LAUNCHED("k_gather_wait", s);
+}
+void launch_gather_signal(unsigned* remoteSync, cudaStream_t s) {
+    k_gather_signal<<<1, 1, 0, s>>>(remoteSync);
+    NRB_LAUNCHED("k_gather_signal", s);
+}
+
 int launch_denoise(const Frame& f, cudaStream_t s) {
     const dim3 grid((f.fp.width + kDnTileW - 1) / kDnTileW, (f.fp.height + kDnTileH - 1) / kDnTileH);
     k_denoise<<<grid, dim3(kDnTileW, kDnTileH), 0, s>>>(f);

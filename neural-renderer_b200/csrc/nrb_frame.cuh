@@ -56,6 +56,10 @@ struct SegTail {
 int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStream_t s, SegTail* tail);
 int launch_finalize(const Frame& f, cudaStream_t s);
 int launch_lambert(const Frame& f, cudaStream_t s);
-int launch_denoise(const Frame& f, cudaStream_t s);  // world == 1 only: reads accum/rec[0] of the whole frame
+int launch_denoise(const Frame& f, cudaStream_t s);
+// peer-memory frame gather hand-shake (nrb_frame.cu)
+void launch_gather_release(unsigned* sync, unsigned frames, cudaStream_t s);
+void launch_gather_wait(const unsigned* flag, unsigned want, unsigned* err, cudaStream_t s);
+void launch_gather_signal(unsigned* remoteSync, cudaStream_t s);  // world == 1 only: reads accum/rec[0] of the whole frame
 
 }  // namespace nrb

@@ -323,6 +323,22 @@ class RendererNeural:
     def set_tile(self, band_rows: int, rank: int, world: int):
         self.lib.check(self.lib.fn("set_tile")(self._h, band_rows, rank, world), "set_tile")
 
+    GATHER_HANDLE_BYTES = 144
+
+    def gather_export(self, peers: int) -> bytes:
+        """Root rank: export the frame buffer for `peers` other ranks to store their row bands into (nrb_gather_export)."""
+        buf = C.create_string_buffer(self.GATHER_HANDLE_BYTES)
+        self.lib.check(self.lib.fn("gather_export")(self._h, peers, buf, self.GATHER_HANDLE_BYTES), "gather_export")
+        return buf.raw
+
+    def gather_attach(self, handle: bytes):
+        """Other ranks: from now on finalize stores this rank's bands into the root's frame over peer memory."""
+        buf = C.create_string_buffer(bytes(handle), len(handle))
+        self.lib.check(self.lib.fn("gather_attach")(self._h, buf, len(handle)), "gather_attach")
+
+    def gather_detach(self):
+        self.lib.check(self.lib.fn("gather_detach")(self._h), "gather_detach")
+
     def read_pixels(self) -> np.ndarray:
         out = np.zeros((self.height(), self.width(), 4), np.uint8)
         self.lib.check(self.lib.fn("read_pixels")(self._h, out.ctypes.data, out.nbytes), "read_pixels")

@@ -357,3 +357,58 @@ def test_gpu_bvh_build_large_and_degenerate():
     assert _check_tree(nodes, idx, prim, pts, tri, 2) <= 64
     with pytest.raises(nrb.NrbError):
         nrb.scenes.build_bvh_gpu(pts, np.array([[0, 1, 7]], np.uint32))
+
+
+@pytest.mark.parametrize("neural", [False, True], ids=["gt", "neural"])
+def test_peer_memory_gather_two_processes(neural):
+    """nrb_gather_export / nrb_gather_attach: a second PROCESS (its own renderer, here on the same GPU, as a second
+    GPU's process would be) stores the row bands it owns into the root's frame buffer through CUDA IPC peer memory;
+    after the root's render the root holds the frame a single full-frame renderer produces, bit for bit."""
+    import multiprocessing as mp
+    from tests.util import peer_rank_main
+    W, H, frames = 320, 208, 3
+    scene = nrb.scenes.make_scene("ico", 3)
+    eye, basis = nrb.scenes.default_camera()
+
+    def renderer():
+        r = nrb.RendererNeural(scene)
+        r.resize(W, H)
+        r.set_camera_basis(basis)
+        r.set_bounce_count(2)
+        if neural:
+            r.load_weights(nrb.scenes.make_weights())
+            r.set_use_neural_query(True)
+        return r
+
+    full = renderer()
+    for _ in range(frames):
+        full.render(eye)
+    want = full.read_pixels()
+    root = renderer()
+    root.set_tile(16, 0, 2)
+    ctx = mp.get_context("spawn")
+    here, there = ctx.Pipe()
+    p = ctx.Process(target=peer_rank_main, args=(there, 1, 2, W, H, frames, neural))
+    p.start()
+    try:
+        here.send(root.gather_export(1))
+        assert here.poll(120) and here.recv() == "attached"
+        for _ in range(frames):
+            root.render(eye)
+        root.sync()
+        got = root.read_pixels()
+        assert here.poll(120) and here.recv() == "done"
+        here.send("bye")
+    finally:
+        p.join(60)
+        if p.is_alive():
+            p.kill()
+    assert np.array_equal(got, want)
+    # a root whose peer never renders gives up instead of hanging the GPU, and says so
+    root.gather_export(1)
+    root.render(eye)
+    with pytest.raises(nrb.NrbError):
+        root.sync()
+    root.gather_detach()
+    root.render(eye)
+    root.sync()

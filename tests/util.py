@@ -48,3 +48,28 @@ def random_rays(n, seed, radius=3.0):
     d = tgt - o
     d /= np.linalg.norm(d, axis=1, keepdims=True)
     return o.astype(np.float32), d.astype(np.float32)
+
+
+def peer_rank_main(conn, rank, world, width, height, frames, neural):
+    """Body of a non-root rank of the peer-memory gather test: its own process, its own renderer."""
+    try:
+        scene = nrb.scenes.make_scene("ico", 3)
+        eye, basis = nrb.scenes.default_camera()
+        r = nrb.RendererNeural(scene)
+        r.resize(width, height)
+        r.set_camera_basis(basis)
+        r.set_bounce_count(2)
+        if neural:
+            r.load_weights(nrb.scenes.make_weights())
+            r.set_use_neural_query(True)
+        r.set_tile(16, rank, world)
+        r.gather_attach(conn.recv())
+        conn.send("attached")
+        for _ in range(frames):
+            r.render(eye)
+        r.sync()
+        conn.send("done")
+        conn.recv()  # keep the mapping alive until the root has read the frame
+        r.close()
+    except Exception as e:  # pragma: no cover
+        conn.send(f"error: {e!r}")
