@@ -257,11 +257,28 @@ def main():
     # for their signals.  --gather nccl keeps the collective (a sum-reduce of the zero-padded frames).
     peer_gather = world > 1 and a.gather == "peer"
     if peer_gather:
-        box = [r.gather_export(world - 1) if rank == 0 else None]
+        ok = 1
+        box = [None]
+        try:
+            if rank == 0:
+                box[0] = r.gather_export(world - 1)
+        except Exception as e:  # noqa: BLE001
+            print(f"[bench] peer gather unavailable on rank 0: {e}", file=sys.stderr)
+            ok = 0
         dist.broadcast_object_list(box, src=0)
         if rank != 0:
-            r.gather_attach(box[0])
-        dist.barrier()
+            try:
+                if box[0] is None:
+                    raise RuntimeError("no handle from rank 0")
+                r.gather_attach(box[0])
+            except Exception as e:  # noqa: BLE001
+                print(f"[bench] peer gather unavailable on rank {rank}: {e}", file=sys.stderr)
+                ok = 0
+        flag = torch.tensor([ok], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0:  # every rank agrees to fall back to the collective
+            r.gather_detach()
+            peer_gather = False
 
     def gather():
         nonlocal gathered
