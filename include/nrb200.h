@@ -132,7 +132,9 @@ typedef enum nrb_trace_mode {
     NRB_TRACE_ANY = 0,
     NRB_TRACE_FORWARD_ONLY = 1,
     NRB_TRACE_BACKWARD_ONLY = 2,
-    NRB_TRACE_ALL_MODES = 3   /* (new, parity hook) one fused pass: out.t/u/v = ANY/FORWARD/BACKWARD distances */
+    NRB_TRACE_ALL_MODES = 3,  /* (new, parity hook) one fused pass: out.t/u/v = ANY/FORWARD/BACKWARD distances */
+    NRB_TRACE_ALL_MODES_UNION = 4 /* (new, parity hook) the same through the bounce entry's resumable engine,
+                                     which prunes by the union of the live modes */
 } nrb_trace_mode;
 
 /* = PreliminaryHitInfo, reference src/hit_info.h:7-13.  t == 1e30f means no hit. */

@@ -43,11 +43,12 @@ __global__ void __launch_bounds__(kQueueThreads) k_gt_bounce(const __grid_consta
                                                              int qout) {
     const FrameParams& fp = f.fp;
     const int n = f.st.counts[qin];
-    const int nWarpRounded = (n + 31) & ~31;
     const SurfRec& cur = f.st.rec[bounce == 1 ? 0 : 1];
     const SurfRec& nxt = f.st.rec[1];
     unsigned int nTrace = 0, nVert = 0;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nWarpRounded; i += gridDim.x * blockDim.x) {
+    const int first = queue_start(n);
+    for (int base = 0; base < n; base += gridDim.x * blockDim.x) {  // the same trip count for every thread
+        const int i = base + first;
         bool alive = false;
         int e = 0;
         if (i < n) {
@@ -197,6 +198,16 @@ __global__ void __launch_bounds__(128) k_trace_rays(const __grid_constant__ Mesh
         if (mode == 3) {  // parity hook for the fused three-mode pass: t = ANY, u = FORWARD, v = BACKWARD distances
             trace_multi(target_of(m), 7, ld3(o, i), ld3(d, i), h.t, h.u, h.v);
             h.prim = 0u;
+        } else if (mode == 4) {  // the same through the resumable engine of the bounce entry (union pruning)
+            MultiTrace tr;
+            tr.begin(target_of(m), 7, ld3(o, i), ld3(d, i));
+            while (!tr.done()) {
+                const int k = tr.kind();
+                if (k == 0) tr.step_node();
+                else if (k == 1) tr.step_tri();
+                else tr.step_pop();
+            }
+            h = Hit{tr.best0, tr.best1, tr.best2, 0u};
         } else {
             h = trace_mode<true>(m, mode, ld3(o, i), ld3(d, i), &st);
             if (h.t >= 1e30f) h = Hit{1e30f, 0.0f, 0.0f, 0u};

@@ -42,6 +42,18 @@ __device__ __forceinline__ ElemId queue_elem(const FrameParams& fp, int e) {
     return id;
 }
 
+// First queue position of this thread in a grid-sized-stride loop.  Long queues: consecutive positions go to
+// consecutive lanes (neighbouring pixels share a warp).  A queue with fewer than four elements per warp - the
+// later bounces, the later segment iterations: a few thousand survivors - is spread one element per warp and
+// lane row (lane L of warp w starts at L * warps + w): such launches are latency-bound, and a warp that traces
+// r rays in lock step takes, phase by phase, as long as its slowest lane, so r should be as small as possible.
+__device__ __forceinline__ int queue_start(int n) {
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const int warps = (gridDim.x * blockDim.x) >> 5;
+    if (n > 4 * warps) return tid;
+    return (threadIdx.x & 31) * warps + (tid >> 5);
+}
+
 __device__ __forceinline__ void stat_flush(unsigned long long* slot, unsigned int v) {
     // all threads of the block reach this point
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

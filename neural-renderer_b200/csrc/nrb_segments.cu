@@ -64,7 +64,7 @@ __device__ __forceinline__ void seg_exits_body(const Frame& f, int qin) {
     const FrameParams& fp = f.fp;
     const int n = f.st.counts[qin];
     const int D = fp.inputDims;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    for (int i = queue_start(n); i < n; i += gridDim.x * blockDim.x) {
         const int e = f.st.queue[qin][i];
         const V3 entry = f4v(f.st.segE[e]), dir = f4v(f.st.segD[e]);
         const V3 shifted = entry + dir * kSegEps;
@@ -105,10 +105,11 @@ __global__ void __launch_bounds__(kQueueThreads) k_seg_exits(const __grid_consta
 __device__ __forceinline__ void seg_apply_body(const Frame& f, int qin, int qout, int recIdx) {
     const FrameParams& fp = f.fp;
     const int n = f.st.counts[qin];
-    const int nWarpRounded = (n + 31) & ~31;
     const SurfRec& rec = f.st.rec[recIdx];
     unsigned int nTrace = 0;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nWarpRounded; i += gridDim.x * blockDim.x) {
+    const int first = queue_start(n);
+    for (int base = 0; base < n; base += gridDim.x * blockDim.x) {  // the same trip count for every thread
+        const int i = base + first;
         bool again = false;
         int e = 0;
         if (i < n) {
@@ -250,7 +251,7 @@ __global__ void __launch_bounds__(kQueueThreads) k_bounce_sample(const __grid_co
     const FrameParams& fp = f.fp;
     const int n = f.st.counts[qin];
     const SurfRec& cur = f.st.rec[bounce == 1 ? 0 : 1];
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    for (int i = queue_start(n); i < n; i += gridDim.x * blockDim.x) {
         const int e = f.st.queue[qin][i];
         const ElemId id = queue_elem(fp, e);
         const float4 P = cur.P[e], N = cur.N[e], C = cur.C[e];
@@ -282,6 +283,8 @@ __global__ void __launch_bounds__(kQueueThreads) k_bounce_begin(const __grid_con
     MultiTrace tr;
     tr.ref = kTraceDone;
     bool more = true;  // warp-uniform: the cursor has not run past the queue
+    const int warpsTotal = gridDim.x * (kQueueThreads / 32);
+    const int cap = max(1, min(32, (n + warpsTotal - 1) / warpsTotal));  // lanes a warp keeps busy
 
     for (;;) {
         // ================= transition phase (convergent) =================
@@ -335,16 +338,21 @@ __global__ void __launch_bounds__(kQueueThreads) k_bounce_begin(const __grid_con
             queue_push(f.st.queue[qray], f.st.counts + qray, finish && alive, e);
             queue_push(f.st.queue[2], f.st.counts + 2, enters, e);
 
-            // idle lanes fetch the next vertex
+            // idle lanes fetch the next vertices, up to `cap` busy lanes per warp.  A launch with fewer vertices
+            // than lanes (later bounces: a few thousand survivors) is latency-bound: a warp that holds r rays needs
+            // about twice the steps of its longest ray in vote iterations whatever r is, so the vertices are spread
+            // one per warp instead of 32 to the first warps (measured: 131 -> 4x us for 3.3 K vertices).
             const unsigned idle = __ballot_sync(full, stage == 0);
-            if (more && idle) {
+            const int take = more ? min(__popc(idle), cap - (32 - __popc(idle))) : 0;
+            if (take > 0) {
                 int base = 0;
                 const int leader = __ffs(idle) - 1;
-                if (lane == leader) base = atomicAdd(cursor, __popc(idle));
+                if (lane == leader) base = atomicAdd(cursor, take);
                 base = __shfl_sync(full, base, leader);
-                more = base + __popc(idle) < n;
-                const int i = base + __popc(idle & ((1u << lane) - 1));
-                if (stage == 0 && i < n) {
+                more = base + take < n;
+                const int rank = __popc(idle & ((1u << lane) - 1));
+                const int i = base + rank;
+                if (stage == 0 && rank < take && i < n) {
                     e = f.st.queue[qin][i];
                     const float4 O = f.st.rayO[e], D = f.st.rayD[e];  // written by k_bounce_sample
                     org = f4v(O);
@@ -358,8 +366,9 @@ __global__ void __launch_bounds__(kQueueThreads) k_bounce_begin(const __grid_con
                     }
                 }
             }
-            // again while a lane still has a finished trace to act on, or is idle with work left
-            const bool pending = (stage != 0 && tr.done()) || (stage == 0 && more);
+            // again while a lane still has a finished trace to act on, or the warp is below its share with work left
+            const unsigned busyB = __ballot_sync(full, stage != 0);
+            const bool pending = (stage != 0 && tr.done()) || (more && take > 0 && __popc(busyB) < cap && busyB != full);
             if (!__any_sync(full, pending)) break;
         }
         if (!__any_sync(full, stage != 0)) break;  // nothing in flight and nothing left to fetch
@@ -372,7 +381,7 @@ __global__ void __launch_bounds__(kQueueThreads) k_bounce_begin(const __grid_con
             const int k = tr.kind();
             const unsigned bN = __ballot_sync(full, k == 0), bT = __ballot_sync(full, k == 1), bP = __ballot_sync(full, k == 2);
             const int busy = __popc(bN | bT | bP);
-            if (busy == 0 || (more && busy < kRefillBelow)) break;
+            if (busy == 0 || (more && busy < min(kRefillBelow, cap))) break;
             const int nN = __popc(bN), nT = __popc(bT), nP = __popc(bP);
             if (nP >= 8 || (nP >= nN && nP >= nT)) {
                 if (k == 2) tr.step_pop();
@@ -391,11 +400,12 @@ __global__ void __launch_bounds__(kQueueThreads) k_bounce_finish(const __grid_co
                                                                  int qout) {
     const FrameParams& fp = f.fp;
     const int n = f.st.counts[qray];
-    const int nWarpRounded = (n + 31) & ~31;
     const SurfRec& rec = f.st.rec[1];
     unsigned int nTrace = 0;
     const bool useAdd = f.additionalEnabled && f.mesh[NRB_SLOT_ADDITIONAL].numTriangles > 0;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nWarpRounded; i += gridDim.x * blockDim.x) {
+    const int first = queue_start(n);
+    for (int base = 0; base < n; base += gridDim.x * blockDim.x) {  // the same trip count for every thread
+        const int i = base + first;
         bool alive = false;
         int e = 0;
         if (i < n) {

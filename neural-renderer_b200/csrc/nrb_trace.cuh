@@ -335,32 +335,38 @@ __device__ __noinline__ static void trace_multi(TraceTarget m, int want, V3 o, V
     tBwd = best2;
 }
 
-// The same fused traversal as a resumable per-lane engine: the warp-level scheduler of a persistent
-// kernel (k_bounce_begin) runs `round()` for the lanes that hold a live trace and refills finished
-// lanes with new work instead of letting them idle until the warp's longest ray ends.
+// The fused traversal as a resumable per-lane engine: the warp-level scheduler of a persistent kernel
+// (k_bounce_begin) steps the lanes that hold a live trace and refills finished lanes with new work instead
+// of letting them idle until the warp's longest ray ends.
+//
+// Pruning here is by the UNION of the live modes: a box is entered while its entry distance is not beyond
+// `limit` = the largest best-t among the wanted modes (1e30 while one of them has no hit yet).  trace_multi
+// above tracks, per node, exactly which modes' own traversals would enter it (three compares per box, a
+// mode set per stack entry); the union visits a superset of those nodes, and a mode m can gain a hit from
+// the extra ones only through a triangle whose computed t is below best_m although its leaf box was entered
+// beyond best_m - mathematically impossible (a hit inside a box is not nearer than the box), possible in
+// fp32 only when t, best_m and the box distance agree to the last bits.  Entry distances are monotone down
+// the tree (nested boxes, monotone fp32 slab arithmetic), so nothing else differs.  The parity hook
+// NRB_TRACE_ALL_MODES_UNION runs this engine against three separate reference traversals.
 struct MultiTrace {
     const NodePair* nodes;
     const TriBlock* tris;
     V3 o, d, inv;
-    float best0, best1, best2;
-    int ref, sp, mask, cur;  // cur: next triangle of the current leaf, -1 = leaf not started
+    float best0, best1, best2, limit;
+    int ref, sp, want, cur;  // cur: next triangle of the current leaf, -1 = leaf not started
     int2 stack[kTraceStack];
-    unsigned char smask[kTraceStack];
 
     __device__ __forceinline__ bool done() const { return ref == kTraceDone; }
-    __device__ __forceinline__ int live(int set, float tNear) const {
-        int out = 0;
-        if ((set & 1) && !(tNear > best0)) out |= 1;
-        if ((set & 2) && !(tNear > best1)) out |= 2;
-        if ((set & 4) && !(tNear > best2)) out |= 4;
-        return out;
+    __device__ __forceinline__ void relimit() {
+        limit = fmaxf(fmaxf((want & 1) ? best0 : -1e30f, (want & 2) ? best1 : -1e30f), (want & 4) ? best2 : -1e30f);
     }
-    __device__ __forceinline__ void begin(const TraceTarget& m, int want, V3 org, V3 dir) {
+    __device__ __forceinline__ void begin(const TraceTarget& m, int wanted, V3 org, V3 dir) {
         best0 = best1 = best2 = 1e30f;
+        limit = 1e30f;
         ref = kTraceDone;
         sp = 0;
         cur = -1;
-        if (m.numTriangles <= 0 || want == 0) return;
+        if (m.numTriangles <= 0 || wanted == 0) return;
         o = org;
         d = dir;
         inv = v3(1.0f / dir.x, 1.0f / dir.y, 1.0f / dir.z);
@@ -368,17 +374,8 @@ struct MultiTrace {
         if (!slab_base(o, inv, m.bmin.x, m.bmin.y, m.bmin.z, m.bmax.x, m.bmax.y, m.bmax.z, tn) || tn > 1e30f) return;
         nodes = m.nodes;
         tris = m.tris;
-        mask = want;
+        want = wanted;
         ref = m.rootRef;
-    }
-    __device__ __forceinline__ int pop() {
-        int next = kTraceDone;
-        while (sp > 0) {
-            --sp;
-            const int again = live(smask[sp], __int_as_float(stack[sp].y));
-            if (again) { next = stack[sp].x; mask = again; break; }
-        }
-        return next;
     }
     // Units of work for a warp-level scheduler that votes on what to run next: a node-pair step, one
     // triangle of the current leaf, or one stack entry of a pop.  kind(): 0 node, 1 triangle, 2 pop,
@@ -388,23 +385,16 @@ struct MultiTrace {
         const float4 a = __ldg(&nodes[ref].a), b = __ldg(&nodes[ref].b), c = __ldg(&nodes[ref].c);
         const int4 k = __ldg(&nodes[ref].d);
         float ln, rn;
-        const bool bl = slab_base(o, inv, a.x, a.y, a.z, a.w, b.x, b.y, ln);
-        const bool br = slab_base(o, inv, b.z, b.w, c.x, c.y, c.z, c.w, rn);
-        const int ml = bl ? live(mask, ln) : 0, mr = br ? live(mask, rn) : 0;
-        if (ml && mr) {
+        const bool hl = slab_base(o, inv, a.x, a.y, a.z, a.w, b.x, b.y, ln) && !(ln > limit);
+        const bool hr = slab_base(o, inv, b.z, b.w, c.x, c.y, c.z, c.w, rn) && !(rn > limit);
+        if (hl && hr) {
             const bool rightFirst = rn < ln;
-            if (sp < kTraceStack) {
-                stack[sp] = make_int2(rightFirst ? k.x : k.y, __float_as_int(rightFirst ? ln : rn));
-                smask[sp++] = static_cast<unsigned char>(rightFirst ? ml : mr);
-            }
+            if (sp < kTraceStack) stack[sp++] = make_int2(rightFirst ? k.x : k.y, __float_as_int(rightFirst ? ln : rn));
             ref = rightFirst ? k.y : k.x;
-            mask = rightFirst ? mr : ml;
-        } else if (ml) {
+        } else if (hl) {
             ref = k.x;
-            mask = ml;
-        } else if (mr) {
+        } else if (hr) {
             ref = k.y;
-            mask = mr;
         } else {
             ref = kTracePop;
         }
@@ -417,9 +407,9 @@ struct MultiTrace {
         const int i = cur < 0 ? first : cur;
         const float4 p = __ldg(&tris[i].p), q = __ldg(&tris[i].q), r = __ldg(&tris[i].r);
         const float facing = dot(v3(p.w, q.w, r.w), d);
-        int acc = mask & 1;
-        if ((mask & 2) && !(facing >= 0.0f)) acc |= 2;
-        if ((mask & 4) && !(facing <= 0.0f)) acc |= 4;
+        int acc = want & 1;
+        if ((want & 2) && !(facing >= 0.0f)) acc |= 2;
+        if ((want & 4) && !(facing <= 0.0f)) acc |= 4;
         const V3 e1 = v3(q.x, q.y, q.z), e2 = v3(r.x, r.y, r.z);
         const V3 pv = cross(d, e2);
         const float det = dot(e1, pv);
@@ -437,6 +427,7 @@ struct MultiTrace {
             if ((acc & 1) && t < best0) best0 = t;
             if ((acc & 2) && t < best1) best1 = t;
             if ((acc & 4) && t < best2) best2 = t;
+            relimit();
         }
         cur = i + 1;
         if (cur >= end) ref = kTracePop;
@@ -446,10 +437,8 @@ struct MultiTrace {
             ref = kTraceDone;
         } else {
             --sp;
-            const int again = live(smask[sp], __int_as_float(stack[sp].y));
-            if (again) {
+            if (!(__int_as_float(stack[sp].y) > limit)) {
                 ref = stack[sp].x;
-                mask = again;
                 cur = -1;
             }
         }

@@ -221,9 +221,14 @@ def test_fused_three_mode_traversal_is_exact(oracle_lib):
     o[:10000] *= 0.3  # many origins inside the shells
     for slot in (nrb.SLOT_OUTER, nrb.SLOT_INNER, nrb.SLOT_ORIGINAL):
         fused = prod.trace_rays(slot, 3, o, d)
+        union = prod.trace_rays(slot, 4, o, d)  # the resumable engine of k_bounce_begin (prunes by the union of modes)
         for mode, key in ((nrb.TRACE_ANY, "t"), (nrb.TRACE_FORWARD_ONLY, "u"), (nrb.TRACE_BACKWARD_ONLY, "v")):
             ref = orc.trace_rays(slot, mode, o, d)
             assert np.array_equal(fused[key], ref["t"]), (slot, mode)
+            # equal except where t, the best t and a box distance agree to the last bits (see nrb_trace.cuh)
+            same = union[key] == ref["t"]
+            assert same.mean() >= 1.0 - 1e-4, (slot, mode, same.mean())
+            assert np.allclose(union[key], ref["t"], rtol=1e-5, atol=0)
 
 
 def test_async_read_back_is_the_frame():
