@@ -60,11 +60,27 @@ __global__ void __launch_bounds__(kTileThreads) k_entry_camera(const __grid_cons
 }
 
 // One iteration, first half: exits + network inputs for every ray in the segment queue.
-__device__ __forceinline__ void seg_exits_body(const Frame& f, int qin) {
+// `dynamic`: warps take 32 consecutive queue positions at a time from the cursor at counts[9] (reset by the
+// host with the bounce cursor) instead of a fixed stride: the per-warp cost of 32 rays varies, and with the
+// static partition the launch ended on its slowest warps at 36 % resident warps (profiles/r1_final).
+__device__ __forceinline__ void seg_exits_body(const Frame& f, int qin, bool dynamic = false) {
     const FrameParams& fp = f.fp;
     const int n = f.st.counts[qin];
     const int D = fp.inputDims;
-    for (int i = queue_start(n); i < n; i += gridDim.x * blockDim.x) {
+    const int total = gridDim.x * blockDim.x;
+    dynamic = dynamic && n > (total >> 5) * 4;  // short queues: one ray per warp (queue_start)
+    int* cursor = f.st.counts + 9;
+    int chunk = 0;
+    for (int i = dynamic ? n : queue_start(n);; i += total) {
+        if (dynamic) {
+            if ((threadIdx.x & 31) == 0) chunk = atomicAdd(cursor, 32);
+            chunk = __shfl_sync(0xffffffffu, chunk, 0);
+            if (chunk >= n) break;
+            i = chunk + (threadIdx.x & 31);
+            if (i >= n) continue;
+        } else if (i >= n) {
+            break;
+        }
         const int e = f.st.queue[qin][i];
         const V3 entry = f4v(f.st.segE[e]), dir = f4v(f.st.segD[e]);
         const V3 shifted = entry + dir * kSegEps;
@@ -98,7 +114,9 @@ __device__ __forceinline__ void seg_exits_body(const Frame& f, int qin) {
         atomicAdd(f.st.stats + 1, static_cast<unsigned long long>(n));
     }
 }
-__global__ void __launch_bounds__(kQueueThreads) k_seg_exits(const __grid_constant__ Frame f, int qin) { seg_exits_body(f, qin); }
+__global__ void __launch_bounds__(kQueueThreads) k_seg_exits(const __grid_constant__ Frame f, int qin, int dynamic) {
+    seg_exits_body(f, qin, dynamic != 0);
+}
 
 // One iteration, second half: decode the network output, record hits, re-enter the shell for the
 // rays that go on, and compact them into the next queue.
@@ -443,7 +461,7 @@ __global__ void __launch_bounds__(kQueueThreads) k_bounce_finish(const __grid_co
 static int seg_iteration(const Frame& f, const NetDev& net, int recIdx, int qin, int grid, cudaStream_t s) {
     const int qout = qin == 2 ? 3 : 2;
     cudaMemsetAsync(f.st.counts + qout, 0, sizeof(int), s);
-    k_seg_exits<<<grid, kQueueThreads, 0, s>>>(f, qin);
+    k_seg_exits<<<grid, kQueueThreads, 0, s>>>(f, qin, qin == 2 && grid > 148 ? 1 : 0);  // iteration 0 of a pass
     NRB_LAUNCHED("k_seg_exits", s);
     int launches = 1 + launch_neural_query(net, f.st.netIn, static_cast<size_t>(f.fp.nElems), f.st.counts + qin, f.st.netOut, s);
     k_seg_apply<<<grid, kQueueThreads, 0, s>>>(f, qin, qout, recIdx);
@@ -592,7 +610,7 @@ int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStr
     for (int b = 1; b <= fp.maxBounces; ++b) {
         // path queue 0 -> ray queue 1 (+ segment queue 2) -> path queue 0
         cudaMemsetAsync(f.st.counts + 1, 0, 3 * sizeof(int), s);
-        cudaMemsetAsync(f.st.counts + 8, 0, sizeof(int), s);  // k_bounce_begin's work cursor
+        cudaMemsetAsync(f.st.counts + 8, 0, 2 * sizeof(int), s);  // work cursors of k_bounce_begin and k_seg_exits
         k_bounce_sample<<<grid, kQueueThreads, 0, s>>>(f, b, 0);
         NRB_LAUNCHED("k_bounce_sample", s);
         k_bounce_begin<<<grid, kQueueThreads, 0, s>>>(f, b, 0, 1);
