@@ -204,8 +204,9 @@ typedef enum nrb_option {
     NRB_OPT_USE_HARDWARE_RT = 9,      /* setUseHardwareRT: accepted, ignored (no OptiX path) */
     NRB_OPT_PROFILE = 10,             /* (new) record a CUDA event after every kernel launch: nrb_get_stage */
     NRB_OPT_QUERY_KERNEL = 11,        /* (new, process-wide) neural query kernel: 0 auto, 1 mma.sync, 2 fused tcgen05, 3 split */
-    NRB_OPT_TAIL_GRAPH = 12,          /* (new) 1 (default): segment-loop iterations 1..9 run as a device-driven CUDA
-                                         conditional WHILE graph; 0: nine fixed launches per pass */
+    NRB_OPT_TAIL_GRAPH = 12,          /* (new) segment-loop iterations 1..9 of a pass: 2 (default) one fused kernel in which
+                                         a warp carries 16 of the few continuing rays through exits -> network -> apply;
+                                         1 a device-driven CUDA conditional WHILE graph; 0 nine fixed launches */
     NRB_OPT_DENOISE = 13              /* (new) 1: the frame written to devicePixels() is the joint bilateral filter of
                                          the accumulation (bilateralDenoiseKernel, src/denoiser.cuh:47-113, which the
                                          reference ships but never launches), guided by the sample-0 primary-hit

@@ -124,7 +124,7 @@ struct nrb_renderer {
     NetDev net{};
     DevBuf grid, mlp, packedW, xt;
     SegTail segTail;
-    bool useTailGraph = true;
+    int tailMode = 2;  // NRB_OPT_TAIL_GRAPH: 0 fixed loop, 1 conditional WHILE graph, 2 fused tail kernel
     bool denoise = false;
     size_t gridParams = 0, mlpParams = 0;
     bool weightsLoaded = false;
@@ -550,7 +550,7 @@ int nrb_set_option(nrb_renderer* r, int option, int value) {
         case NRB_OPT_CAPTURE: r->capture = value; break;
         case NRB_OPT_PROFILE: r->profile = value; break;
         case NRB_OPT_QUERY_KERNEL: set_query_kernel(value); break;
-        case NRB_OPT_TAIL_GRAPH: r->useTailGraph = value != 0; break;
+        case NRB_OPT_TAIL_GRAPH: r->tailMode = value < 0 ? 0 : (value > 2 ? 2 : value); break;
         case NRB_OPT_DENOISE: r->denoise = value != 0; break;
         case NRB_OPT_USE_HARDWARE_RT: break;  // accepted, ignored: there is no OptiX path
         default: return fail(NRB_ERR_INVALID, "unknown option");
@@ -571,7 +571,7 @@ int nrb_get_option(const nrb_renderer* r, int option) {
         case NRB_OPT_CAPTURE: return r->capture;
         case NRB_OPT_PROFILE: return r->profile;
         case NRB_OPT_QUERY_KERNEL: return query_kernel();
-        case NRB_OPT_TAIL_GRAPH: return r->useTailGraph ? 1 : 0;
+        case NRB_OPT_TAIL_GRAPH: return r->tailMode;
         case NRB_OPT_DENOISE: return r->denoise ? 1 : 0;
         default: return 0;
     }
@@ -833,7 +833,7 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     }
     const bool neural = r->useNeuralQuery && r->weightsLoaded && outer.view.numTriangles > 0;  // (:2258-2260)
     int launches;
-    if (neural) launches = launch_neural_frame(f, r->net, r->lambertView, s, (r->useTailGraph && getenv("NRB_DEBUG") == nullptr) ? &r->segTail : nullptr);
+    if (neural) launches = launch_neural_frame(f, r->net, r->lambertView, s, (r->tailMode == 1 && getenv("NRB_DEBUG") == nullptr) ? &r->segTail : nullptr, r->tailMode == 2);
     else launches = launch_gt_frame(f, r->lambertView, s);
     if (r->denoise && !r->lambertView) launches += launch_denoise(f, s);
     if (r->gather.role != 0) {

@@ -21,6 +21,7 @@
 
 #include "nrb_frame_dev.cuh"
 #include "nrb_neural.cuh"
+#include "nrb_query_warp.cuh"
 
 namespace nrb {
 
@@ -60,6 +61,38 @@ __global__ void __launch_bounds__(kTileThreads) k_entry_camera(const __grid_cons
 }
 
 // One iteration, first half: exits + network inputs for every ray in the segment queue.
+// traceSegmentExitsKernel + buildSegmentNeuralInputsKernel for one ray: exits into segX / segI, the D network
+// inputs into dst.
+__device__ __forceinline__ void seg_exit_one(const Frame& f, int e, float* dst) {
+    const FrameParams& fp = f.fp;
+    const int D = fp.inputDims;
+    const V3 entry = f4v(f.st.segE[e]), dir = f4v(f.st.segD[e]);
+    const V3 shifted = entry + dir * kSegEps;
+    const Hit ho = trace_dyn(target_of(f.mesh[NRB_SLOT_OUTER]), TRACE_BACKWARD, shifted, dir);
+    const float exitT = ho.t < 1e30f ? ho.t : kSegEps;
+    const Hit hi = trace_dyn(target_of(f.mesh[NRB_SLOT_INNER]), TRACE_ANY, shifted, dir);
+    const bool hitInner = hi.t < 1e30f;
+    const float innerT = hitInner ? hi.t : 1e30f;
+    const bool innerFirst = hitInner && (innerT < exitT);
+    const V3 exitPos = innerFirst ? shifted + dir * innerT : shifted + dir * exitT;
+    f.st.segX[e] = make_float4(exitPos.x, exitPos.y, exitPos.z, exitT);
+    f.st.segI[e] = make_float2(innerT, __int_as_float(hitInner ? 1 : 0));
+    const V3 a = shell_norm(fp, shifted), b = shell_norm(fp, exitPos);
+    dst[0] = a.x; dst[1] = a.y; dst[2] = a.z;
+    dst[3] = b.x; dst[4] = b.y; dst[5] = b.z;
+    int o = 6;
+    if (fp.nPoints == 3) {
+        const V3 c = shell_norm(fp, (shifted + exitPos) * 0.5f);
+        dst[6] = c.x; dst[7] = c.y; dst[8] = c.z;
+        o = 9;
+    }
+    if (D >= o + 3) {
+        dst[o] = (dir.x + 1.0f) * 0.5f;
+        dst[o + 1] = (dir.y + 1.0f) * 0.5f;
+        dst[o + 2] = (dir.z + 1.0f) * 0.5f;
+    }
+}
+
 // `dynamic`: warps take 32 consecutive queue positions at a time from the cursor at counts[9] (reset by the
 // host with the bounce cursor) instead of a fixed stride: the per-warp cost of 32 rays varies, and with the
 // static partition the launch ended on its slowest warps at 36 % resident warps (profiles/r1_final).
@@ -81,33 +114,7 @@ __device__ __forceinline__ void seg_exits_body(const Frame& f, int qin, bool dyn
         } else if (i >= n) {
             break;
         }
-        const int e = f.st.queue[qin][i];
-        const V3 entry = f4v(f.st.segE[e]), dir = f4v(f.st.segD[e]);
-        const V3 shifted = entry + dir * kSegEps;
-        const Hit ho = trace_dyn(target_of(f.mesh[NRB_SLOT_OUTER]), TRACE_BACKWARD, shifted, dir);
-        const float exitT = ho.t < 1e30f ? ho.t : kSegEps;
-        const Hit hi = trace_dyn(target_of(f.mesh[NRB_SLOT_INNER]), TRACE_ANY, shifted, dir);
-        const bool hitInner = hi.t < 1e30f;
-        const float innerT = hitInner ? hi.t : 1e30f;
-        const bool innerFirst = hitInner && (innerT < exitT);
-        const V3 exitPos = innerFirst ? shifted + dir * innerT : shifted + dir * exitT;
-        f.st.segX[e] = make_float4(exitPos.x, exitPos.y, exitPos.z, exitT);
-        f.st.segI[e] = make_float2(innerT, __int_as_float(hitInner ? 1 : 0));
-        float* dst = f.st.netIn + static_cast<size_t>(i) * D;
-        const V3 a = shell_norm(fp, shifted), b = shell_norm(fp, exitPos);
-        dst[0] = a.x; dst[1] = a.y; dst[2] = a.z;
-        dst[3] = b.x; dst[4] = b.y; dst[5] = b.z;
-        int o = 6;
-        if (fp.nPoints == 3) {
-            const V3 c = shell_norm(fp, (shifted + exitPos) * 0.5f);
-            dst[6] = c.x; dst[7] = c.y; dst[8] = c.z;
-            o = 9;
-        }
-        if (D >= o + 3) {
-            dst[o] = (dir.x + 1.0f) * 0.5f;
-            dst[o + 1] = (dir.y + 1.0f) * 0.5f;
-            dst[o + 2] = (dir.z + 1.0f) * 0.5f;
-        }
+        seg_exit_one(f, f.st.queue[qin][i], f.st.netIn + static_cast<size_t>(i) * D);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         atomicAdd(f.st.stats + 0, 2ull * static_cast<unsigned long long>(n));
@@ -116,6 +123,48 @@ __device__ __forceinline__ void seg_exits_body(const Frame& f, int qin, bool dyn
 }
 __global__ void __launch_bounds__(kQueueThreads) k_seg_exits(const __grid_constant__ Frame f, int qin, int dynamic) {
     seg_exits_body(f, qin, dynamic != 0);
+}
+
+// applySegmentNeuralOutputKernel + prepareNextIterationKernel for one ray: decode the 16 fp16 outputs, record
+// the hit, or re-enter the shell; true when the ray goes on to another segment.
+__device__ __forceinline__ bool seg_apply_one(const Frame& f, int e, uint4 raw, const SurfRec& rec, unsigned int& nTrace) {
+    const FrameParams& fp = f.fp;
+    bool again = false;
+    const float2 o01 = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
+    const float2 o23 = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+    const float2 o45 = __half22float2(*reinterpret_cast<const __half2*>(&raw.z));
+    const float2 o67 = __half22float2(*reinterpret_cast<const __half2*>(&raw.w));
+    const float4 E = f.st.segE[e], X = f.st.segX[e];
+    const float2 I = f.st.segI[e];
+    const V3 entry = f4v(E), dir = f4v(f.st.segD[e]);
+    const float innerT = I.x, exitT = X.w;
+    const bool innerHit = __float_as_int(I.y) != 0;
+    const bool neuralHit = o01.x >= 0.0f;
+    if (neuralHit || (innerHit && innerT < exitT)) {
+        const V3 shifted = entry + dir * kSegEps;
+        const float distance = o01.y;
+        float d = distance * 1.0f;
+        if (innerT > 0.0f) d = fminf(d, innerT - kSegEps);
+        const V3 pos = shifted + dir * d;
+        V3 nrm = v3(o23.x, o23.y, o45.x);
+        const float nl = length(nrm);
+        nrm = nl > 1e-6f ? nrm / nl : v3(0.0f, 1.0f, 0.0f);
+        const V3 col = fp.useConstantNeuralColor ? fp.constantNeuralColor
+                                                 : v3(clamp01(o45.y), clamp01(o67.x), clamp01(o67.y));
+        rec_store(rec, e, pos, 1, nrm, distance, col, global_mparams(f.gmat));
+    } else {
+        const V3 shiftedExit = f4v(X) + dir * kSegEps;
+        const Hit hr = trace_dyn(target_of(f.mesh[NRB_SLOT_OUTER]), TRACE_FORWARD, shiftedExit, dir);
+        ++nTrace;
+        const bool re = hr.t < 1e30f;
+        if (re || innerHit) {
+            const float rd = re ? hr.t : 0.0f;
+            const V3 ne = shiftedExit + dir * rd;
+            f.st.segE[e] = make_float4(ne.x, ne.y, ne.z, E.w + exitT + rd + 2.0f * kSegEps);
+            again = true;
+        }
+    }
+    return again;
 }
 
 // One iteration, second half: decode the network output, record hits, re-enter the shell for the
@@ -132,41 +181,7 @@ __device__ __forceinline__ void seg_apply_body(const Frame& f, int qin, int qout
         int e = 0;
         if (i < n) {
             e = f.st.queue[qin][i];
-            const uint4 raw = *reinterpret_cast<const uint4*>(f.st.netOut + static_cast<size_t>(i) * 16);
-            const float2 o01 = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
-            const float2 o23 = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
-            const float2 o45 = __half22float2(*reinterpret_cast<const __half2*>(&raw.z));
-            const float2 o67 = __half22float2(*reinterpret_cast<const __half2*>(&raw.w));
-            const float4 E = f.st.segE[e], X = f.st.segX[e];
-            const float2 I = f.st.segI[e];
-            const V3 entry = f4v(E), dir = f4v(f.st.segD[e]);
-            const float innerT = I.x, exitT = X.w;
-            const bool innerHit = __float_as_int(I.y) != 0;
-            const bool neuralHit = o01.x >= 0.0f;
-            if (neuralHit || (innerHit && innerT < exitT)) {
-                const V3 shifted = entry + dir * kSegEps;
-                const float distance = o01.y;
-                float d = distance * 1.0f;
-                if (innerT > 0.0f) d = fminf(d, innerT - kSegEps);
-                const V3 pos = shifted + dir * d;
-                V3 nrm = v3(o23.x, o23.y, o45.x);
-                const float nl = length(nrm);
-                nrm = nl > 1e-6f ? nrm / nl : v3(0.0f, 1.0f, 0.0f);
-                const V3 col = fp.useConstantNeuralColor ? fp.constantNeuralColor
-                                                         : v3(clamp01(o45.y), clamp01(o67.x), clamp01(o67.y));
-                rec_store(rec, e, pos, 1, nrm, distance, col, global_mparams(f.gmat));
-            } else {
-                const V3 shiftedExit = f4v(X) + dir * kSegEps;
-                const Hit hr = trace_dyn(target_of(f.mesh[NRB_SLOT_OUTER]), TRACE_FORWARD, shiftedExit, dir);
-                ++nTrace;
-                const bool re = hr.t < 1e30f;
-                if (re || innerHit) {
-                    const float rd = re ? hr.t : 0.0f;
-                    const V3 ne = shiftedExit + dir * rd;
-                    f.st.segE[e] = make_float4(ne.x, ne.y, ne.z, E.w + exitT + rd + 2.0f * kSegEps);
-                    again = true;
-                }
-            }
+            again = seg_apply_one(f, e, *reinterpret_cast<const uint4*>(f.st.netOut + static_cast<size_t>(i) * 16), rec, nTrace);
         }
         queue_push(f.st.queue[qout], f.st.counts + qout, again, e);
     }
@@ -578,8 +593,99 @@ static bool prepare_tail(SegTail& t, const Frame& f, const NetDev& net, cudaStre
     return true;
 }
 
-static int run_segments(const Frame& f, const NetDev& net, int recIdx, cudaStream_t s, SegTail* tail) {
+// ---- the tail of the segment loop as ONE launch ------------------------------------------------------
+// The rays that leave iteration 0 of a pass without a hit and re-enter the shell (queue 3) are few - usually
+// none - and independent of each other, so nothing needs a grid-wide step between their iterations: a warp
+// takes 16 of them and carries them through exits -> network -> apply until each has hit, left, or used up
+// its iterations.  The network runs as the warp-autonomous mma.sync tile of nrb_query_warp.cuh against weights
+// the CTA loads once.  With an empty queue the launch returns at once: 4 such launches per frame replace four
+// conditional-graph launches of ~23 us each (profiles/: segment_tail_graph 0.094 ms per frame).
+template <int WIDTH>
+__global__ void __launch_bounds__(512, 1)
+    k_seg_tail(const __grid_constant__ Frame f, const __grid_constant__ NetDev net, int recIdx, int ek, int warps) {
+    using namespace qwarp;
+    const int n = f.st.counts[3];
+    if (n == 0 || blockIdx.x * warps * kRows >= n) return;
+    extern __shared__ __align__(16) unsigned char tailSmem[];
+    const int H = net.nHidden;
+    const int ld0 = ek + 8, ldw = WIDTH + 8, ldA = (ek > WIDTH ? ek : WIDTH) + 8;
+    __half* w0 = reinterpret_cast<__half*>(tailSmem);
+    __half* wh = w0 + WIDTH * ld0;
+    __half* wl = wh + (H - 1) * WIDTH * ldw;
+    unsigned char* perWarp = reinterpret_cast<unsigned char*>(wl + 16 * ldw);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    preload_weights<WIDTH>(net, ek, w0, wh, wl);
+    __syncthreads();
+    if (warp >= warps) return;
+    const size_t perWarpBytes = static_cast<size_t>(kRows) * ldA * 2 + static_cast<size_t>(kRows) * 16 * 4 + kRows * 16 * 2;
+    __half* act = reinterpret_cast<__half*>(perWarp + warp * perWarpBytes);
+    float* inp = reinterpret_cast<float*>(act + kRows * ldA);          // [16][16] fp32 inputs
+    __half* outRows = reinterpret_cast<__half*>(inp + kRows * 16);      // [16][16] fp16 outputs
+    const SurfRec& rec = f.st.rec[recIdx];
+    unsigned int nTrace = 0, nQuery = 0;
+    const int tiles = (n + kRows - 1) / kRows;
+    for (int tile = blockIdx.x * warps + warp; tile < tiles; tile += gridDim.x * warps) {
+        const int i = tile * kRows + lane;
+        bool alive = lane < kRows && i < n;
+        const int e = alive ? f.st.queue[3][i] : 0;
+        for (int it = 1; it < kMaxSegIters; ++it) {
+            if (lane < kRows)
+                for (int c = 0; c < 16; ++c) inp[lane * 16 + c] = 0.0f;
+            if (alive) {
+                seg_exit_one(f, e, inp + lane * 16);
+                ++nQuery;
+            }
+            __syncwarp();
+            query_tile<WIDTH>(net, ek, w0, wh, wl, act, inp, outRows, 16, kRows);
+            if (alive) alive = seg_apply_one(f, e, *reinterpret_cast<const uint4*>(outRows + lane * 16), rec, nTrace);
+            __syncwarp();
+            if (!__any_sync(0xffffffffu, alive)) break;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        nTrace += __shfl_xor_sync(0xffffffffu, nTrace, o);
+        nQuery += __shfl_xor_sync(0xffffffffu, nQuery, o);
+    }
+    if (lane == 0 && (nTrace | nQuery)) {
+        atomicAdd(f.st.stats + 0, static_cast<unsigned long long>(nTrace) + 2ull * nQuery);
+        atomicAdd(f.st.stats + 1, static_cast<unsigned long long>(nQuery));
+    }
+}
+
+// Shared-memory plan of k_seg_tail (weights + per-warp tiles); 0 warps = shape not supported by the mma.sync tile.
+static size_t seg_tail_smem(const NetDev& net, int* warpsOut, int* ekOut) {
+    int w = 0;
+    *warpsOut = 0;
+    if (neural_query_smem(net, &w) == 0 || w <= 0) return 0;
+    const qwarp::SmemPlan p = qwarp::plan_smem(net);
+    const size_t wbytes = p.weightHalfs * 2, per = p.perWarpBytes + qwarp::kRows * 16 * 2;
+    int warps = static_cast<int>((227 * 1024 - wbytes) / per);
+    if (warps > 16) warps = 16;
+    if (warps <= 0) return 0;
+    *warpsOut = warps;
+    *ekOut = p.ek;
+    return wbytes + per * warps;
+}
+
+static bool launch_seg_tail(const Frame& f, const NetDev& net, int recIdx, cudaStream_t s) {
+    int warps = 0, ek = 0;
+    const size_t smem = seg_tail_smem(net, &warps, &ek);
+    if (smem == 0) return false;
+    static bool attr = false;
+    if (!attr) {
+        cudaFuncSetAttribute(k_seg_tail<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaFuncSetAttribute(k_seg_tail<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        attr = true;
+    }
+    if (net.width == 128) k_seg_tail<128><<<148, 512, smem, s>>>(f, net, recIdx, ek, warps);
+    else k_seg_tail<64><<<148, 512, smem, s>>>(f, net, recIdx, ek, warps);
+    NRB_LAUNCHED("k_seg_tail", s);
+    return true;
+}
+
+static int run_segments(const Frame& f, const NetDev& net, int recIdx, cudaStream_t s, SegTail* tail, bool fused) {
     int launches = seg_iteration(f, net, recIdx, 2, queue_grid(f.fp.nElems), s);
+    if (fused && launch_seg_tail(f, net, recIdx, s)) return launches + 1;
     if (tail) {
         cudaGraphLaunch(tail->exec[recIdx], s);
         NRB_LAUNCHED("segment_tail_graph", s);
@@ -593,9 +699,10 @@ static int run_segments(const Frame& f, const NetDev& net, int recIdx, cudaStrea
     return launches;
 }
 
-int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStream_t s, SegTail* tail) {
+int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStream_t s, SegTail* tail, bool fusedTail) {
     const FrameParams& fp = f.fp;
     int launches = 0;
+    if (fusedTail) tail = nullptr;  // the fused tail kernel needs no graph
     if (tail && !prepare_tail(*tail, f, net, s)) tail = nullptr;
     if (tail) cudaMemcpyAsync(tail->dFrame, &f, sizeof(Frame), cudaMemcpyHostToDevice, s);
     cudaMemsetAsync(f.st.counts, 0, 16 * sizeof(int), s);
@@ -603,7 +710,7 @@ int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStr
     k_entry_camera<<<tiles, kTileThreads, 0, s>>>(f);
     NRB_LAUNCHED("k_entry_camera", s);
     ++launches;
-    launches += run_segments(f, net, 0, s, tail);
+    launches += run_segments(f, net, 0, s, tail, fusedTail);
     k_primary_finish<<<tiles, kTileThreads, 0, s>>>(f);
     NRB_LAUNCHED("k_primary_finish", s);
     ++launches;
@@ -622,7 +729,7 @@ int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStr
         }
         NRB_LAUNCHED("k_bounce_begin", s);
         launches += 2;
-        launches += run_segments(f, net, 1, s, tail);
+        launches += run_segments(f, net, 1, s, tail, fusedTail);
         cudaMemsetAsync(f.st.counts + 0, 0, sizeof(int), s);
         k_bounce_finish<<<grid, kQueueThreads, 0, s>>>(f, b, 1, 0);
         NRB_LAUNCHED("k_bounce_finish", s);

@@ -293,10 +293,10 @@ class RendererNeural:
         (process-wide)."""
         self._opt(K.OPT_QUERY_KERNEL, which)
 
-    def set_tail_graph(self, v: bool):
-        """Segment-loop iterations 1..9 as a device-driven conditional WHILE graph (default) or as
-        nine fixed launches per pass."""
-        self._opt(K.OPT_TAIL_GRAPH, 1 if v else 0)
+    def set_tail_graph(self, mode):
+        """Segment-loop iterations 1..9 of a pass: 0 / False = nine fixed launches, 1 / True = a device-driven
+        conditional WHILE graph, 2 = one fused tail kernel (the default)."""
+        self._opt(K.OPT_TAIL_GRAPH, int(mode))
 
     def set_denoise(self, v: bool):
         """Joint bilateral filter of the accumulated frame (reference src/denoiser.cuh) on the way to devicePixels()."""
