@@ -417,6 +417,19 @@ __global__ void __launch_bounds__(kQueueThreads, kBounceCtasPerSm) k_bounce_begi
             const unsigned bN = __ballot_sync(full, k == 0), bT = __ballot_sync(full, k == 1), bP = __ballot_sync(full, k == 2);
             const int busy = __popc(bN | bT | bP);
             if (busy == 0 || (more && busy < min(kRefillBelow, cap))) break;
+            if (busy == 1) {
+                // a lone ray (short launches: one per warp; the end of the drain): nobody to vote with, and the
+                // latency of this warp's instruction stream is all there is - run the ray to its end directly
+                if (k < 3) {
+                    do {
+                        const int kk = tr.kind();
+                        if (kk == 0) tr.step_node();
+                        else if (kk == 1) tr.step_tri();
+                        else tr.step_pop();
+                    } while (!tr.done());
+                }
+                break;
+            }
             const int nN = __popc(bN), nT = __popc(bT), nP = __popc(bP);
             if (nP >= 8 || (nP >= nN && nP >= nT)) {
                 if (k == 2) tr.step_pop();
