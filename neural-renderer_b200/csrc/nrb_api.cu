@@ -309,9 +309,9 @@ int relayout_mesh(nrb_renderer* r, MeshSlot& m, const nrb_mesh_desc* d) {
             const nrb_bvh_node& L = src[kids[0]];
             const nrb_bvh_node& R = src[kids[1]];
             NodePair& p = pairs[it.pair];
-            p.a = make_float4(lo(L.bounds_min[0]), lo(L.bounds_min[1]), lo(L.bounds_min[2]), hi(L.bounds_max[0]));
-            p.b = make_float4(hi(L.bounds_max[1]), hi(L.bounds_max[2]), lo(R.bounds_min[0]), lo(R.bounds_min[1]));
-            p.c = make_float4(lo(R.bounds_min[2]), hi(R.bounds_max[0]), hi(R.bounds_max[1]), hi(R.bounds_max[2]));
+            p.a = make_float4(lo(L.bounds_min[0]), lo(L.bounds_min[1]), hi(L.bounds_max[0]), hi(L.bounds_max[1]));
+            p.b = make_float4(lo(R.bounds_min[0]), lo(R.bounds_min[1]), hi(R.bounds_max[0]), hi(R.bounds_max[1]));
+            p.c = make_float4(lo(L.bounds_min[2]), hi(L.bounds_max[2]), lo(R.bounds_min[2]), hi(R.bounds_max[2]));
             p.d = make_int4(refs[0], refs[1], L.is_leaf ? L.count : 0, R.is_leaf ? R.count : 0);
         }
         v.rootRef = 0;

@@ -47,10 +47,12 @@ __device__ __forceinline__ ElemId queue_elem(const FrameParams& fp, int e) {
 // later bounces, the later segment iterations: a few thousand survivors - is spread one element per warp and
 // lane row (lane L of warp w starts at L * warps + w): such launches are latency-bound, and a warp that traces
 // r rays in lock step takes, phase by phase, as long as its slowest lane, so r should be as small as possible.
-__device__ __forceinline__ int queue_start(int n) {
+// `perWarp`: spread when the queue has at most this many elements per warp; stages that trace (divergent, no
+// coalescing to lose) pass 32 - every queue that fits the grid once is spread over all its warps.
+__device__ __forceinline__ int queue_start(int n, int perWarp = 4) {
     const int tid = blockIdx.x * blockDim.x + threadIdx.x;
     const int warps = (gridDim.x * blockDim.x) >> 5;
-    if (n > 4 * warps) return tid;
+    if (n > perWarp * warps) return tid;
     return (threadIdx.x & 31) * warps + (tid >> 5);
 }
 

@@ -19,9 +19,11 @@ namespace nrb {
 
 // Child reference: >= 0 -> index into NodePair[]; < 0 -> leaf, first triangle = ~ref.
 struct __align__(16) NodePair {
-    float4 a;  // lmin.x lmin.y lmin.z lmax.x
-    float4 b;  // lmax.y lmax.z rmin.x rmin.y
-    float4 c;  // rmin.z rmax.x rmax.y rmax.z
+    // (x, y) and (z, z) couples: every 8-byte half of a record meets the same couple of ray constants, so
+    // the 12 subtractions and 12 multiplications of the two slab tests are 6 + 6 packed fp32x2 instructions
+    float4 a;  // lmin.x lmin.y lmax.x lmax.y
+    float4 b;  // rmin.x rmin.y rmax.x rmax.y
+    float4 c;  // lmin.z lmax.z rmin.z rmax.z
     int4 d;    // leftRef rightRef leftCount rightCount
 };
 static_assert(sizeof(NodePair) == 64, "NodePair");

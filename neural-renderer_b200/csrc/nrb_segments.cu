@@ -63,16 +63,36 @@ __global__ void __launch_bounds__(kTileThreads) k_entry_camera(const __grid_cons
 // One iteration, first half: exits + network inputs for every ray in the segment queue.
 // traceSegmentExitsKernel + buildSegmentNeuralInputsKernel for one ray: exits into segX / segI, the D network
 // inputs into dst.
-__device__ __forceinline__ void seg_exit_one(const Frame& f, int e, float* dst) {
+// `pass`: -1 = both traces in this lane; 0 / 1 = this lane traces only the outer / the inner shell and its
+// partner lane (lane ^ 1, same ray) the other one - sparse launches, where the latency of one lane's chain of
+// traces is all there is.  All 32 lanes call (valid = false: no ray).
+__device__ __forceinline__ void seg_exit_one(const Frame& f, int e, float* dst, int pass = -1, bool valid = true) {
     const FrameParams& fp = f.fp;
     const int D = fp.inputDims;
-    const V3 entry = f4v(f.st.segE[e]), dir = f4v(f.st.segD[e]);
+    V3 entry = v3(0.f, 0.f, 0.f), dir = v3(0.f, 0.f, 1.f);
+    if (valid) {
+        entry = f4v(f.st.segE[e]);
+        dir = f4v(f.st.segD[e]);
+    }
     const V3 shifted = entry + dir * kSegEps;
-    const Hit ho = trace_dyn(target_of(f.mesh[NRB_SLOT_OUTER]), TRACE_BACKWARD, shifted, dir);
-    const float exitT = ho.t < 1e30f ? ho.t : kSegEps;
-    const Hit hi = trace_dyn(target_of(f.mesh[NRB_SLOT_INNER]), TRACE_ANY, shifted, dir);
-    const bool hitInner = hi.t < 1e30f;
-    const float innerT = hitInner ? hi.t : 1e30f;
+    // outer shell BACKWARD, then inner shell ANY: passes through ONE inlined copy of the traversal loop
+    float tOuter = 1e30f, tInner = 1e30f;
+    const int k0 = pass < 0 ? 0 : pass, k1 = !valid ? -1 : (pass < 0 ? 1 : pass);
+#pragma unroll 1
+    for (int k = k0; k <= k1; ++k) {
+        const MeshDev& m = f.mesh[k == 0 ? NRB_SLOT_OUTER : NRB_SLOT_INNER];
+        const Hit h = trace_dyn_inline(target_of(m), k == 0 ? TRACE_BACKWARD : TRACE_ANY, shifted, dir);
+        if (k == 0) tOuter = h.t; else tInner = h.t;
+    }
+    if (pass >= 0) {
+        const float mine = pass == 0 ? tOuter : tInner;
+        const float other = __shfl_xor_sync(0xffffffffu, mine, 1);
+        if (pass == 0) tInner = other; else tOuter = other;
+        if (!valid || pass != 0) return;  // the even lane of a couple writes
+    }
+    const float exitT = tOuter < 1e30f ? tOuter : kSegEps;
+    const bool hitInner = tInner < 1e30f;
+    const float innerT = hitInner ? tInner : 1e30f;
     const bool innerFirst = hitInner && (innerT < exitT);
     const V3 exitPos = innerFirst ? shifted + dir * innerT : shifted + dir * exitT;
     f.st.segX[e] = make_float4(exitPos.x, exitPos.y, exitPos.z, exitT);
@@ -102,9 +122,17 @@ __device__ __forceinline__ void seg_exits_body(const Frame& f, int qin, bool dyn
     const int D = fp.inputDims;
     const int total = gridDim.x * blockDim.x;
     dynamic = dynamic && n > (total >> 5) * 4;  // short queues: one ray per warp (queue_start)
+    if (!dynamic && 2 * n <= total) {
+        // sparse: one (ray, trace) task per lane, the couples of a queue spread over all warps
+        const int warps = total >> 5, lane = threadIdx.x & 31;
+        const int i = (lane >> 1) * warps + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+        const bool valid = i < n;
+        const int e = valid ? f.st.queue[qin][i] : 0;
+        seg_exit_one(f, e, f.st.netIn + static_cast<size_t>(valid ? i : 0) * D, lane & 1, valid);
+    } else {
     int* cursor = f.st.counts + 9;
     int chunk = 0;
-    for (int i = dynamic ? n : queue_start(n);; i += total) {
+    for (int i = dynamic ? n : queue_start(n, 32);; i += total) {
         if (dynamic) {
             if ((threadIdx.x & 31) == 0) chunk = atomicAdd(cursor, 32);
             chunk = __shfl_sync(0xffffffffu, chunk, 0);
@@ -115,6 +143,7 @@ __device__ __forceinline__ void seg_exits_body(const Frame& f, int qin, bool dyn
             break;
         }
         seg_exit_one(f, f.st.queue[qin][i], f.st.netIn + static_cast<size_t>(i) * D);
+    }
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         atomicAdd(f.st.stats + 0, 2ull * static_cast<unsigned long long>(n));
@@ -154,7 +183,7 @@ __device__ __forceinline__ bool seg_apply_one(const Frame& f, int e, uint4 raw, 
         rec_store(rec, e, pos, 1, nrm, distance, col, global_mparams(f.gmat));
     } else {
         const V3 shiftedExit = f4v(X) + dir * kSegEps;
-        const Hit hr = trace_dyn(target_of(f.mesh[NRB_SLOT_OUTER]), TRACE_FORWARD, shiftedExit, dir);
+        const Hit hr = trace_dyn_inline(target_of(f.mesh[NRB_SLOT_OUTER]), TRACE_FORWARD, shiftedExit, dir);
         ++nTrace;
         const bool re = hr.t < 1e30f;
         if (re || innerHit) {
@@ -173,7 +202,7 @@ __device__ __forceinline__ void seg_apply_body(const Frame& f, int qin, int qout
     const int n = f.st.counts[qin];
     const SurfRec& rec = f.st.rec[recIdx];
     unsigned int nTrace = 0;
-    const int first = queue_start(n);
+    const int first = queue_start(n, 32);
     for (int base = 0; base < n; base += gridDim.x * blockDim.x) {  // the same trip count for every thread
         const int i = base + first;
         bool again = false;
@@ -296,7 +325,13 @@ __global__ void __launch_bounds__(kQueueThreads) k_bounce_sample(const __grid_co
         f.st.rayD[e] = make_float4(wi.x, wi.y, wi.z, N.w);
         f.st.rayW[e] = make_float4(weight.x, weight.y, weight.z, 0.0f);
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(f.st.stats + 2, static_cast<unsigned long long>(n));
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        atomicAdd(f.st.stats + 2, static_cast<unsigned long long>(n));
+        // the counters this bounce fills (ray queue 1, segment queues 2 and 3, the two work cursors): their last
+        // readers were earlier launches and their first writers are later ones, so no memset nodes are needed
+        f.st.counts[1] = f.st.counts[2] = f.st.counts[3] = 0;
+        f.st.counts[8] = f.st.counts[9] = 0;
+    }
 }
 
 // Ten resident CTAs per SM (48 registers) measured best: 8 / 10 / 12 / 16 -> 0.808 / 0.791 / 0.800 / 0.921 ms.
@@ -498,9 +533,10 @@ __global__ void __launch_bounds__(kQueueThreads) k_bounce_finish(const __grid_co
 // frame block in the constant bank).  The remaining iterations run either as the WHILE graph above
 // (tail != nullptr) or, for the per-launch profiler and as the fallback, as nine fixed one-wave
 // launches whose grid-stride loops make any count correct.
-static int seg_iteration(const Frame& f, const NetDev& net, int recIdx, int qin, int grid, cudaStream_t s) {
+static int seg_iteration(const Frame& f, const NetDev& net, int recIdx, int qin, int grid, cudaStream_t s, bool first) {
     const int qout = qin == 2 ? 3 : 2;
-    cudaMemsetAsync(f.st.counts + qout, 0, sizeof(int), s);
+    // iteration 0 of a pass finds queue 3 empty (frame start / k_bounce_sample); the fixed loop resets per iteration
+    if (!first) cudaMemsetAsync(f.st.counts + qout, 0, sizeof(int), s);
     k_seg_exits<<<grid, kQueueThreads, 0, s>>>(f, qin, qin == 2 && grid > 148 ? 1 : 0);  // iteration 0 of a pass
     NRB_LAUNCHED("k_seg_exits", s);
     int launches = 1 + launch_neural_query(net, f.st.netIn, static_cast<size_t>(f.fp.nElems), f.st.counts + qin, f.st.netOut, s);
@@ -628,6 +664,8 @@ __global__ void __launch_bounds__(512, 1)
     k_seg_tail(const __grid_constant__ Frame f, const __grid_constant__ NetDev net, int recIdx, int ek, int warps) {
     using namespace qwarp;
     const int n = f.st.counts[3];
+    // path queue 0 was read by the stages before the segment loop and is refilled by k_bounce_finish after it
+    if (recIdx == 1 && blockIdx.x == 0 && threadIdx.x == 0) f.st.counts[0] = 0;
     if (n == 0 || blockIdx.x * warps * kRows >= n) return;
     extern __shared__ __align__(16) unsigned char tailSmem[];
     const int H = net.nHidden;
@@ -706,9 +744,12 @@ static bool launch_seg_tail(const Frame& f, const NetDev& net, int recIdx, cudaS
     return true;
 }
 
-static int run_segments(const Frame& f, const NetDev& net, int recIdx, cudaStream_t s, SegTail* tail, bool fused) {
-    int launches = seg_iteration(f, net, recIdx, 2, queue_grid(f.fp.nElems), s);
-    if (fused && launch_seg_tail(f, net, recIdx, s)) return launches + 1;
+static int run_segments(const Frame& f, const NetDev& net, int recIdx, cudaStream_t s, SegTail* tail, bool fused,
+                        bool* fusedRan = nullptr) {
+    int launches = seg_iteration(f, net, recIdx, 2, queue_grid(f.fp.nElems), s, true);
+    const bool ran = fused && launch_seg_tail(f, net, recIdx, s);
+    if (fusedRan) *fusedRan = ran;
+    if (ran) return launches + 1;
     if (tail) {
         cudaGraphLaunch(tail->exec[recIdx], s);
         NRB_LAUNCHED("segment_tail_graph", s);
@@ -716,7 +757,7 @@ static int run_segments(const Frame& f, const NetDev& net, int recIdx, cudaStrea
     }
     int qin = 3;
     for (int it = 1; it < kMaxSegIters; ++it) {
-        launches += seg_iteration(f, net, recIdx, qin, 148, s);
+        launches += seg_iteration(f, net, recIdx, qin, 148, s, false);
         qin = qin == 2 ? 3 : 2;
     }
     return launches;
@@ -741,8 +782,7 @@ int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStr
     const int grid = queue_grid(fp.nElems);
     for (int b = 1; b <= fp.maxBounces; ++b) {
         // path queue 0 -> ray queue 1 (+ segment queue 2) -> path queue 0
-        cudaMemsetAsync(f.st.counts + 1, 0, 3 * sizeof(int), s);
-        cudaMemsetAsync(f.st.counts + 8, 0, 2 * sizeof(int), s);  // work cursors of k_bounce_begin and k_seg_exits
+        // (k_bounce_sample resets the counters of the bounce: queues 1-3 and the two work cursors)
         k_bounce_sample<<<grid, kQueueThreads, 0, s>>>(f, b, 0);
         NRB_LAUNCHED("k_bounce_sample", s);
         {
@@ -752,8 +792,9 @@ int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStr
         }
         NRB_LAUNCHED("k_bounce_begin", s);
         launches += 2;
-        launches += run_segments(f, net, 1, s, tail, fusedTail);
-        cudaMemsetAsync(f.st.counts + 0, 0, sizeof(int), s);
+        bool fusedRan = false;
+        launches += run_segments(f, net, 1, s, tail, fusedTail, &fusedRan);
+        if (!fusedRan) cudaMemsetAsync(f.st.counts + 0, 0, sizeof(int), s);  // the fused tail kernel resets path queue 0 itself
         k_bounce_finish<<<grid, kQueueThreads, 0, s>>>(f, b, 1, 0);
         NRB_LAUNCHED("k_bounce_finish", s);
         ++launches;

@@ -36,6 +36,52 @@ __device__ __forceinline__ bool slab(V3 o, V3 inv, float mnx, float mny, float m
     return !(tmax < 0.0f || tmin > tMax || tmin > tmax);
 }
 
+// Both boxes of a NodePair against one ray with packed fp32x2 arithmetic (FADD2 / FMUL2 on sm_100: two
+// IEEE round-to-nearest results per instruction, the same values as the scalar form above; min/max have no
+// packed form).  The ray's origin and reciprocal direction are kept as (x, y) and (z, z) register couples.
+// Returns the best-independent part of intersectAabb per box (tmax >= 0 and tmin <= tmax) and the entry
+// distances; the caller adds "entry distance not beyond the current best".
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 submul2(f32x2 a, f32x2 o, f32x2 inv) {  // (a - o) * inv, two roundings
+    f32x2 d, r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(o));
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(d), "l"(inv));
+    return r;
+}
+struct RayPack {
+    f32x2 oxy, ozz, ixy, izz;
+};
+__device__ __forceinline__ RayPack ray_pack(V3 o, V3 inv) {
+    return RayPack{pack2(o.x, o.y), pack2(o.z, o.z), pack2(inv.x, inv.y), pack2(inv.z, inv.z)};
+}
+__device__ __forceinline__ bool slab_finish(float t1x, float t1y, float t1z, float t2x, float t2y, float t2z, float& tNear) {
+    float tmin = fminf(t1x, t2x), tmax = fmaxf(t1x, t2x);
+    tmin = fmaxf(tmin, fminf(t1y, t2y)); tmax = fminf(tmax, fmaxf(t1y, t2y));
+    tmin = fmaxf(tmin, fminf(t1z, t2z)); tmax = fminf(tmax, fmaxf(t1z, t2z));
+    tNear = tmin;
+    return !(tmax < 0.0f || tmin > tmax);
+}
+__device__ __forceinline__ void slab_pair(const RayPack& rp, float4 a, float4 b, float4 c, bool& okL, float& nearL,
+                                          bool& okR, float& nearR) {
+    float l1x, l1y, l2x, l2y, l1z, l2z, r1x, r1y, r2x, r2y, r1z, r2z;
+    unpack2(submul2(pack2(a.x, a.y), rp.oxy, rp.ixy), l1x, l1y);
+    unpack2(submul2(pack2(a.z, a.w), rp.oxy, rp.ixy), l2x, l2y);
+    unpack2(submul2(pack2(b.x, b.y), rp.oxy, rp.ixy), r1x, r1y);
+    unpack2(submul2(pack2(b.z, b.w), rp.oxy, rp.ixy), r2x, r2y);
+    unpack2(submul2(pack2(c.x, c.y), rp.ozz, rp.izz), l1z, l2z);
+    unpack2(submul2(pack2(c.z, c.w), rp.ozz, rp.izz), r1z, r2z);
+    okL = slab_finish(l1x, l1y, l1z, l2x, l2y, l2z, nearL);
+    okR = slab_finish(r1x, r1y, r1z, r2x, r2y, r2z, nearR);
+}
+
 // Counters for the roofline's algorithmic bytes (node pairs fetched, triangles fetched).
 struct TraceStats {
     unsigned int pairs, tris;
@@ -49,6 +95,7 @@ __device__ __forceinline__ Hit trace_closest(const MeshDev& m, V3 o, V3 d, Trace
     float tn;
     if (!slab(o, inv, m.rootMin[0], m.rootMin[1], m.rootMin[2], m.rootMax[0], m.rootMax[1], m.rootMax[2], best.t, tn))
         return best;
+    const RayPack rp = ray_pack(o, inv);
 
     int2 stack[kTraceStack];
     int sp = 0;
@@ -62,8 +109,10 @@ __device__ __forceinline__ Hit trace_closest(const MeshDev& m, V3 o, V3 d, Trace
             const int4 k = __ldg(&nodes[ref].d);
             if (STATS) st->pairs++;
             float ln, rn;
-            const bool hl = slab(o, inv, a.x, a.y, a.z, a.w, b.x, b.y, best.t, ln);
-            const bool hr = slab(o, inv, b.z, b.w, c.x, c.y, c.z, c.w, best.t, rn);
+            bool hl, hr;
+            slab_pair(rp, a, b, c, hl, ln, hr, rn);
+            hl = hl && !(ln > best.t);
+            hr = hr && !(rn > best.t);
             if (hl && hr) {
                 int nearRef = k.x, farRef = k.y;
                 float farT = rn;
@@ -153,12 +202,13 @@ __device__ __forceinline__ TraceTarget pick_target(bool first, const TraceTarget
 constexpr int kTraceDone = static_cast<int>(0x80000000u);  // not a leaf ref: first < 2^26 (checked at upload)
 constexpr int kTracePop = static_cast<int>(0x80000001u);   // MultiTrace: the lane must pop its stack next
 
-static __device__ __noinline__ Hit trace_dyn(TraceTarget m, int mode, V3 o, V3 d) {
+__device__ __forceinline__ Hit trace_dyn_inline(const TraceTarget& m, int mode, V3 o, V3 d) {
     Hit best{1e30f, 0.0f, 0.0f, 0u};
     if (m.numTriangles <= 0) return best;
     const V3 inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
     float tn;
     if (!slab(o, inv, m.bmin.x, m.bmin.y, m.bmin.z, m.bmax.x, m.bmax.y, m.bmax.z, best.t, tn)) return best;
+    const RayPack rp = ray_pack(o, inv);
     int2 stack[kTraceStack];
     int sp = 0;
     int ref = m.rootRef;
@@ -178,8 +228,10 @@ static __device__ __noinline__ Hit trace_dyn(TraceTarget m, int mode, V3 o, V3 d
             const float4 a = __ldg(&nodes[ref].a), b = __ldg(&nodes[ref].b), c = __ldg(&nodes[ref].c);
             const int4 k = __ldg(&nodes[ref].d);
             float ln, rn;
-            const bool hl = slab(o, inv, a.x, a.y, a.z, a.w, b.x, b.y, best.t, ln);
-            const bool hr = slab(o, inv, b.z, b.w, c.x, c.y, c.z, c.w, best.t, rn);
+            bool hl, hr;
+            slab_pair(rp, a, b, c, hl, ln, hr, rn);
+            hl = hl && !(ln > best.t);
+            hr = hr && !(rn > best.t);
             if (hl && hr) {
                 const bool rightFirst = rn < ln;
                 if (sp < kTraceStack) stack[sp++] = make_int2(rightFirst ? k.x : k.y, __float_as_int(rightFirst ? ln : rn));
@@ -221,6 +273,11 @@ static __device__ __noinline__ Hit trace_dyn(TraceTarget m, int mode, V3 o, V3 d
     return best;
 }
 
+// The out-of-line copy.  A function that is really called keeps the global-memory descriptor in a vector
+// register and moves it to a uniform one before every load (6 R2UR per node step): stages with one or two
+// traces on their critical path (segment exits, re-entry) inline the loop instead, once per kernel.
+static __device__ __noinline__ Hit trace_dyn(TraceTarget m, int mode, V3 o, V3 d) { return trace_dyn_inline(m, mode, o, d); }
+
 // Slab test split into its best-independent part (ok) and the entry distance; the reference's full
 // test is  ok && !(tNear > tMax).
 __device__ __forceinline__ bool slab_base(V3 o, V3 inv, float mnx, float mny, float mnz, float mxx, float mxy,
@@ -251,6 +308,7 @@ __device__ __noinline__ static void trace_multi(TraceTarget m, int want, V3 o, V
     const V3 inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
     float tn;
     if (!slab_base(o, inv, m.bmin.x, m.bmin.y, m.bmin.z, m.bmax.x, m.bmax.y, m.bmax.z, tn) || tn > 1e30f) return;
+    const RayPack rp = ray_pack(o, inv);
     int2 stack[kTraceStack];
     unsigned char smask[kTraceStack];
     int sp = 0, ref = m.rootRef, mask = want;
@@ -277,8 +335,8 @@ __device__ __noinline__ static void trace_multi(TraceTarget m, int want, V3 o, V
             const float4 a = __ldg(&nodes[ref].a), b = __ldg(&nodes[ref].b), c = __ldg(&nodes[ref].c);
             const int4 k = __ldg(&nodes[ref].d);
             float ln, rn;
-            const bool bl = slab_base(o, inv, a.x, a.y, a.z, a.w, b.x, b.y, ln);
-            const bool br = slab_base(o, inv, b.z, b.w, c.x, c.y, c.z, c.w, rn);
+            bool bl, br;
+            slab_pair(rp, a, b, c, bl, ln, br, rn);
             const int ml = bl ? live(mask, ln) : 0, mr = br ? live(mask, rn) : 0;
             if (ml && mr) {
                 const bool rightFirst = rn < ln;
@@ -351,7 +409,8 @@ __device__ __noinline__ static void trace_multi(TraceTarget m, int want, V3 o, V
 struct MultiTrace {
     const NodePair* nodes;
     const TriBlock* tris;
-    V3 o, d, inv;
+    V3 d;
+    RayPack rp;  // origin and reciprocal direction as fp32x2 couples (the origin is read back from it)
     float best0, best1, best2, limit;
     int ref, sp, want, cur;  // cur: next triangle of the current leaf, -1 = leaf not started
     int2 stack[kTraceStack];
@@ -367,11 +426,11 @@ struct MultiTrace {
         sp = 0;
         cur = -1;
         if (m.numTriangles <= 0 || wanted == 0) return;
-        o = org;
         d = dir;
-        inv = v3(1.0f / dir.x, 1.0f / dir.y, 1.0f / dir.z);
+        const V3 inv = v3(1.0f / dir.x, 1.0f / dir.y, 1.0f / dir.z);
         float tn;
-        if (!slab_base(o, inv, m.bmin.x, m.bmin.y, m.bmin.z, m.bmax.x, m.bmax.y, m.bmax.z, tn) || tn > 1e30f) return;
+        if (!slab_base(org, inv, m.bmin.x, m.bmin.y, m.bmin.z, m.bmax.x, m.bmax.y, m.bmax.z, tn) || tn > 1e30f) return;
+        rp = ray_pack(org, inv);
         nodes = m.nodes;
         tris = m.tris;
         want = wanted;
@@ -385,8 +444,10 @@ struct MultiTrace {
         const float4 a = __ldg(&nodes[ref].a), b = __ldg(&nodes[ref].b), c = __ldg(&nodes[ref].c);
         const int4 k = __ldg(&nodes[ref].d);
         float ln, rn;
-        const bool hl = slab_base(o, inv, a.x, a.y, a.z, a.w, b.x, b.y, ln) && !(ln > limit);
-        const bool hr = slab_base(o, inv, b.z, b.w, c.x, c.y, c.z, c.w, rn) && !(rn > limit);
+        bool hl, hr;
+        slab_pair(rp, a, b, c, hl, ln, hr, rn);
+        hl = hl && !(ln > limit);
+        hr = hr && !(rn > limit);
         if (hl && hr) {
             const bool rightFirst = rn < ln;
             if (sp < kTraceStack) stack[sp++] = make_int2(rightFirst ? k.x : k.y, __float_as_int(rightFirst ? ln : rn));
@@ -415,6 +476,9 @@ struct MultiTrace {
         const float det = dot(e1, pv);
         bool ok = acc != 0 && !(fabsf(det) < 1e-8f);
         const float invDet = 1.0f / det;
+        V3 o;
+        unpack2(rp.oxy, o.x, o.y);
+        o.z = __uint_as_float(static_cast<unsigned int>(rp.ozz));
         const V3 tv = o - v3(p.x, p.y, p.z);
         const float u = dot(tv, pv) * invDet;
         ok = ok && !(u < 0.0f || u > 1.0f);
