@@ -122,7 +122,7 @@ struct nrb_renderer {
     // network
     nrb_nn_config cfg{};
     NetDev net{};
-    DevBuf grid, mlp, packedW, xt;
+    DevBuf grid, mlp, packedW, xt, encCur;
     SegTail segTail;
     int tailMode = 2;  // NRB_OPT_TAIL_GRAPH: 0 fixed loop, 1 conditional WHILE graph, 2 fused tail kernel
     bool denoise = false;
@@ -684,6 +684,11 @@ int ensure_xt(nrb_renderer* r, size_t rows) {
         NRB_CUDA(cudaStreamSynchronize(r->stream));
         NRB_CUDA(r->xt.alloc(need));
     }
+    if (!r->encCur.p) {
+        NRB_CUDA(r->encCur.alloc(kMaxLevels * sizeof(int)));
+        NRB_CUDA(cudaMemsetAsync(r->encCur.p, 0, r->encCur.bytes, r->stream));
+    }
+    r->net.encCursor = r->encCur.as<int>();
     r->net.xt = r->xt.p;
     r->net.xtRows = static_cast<uint32_t>(r->xt.bytes / split_xt_bytes(r->net, 128) * 128);
     return NRB_OK;

@@ -25,6 +25,7 @@ struct NetDev {
     const void* packedW;  // split_packed_bytes(net) bytes, written by split_prepack()
     void* xt;             // [xtRows/128][EK/8][128][8] fp16 encoded tiles
     uint32_t xtRows;      // capacity of xt in rows (multiple of 128); 0 = split path unavailable
+    int* encCursor;       // [nLevels] k_query_encode's per-level tile cursors (zero between launches)
     uint32_t levelOffset[kMaxLevels];
     uint32_t levelSize[kMaxLevels];     // hashmap_size of the level (entries)
     uint32_t levelRes[kMaxLevels];

@@ -79,7 +79,7 @@ SplitPlan make_plan(const NetDev& net) {
     uint32_t best = 0;
     for (int l = 0; l < net.nLevels; ++l) {
         const uint64_t bytes = (static_cast<uint64_t>(net.levelSize[l]) * net.nFeatures * 2 + 127u) / 128u * 128u;
-        if (bytes + p.encRing <= kSmemMax && bytes > best) best = static_cast<uint32_t>(bytes);
+        if (bytes + p.encRing + 16u <= kSmemMax && bytes > best) best = static_cast<uint32_t>(bytes);
     }
     p.encSmem = best;
     p.slices = net.nLevels > 0 ? (148 / net.nLevels > 0 ? 148 / net.nLevels : 1) : 1;
@@ -217,11 +217,17 @@ __device__ __forceinline__ void encode_point(const LevelInfo& lv, const unsigned
 template <int F, bool SMEM>
 __device__ __forceinline__ void encode_tasks(const NetDev& net, const LevelInfo& lv, int level, const unsigned char* gtable,
                                              uint32_t stable, const float* __restrict__ in, int rowBase, int rowEnd,
-                                             int tiles, int slice, int slices, unsigned char* __restrict__ xt, int ek,
+                                             int tiles, int* cursor, unsigned char* __restrict__ xt, int ek,
                                              float* stageBase) {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nWarps = blockDim.x >> 5;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int P = net.nPoints, D = net.inputDims, L = net.nLevels;
-    const int myTiles = (tiles - slice + slices - 1) / slices;
+    // the next tile of this level nobody has taken yet (warp-uniform), -1 when the level is finished
+    auto claim = [&]() {
+        int t = 0;
+        if (lane == 0) t = atomicAdd(cursor, 1);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        return t < tiles ? t : -1;
+    };
     const int PF = P * F, PLF = PF * L, shN = net.shDegree * net.shDegree;
     const uint32_t tileBytes = static_cast<uint32_t>(ek) * kTileM * 2;
     const int k0 = level * PF;  // first column of this level
@@ -232,9 +238,8 @@ __device__ __forceinline__ void encode_tasks(const NetDev& net, const LevelInfo&
     const int stageFloats = 32 * D;
     float* stage = stageBase + warp * 2 * stageFloats;
     const size_t inBytes = static_cast<size_t>(rowEnd) * D * 4;
-    auto fetch = [&](int task, int slot) {
-        const int tile = slice + (task >> 2) * slices;
-        const size_t off = static_cast<size_t>(rowBase + tile * kTileM + ((task & 3) << 5)) * D * 4;
+    auto fetch = [&](int tile, int group, int slot) {
+        const size_t off = static_cast<size_t>(rowBase + tile * kTileM + (group << 5)) * D * 4;
         const unsigned char* src = reinterpret_cast<const unsigned char*>(in) + off;
         const uint32_t dst = tc::s32(stage + slot * stageFloats);
         if (off + 128u * D <= inBytes) {  // the whole 32-row block is inside the batch (all but the last task)
@@ -249,23 +254,26 @@ __device__ __forceinline__ void encode_tasks(const NetDev& net, const LevelInfo&
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
-    const int nTasks = myTiles * 4;
-    int it = 0;
-    if (warp < nTasks) fetch(warp, 0);
-    for (int task = warp; task < nTasks; task += nWarps, ++it) {
-        const int tl = task >> 2, g = task & 3;
-        const int tile = slice + tl * slices;
-        const int r = (g << 5) + lane;
-        const int row = rowBase + tile * kTileM + r;
+    int tile = claim(), g = 0, it = 0;
+    if (tile >= 0) fetch(tile, 0, 0);
+    for (; tile >= 0; ++it) {
+        const int curTile = tile, curG = g;
+        // the task after this one: the next 32-row group of the tile, then the next tile of the level
+        if (++g == 4) {
+            g = 0;
+            tile = claim();
+        }
         const int slot = it & 1;
-        if (task + nWarps < nTasks) {
-            fetch(task + nWarps, slot ^ 1);
+        if (tile >= 0) {
+            fetch(tile, g, slot ^ 1);
             asm volatile("cp.async.wait_group 1;" ::: "memory");
         } else {
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
+        const int r = (curG << 5) + lane;
+        const int row = rowBase + curTile * kTileM + r;
         __syncwarp();  // this task's rows have landed in the slot
-        unsigned char* tbase = xt + static_cast<size_t>(tile) * tileBytes + r * 16;
+        unsigned char* tbase = xt + static_cast<size_t>(curTile) * tileBytes + r * 16;
         float x[16];
         const float* xs = stage + slot * stageFloats + lane * D;
         if ((D & 3) == 0) {
@@ -306,7 +314,7 @@ __device__ __forceinline__ void encode_tasks(const NetDev& net, const LevelInfo&
                     else *reinterpret_cast<uint32_t*>(dst) = w[p][0];
                 }
         }
-        if (shOwner(tile * 4 + g) && PLF < ek) {
+        if (shOwner(curTile * 4 + curG) && PLF < ek) {
             // spherical harmonics + K padding: columns [PLF, ek), PLF % 8 == 0 is a support condition
             __half tail[32];
 #pragma unroll
@@ -337,29 +345,48 @@ __global__ void __launch_bounds__(kEncThreads, 1)
     if (n < rowEnd) rowEnd = n;
     if (rowEnd <= rowBase) return;
     const int tiles = (rowEnd - rowBase + kTileM - 1) / kTileM;
-    const int L = net.nLevels, slices = gridDim.x / L;
-    const int level = blockIdx.x % L, slice = blockIdx.x / L;
-    if (slice >= tiles || slice >= slices) return;
-
-    LevelInfo lv;
-    lv.scale = net.levelScale[level];
-    lv.res = net.levelRes[level];
-    lv.size = net.levelSize[level];
-    lv.dense = net.levelDense[level] != 0;
-    lv.pow2 = net.levelPow2[level] != 0;
-    lv.mask = (lv.size - 1u) * (F * 2u);
-    const unsigned char* gtable = reinterpret_cast<const unsigned char*>(net.grid + static_cast<size_t>(net.levelOffset[level]) * F);
-    const uint32_t tableBytes = lv.size * F * 2u;
-    const bool staged = tableBytes <= smemBytes && !(net.debug & 4);
-    if (staged) {
-        for (uint32_t i = threadIdx.x * 16u; i < tableBytes; i += blockDim.x * 16u)
-            *reinterpret_cast<uint4*>(smem + i) = __ldg(reinterpret_cast<const uint4*>(gtable + i));
+    const int L = net.nLevels;
+    int* cursors = net.encCursor;  // [L] next unclaimed tile per level; zero at launch, reset by k_query_mlp
+    // (a static __shared__ variable would push the 227 KB dynamic allocation over the per-block limit)
+    int& sNext = *reinterpret_cast<int*>(smem + smemBytes + (blockDim.x >> 5) * 2u * 32u * net.inputDims * 4u);
+    int staged = -1;
+    for (int level = blockIdx.x % L; level >= 0;) {
+        LevelInfo lv;
+        lv.scale = net.levelScale[level];
+        lv.res = net.levelRes[level];
+        lv.size = net.levelSize[level];
+        lv.dense = net.levelDense[level] != 0;
+        lv.pow2 = net.levelPow2[level] != 0;
+        lv.mask = (lv.size - 1u) * (F * 2u);
+        const unsigned char* gtable = reinterpret_cast<const unsigned char*>(net.grid + static_cast<size_t>(net.levelOffset[level]) * F);
+        const uint32_t tableBytes = lv.size * F * 2u;
+        const bool fits = tableBytes <= smemBytes && !(net.debug & 4);
+        if (fits) {
+            if (staged != level) {
+                for (uint32_t i = threadIdx.x * 16u; i < tableBytes; i += blockDim.x * 16u)
+                    *reinterpret_cast<uint4*>(smem + i) = __ldg(reinterpret_cast<const uint4*>(gtable + i));
+                staged = level;
+                __syncthreads();
+            }
+            encode_tasks<F, true>(net, lv, level, gtable, tc::s32(smem), in, rowBase, rowEnd, tiles, cursors + level, xt, ek,
+                                  reinterpret_cast<float*>(smem + smemBytes));
+        } else {
+            encode_tasks<F, false>(net, lv, level, gtable, 0u, in, rowBase, rowEnd, tiles, cursors + level, xt, ek,
+                                   reinterpret_cast<float*>(smem + smemBytes));
+        }
+        __syncthreads();  // every warp has found this level's cursor past the end
+        // The levels do not cost the same (coarse levels gather a few shared cells, fine ones 24 random entries
+        // per query): a CTA whose level is finished restages the table of the level furthest behind.
+        if (threadIdx.x == 0) {
+            int best = -1, bestAt = tiles;
+            for (int l = 0; l < L; ++l) {
+                const int at = *reinterpret_cast<volatile int*>(cursors + l);
+                if (at < bestAt) { bestAt = at; best = l; }
+            }
+            sNext = best;
+        }
         __syncthreads();
-        encode_tasks<F, true>(net, lv, level, gtable, tc::s32(smem), in, rowBase, rowEnd, tiles, slice, slices, xt, ek,
-                              reinterpret_cast<float*>(smem + smemBytes));
-    } else {
-        encode_tasks<F, false>(net, lv, level, gtable, 0u, in, rowBase, rowEnd, tiles, slice, slices, xt, ek,
-                               reinterpret_cast<float*>(smem + smemBytes));
+        level = sNext;
     }
 }
 
@@ -395,6 +422,7 @@ __global__ void __launch_bounds__(kMlpThreads, 1)
     if (n < rowEnd) rowEnd = n;
     if (rowEnd <= rowBase) return;
     const int tiles = (rowEnd - rowBase + kTileM - 1) / kTileM;
+    if (blockIdx.x == 0 && tid < net.nLevels) net.encCursor[tid] = 0;  // k_query_encode's tile cursors, for its next launch
     if (static_cast<int>(blockIdx.x) >= tiles) return;
     const bool tr = (net.debug & 16) && blockIdx.x == 0;
     const int nMine = (tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
@@ -606,7 +634,7 @@ int split_prepack(const NetDev& net, void* packedW, cudaStream_t s) {
 
 int launch_split_query(const NetDev& net, const float* in, size_t n, const int* dCount, __half* out, cudaStream_t s) {
     if (n == 0) return 0;
-    if (!net.packedW || !net.xt || net.xtRows < kTileM) return -1;
+    if (!net.packedW || !net.xt || net.xtRows < kTileM || !net.encCursor) return -1;
     const SplitPlan p = make_plan(net);
     static bool attr = false;
     if (!attr) {
@@ -622,14 +650,15 @@ int launch_split_query(const NetDev& net, const float* in, size_t n, const int* 
     for (size_t base = 0; base < n; base += chunkRows) {
         const size_t rows = n - base < static_cast<size_t>(chunkRows) ? n - base : chunkRows;
         const int tiles = static_cast<int>((rows + kTileM - 1) / kTileM);
-        int slices = p.slices < tiles ? p.slices : tiles;
-        const int egrid = net.nLevels * slices;
+        // one CTA per SM, never more than four tiles' worth of CTAs per level
+        const int want = net.nLevels * ((tiles + 3) / 4);
+        const int egrid = want < 148 ? want : 148;
         unsigned char* xt = static_cast<unsigned char*>(net.xt);
         if (net.nFeatures == 4)
-            k_query_encode<4><<<egrid, kEncThreads, p.encSmem + p.encRing, s>>>(net, in, static_cast<int>(n), dCount, static_cast<int>(base),
+            k_query_encode<4><<<egrid, kEncThreads, p.encSmem + p.encRing + 16u, s>>>(net, in, static_cast<int>(n), dCount, static_cast<int>(base),
                                                                     chunkRows, xt, p.ek, p.encSmem);
         else
-            k_query_encode<2><<<egrid, kEncThreads, p.encSmem + p.encRing, s>>>(net, in, static_cast<int>(n), dCount, static_cast<int>(base),
+            k_query_encode<2><<<egrid, kEncThreads, p.encSmem + p.encRing + 16u, s>>>(net, in, static_cast<int>(n), dCount, static_cast<int>(base),
                                                                     chunkRows, xt, p.ek, p.encSmem);
         NRB_LAUNCHED("k_query_encode", s);
         const int mgrid = tiles < 148 ? tiles : 148;
