@@ -154,22 +154,22 @@ __global__ void __launch_bounds__(kQueueThreads) k_seg_exits(const __grid_consta
     seg_exits_body(f, qin, dynamic != 0);
 }
 
-// applySegmentNeuralOutputKernel + prepareNextIterationKernel for one ray: decode the 16 fp16 outputs, record
-// the hit, or re-enter the shell; true when the ray goes on to another segment.
-__device__ __forceinline__ bool seg_apply_one(const Frame& f, int e, uint4 raw, const SurfRec& rec, unsigned int& nTrace) {
+// applySegmentNeuralOutputKernel + prepareNextIterationKernel for one ray, in two halves.  seg_apply_decode:
+// decode the 16 fp16 outputs and record the hit; returns -1 when the ray hit, else the inner-hit flag (0 / 1) of a
+// ray that left the segment and must look for its re-entry.  seg_apply_reenter: that trace; true when the ray goes
+// on to another segment.
+__device__ __forceinline__ int seg_apply_decode(const Frame& f, int e, uint4 raw, const SurfRec& rec) {
     const FrameParams& fp = f.fp;
-    bool again = false;
     const float2 o01 = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
     const float2 o23 = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
     const float2 o45 = __half22float2(*reinterpret_cast<const __half2*>(&raw.z));
     const float2 o67 = __half22float2(*reinterpret_cast<const __half2*>(&raw.w));
-    const float4 E = f.st.segE[e], X = f.st.segX[e];
     const float2 I = f.st.segI[e];
-    const V3 entry = f4v(E), dir = f4v(f.st.segD[e]);
-    const float innerT = I.x, exitT = X.w;
+    const float innerT = I.x, exitT = f.st.segX[e].w;
     const bool innerHit = __float_as_int(I.y) != 0;
     const bool neuralHit = o01.x >= 0.0f;
     if (neuralHit || (innerHit && innerT < exitT)) {
+        const V3 entry = f4v(f.st.segE[e]), dir = f4v(f.st.segD[e]);
         const V3 shifted = entry + dir * kSegEps;
         const float distance = o01.y;
         float d = distance * 1.0f;
@@ -181,38 +181,74 @@ __device__ __forceinline__ bool seg_apply_one(const Frame& f, int e, uint4 raw, 
         const V3 col = fp.useConstantNeuralColor ? fp.constantNeuralColor
                                                  : v3(clamp01(o45.y), clamp01(o67.x), clamp01(o67.y));
         rec_store(rec, e, pos, 1, nrm, distance, col, global_mparams(f.gmat));
-    } else {
-        const V3 shiftedExit = f4v(X) + dir * kSegEps;
-        const Hit hr = trace_dyn_inline(target_of(f.mesh[NRB_SLOT_OUTER]), TRACE_FORWARD, shiftedExit, dir);
-        ++nTrace;
-        const bool re = hr.t < 1e30f;
-        if (re || innerHit) {
-            const float rd = re ? hr.t : 0.0f;
-            const V3 ne = shiftedExit + dir * rd;
-            f.st.segE[e] = make_float4(ne.x, ne.y, ne.z, E.w + exitT + rd + 2.0f * kSegEps);
-            again = true;
-        }
+        return -1;
     }
-    return again;
+    return innerHit ? 1 : 0;
+}
+__device__ __forceinline__ bool seg_apply_reenter(const Frame& f, int e, bool innerHit) {
+    const float4 X = f.st.segX[e];
+    const V3 dir = f4v(f.st.segD[e]);
+    const V3 shiftedExit = f4v(X) + dir * kSegEps;
+    const Hit hr = trace_dyn_inline(target_of(f.mesh[NRB_SLOT_OUTER]), TRACE_FORWARD, shiftedExit, dir);
+    const bool re = hr.t < 1e30f;
+    if (re || innerHit) {
+        const float rd = re ? hr.t : 0.0f;
+        const V3 ne = shiftedExit + dir * rd;
+        f.st.segE[e] = make_float4(ne.x, ne.y, ne.z, f.st.segE[e].w + X.w + rd + 2.0f * kSegEps);
+        return true;
+    }
+    return false;
+}
+__device__ __forceinline__ bool seg_apply_one(const Frame& f, int e, uint4 raw, const SurfRec& rec, unsigned int& nTrace) {
+    const int st = seg_apply_decode(f, e, raw, rec);
+    if (st < 0) return false;
+    ++nTrace;
+    return seg_apply_reenter(f, e, st != 0);
 }
 
 // One iteration, second half: decode the network output, record hits, re-enter the shell for the
 // rays that go on, and compact them into the next queue.
+//
+// Only the rays that leave their segment without a hit trace here (10 of 32 lanes with the trace inside the
+// per-ray branch, profiles/r1_v12_mid_kernels_ncu.txt): a warp decodes 32 rays per trip, parks those that must
+// look for a re-entry in a 64-entry list in shared memory, and traces 32 of them at a time with every lane busy.
 __device__ __forceinline__ void seg_apply_body(const Frame& f, int qin, int qout, int recIdx) {
+    __shared__ int parked[kQueueThreads / 32][64];  // e | innerHit << 31
     const int n = f.st.counts[qin];
     const SurfRec& rec = f.st.rec[recIdx];
     unsigned int nTrace = 0;
     const int first = queue_start(n, 32);
-    for (int base = 0; base < n; base += gridDim.x * blockDim.x) {  // the same trip count for every thread
-        const int i = base + first;
+    const int lane = threadIdx.x & 31;
+    int* mine = parked[threadIdx.x >> 5];
+    int nParked = 0;  // warp-uniform
+    auto drain = [&](int take) {  // the last `take` parked rays, one per lane
+        nParked -= take;
+        const bool on = lane < take;
         bool again = false;
         int e = 0;
-        if (i < n) {
-            e = f.st.queue[qin][i];
-            again = seg_apply_one(f, e, *reinterpret_cast<const uint4*>(f.st.netOut + static_cast<size_t>(i) * 16), rec, nTrace);
+        if (on) {
+            const int v = mine[nParked + lane];
+            e = v & 0x7fffffff;
+            again = seg_apply_reenter(f, e, v < 0);
+            ++nTrace;
         }
         queue_push(f.st.queue[qout], f.st.counts + qout, again, e);
+        __syncwarp();
+    };
+    for (int base = 0; base < n; base += gridDim.x * blockDim.x) {  // the same trip count for every thread
+        const int i = base + first;
+        int st = -1, e = 0;
+        if (i < n) {
+            e = f.st.queue[qin][i];
+            st = seg_apply_decode(f, e, *reinterpret_cast<const uint4*>(f.st.netOut + static_cast<size_t>(i) * 16), rec);
+        }
+        const unsigned votes = __ballot_sync(0xffffffffu, st >= 0);
+        if (st >= 0) mine[nParked + __popc(votes & ((1u << lane) - 1))] = e | (st << 31);
+        nParked += __popc(votes);
+        __syncwarp();
+        if (nParked >= 32) drain(32);
     }
+    if (nParked > 0) drain(nParked);
     stat_flush(f.st.stats + 0, nTrace);
 }
 __global__ void __launch_bounds__(kQueueThreads) k_seg_apply(const __grid_constant__ Frame f, int qin, int qout,
@@ -308,7 +344,7 @@ constexpr int kRefillBelow = 22;
 
 // sampleBounceDirectionsKernel (:357-499) on the live-path queue: fully convergent apart from the
 // three-way lobe choice.  A path the reference deactivates here is marked by pdf = -1.
-__global__ void __launch_bounds__(kQueueThreads) k_bounce_sample(const __grid_constant__ Frame f, int bounce, int qin) {
+__global__ void __launch_bounds__(kQueueThreads, 8) k_bounce_sample(const __grid_constant__ Frame f, int bounce, int qin) {
     const FrameParams& fp = f.fp;
     const int n = f.st.counts[qin];
     const SurfRec& cur = f.st.rec[bounce == 1 ? 0 : 1];
