@@ -207,11 +207,19 @@ typedef enum nrb_option {
     NRB_OPT_TAIL_GRAPH = 12,          /* (new) segment-loop iterations 1..9 of a pass: 2 (default) one fused kernel in which
                                          a warp carries 16 of the few continuing rays through exits -> network -> apply;
                                          1 a device-driven CUDA conditional WHILE graph; 0 nine fixed launches */
-    NRB_OPT_DENOISE = 13              /* (new) 1: the frame written to devicePixels() is the joint bilateral filter of
+    NRB_OPT_DENOISE = 13,             /* (new) 1: the frame written to devicePixels() is the joint bilateral filter of
                                          the accumulation (bilateralDenoiseKernel, src/denoiser.cuh:47-113, which the
                                          reference ships but never launches), guided by the sample-0 primary-hit
                                          normal and albedo; accumulation itself is untouched.  Single-GPU frames only
                                          (nrb_set_tile world 1): the 11x11 window would need rows of other ranks. */
+    NRB_OPT_LITERAL_BOUNCE_TRACES = 14 /* (new, parity hook) 1: the bounce entry runs every trace of
+                                         checkBounceEarlyTermination / traceOuterShellEntryFromRays
+                                         (src/cuda_renderer_neural.cu:503-553, 773-852) literally.  0 (default): traces
+                                         whose outcome is already decided are not run - the inner-shell trace stops
+                                         at the outer-shell distance it is compared with (and is skipped when there is
+                                         none), and the FORWARD re-entry trace from beyond the BACKWARD exit is skipped
+                                         when the first FORWARD trace found no front face along the WHOLE ray: its
+                                         candidates are a subset of that trace's. */
 } nrb_option;
 int nrb_set_option(nrb_renderer* r, int option, int value);
 int nrb_get_option(const nrb_renderer* r, int option);

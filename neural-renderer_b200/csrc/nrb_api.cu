@@ -126,6 +126,7 @@ struct nrb_renderer {
     SegTail segTail;
     int tailMode = 2;  // NRB_OPT_TAIL_GRAPH: 0 fixed loop, 1 conditional WHILE graph, 2 fused tail kernel
     bool denoise = false;
+    bool literalBounceTraces = false;
     size_t gridParams = 0, mlpParams = 0;
     bool weightsLoaded = false;
 
@@ -552,6 +553,7 @@ int nrb_set_option(nrb_renderer* r, int option, int value) {
         case NRB_OPT_QUERY_KERNEL: set_query_kernel(value); break;
         case NRB_OPT_TAIL_GRAPH: r->tailMode = value < 0 ? 0 : (value > 2 ? 2 : value); break;
         case NRB_OPT_DENOISE: r->denoise = value != 0; break;
+        case NRB_OPT_LITERAL_BOUNCE_TRACES: r->literalBounceTraces = value != 0; break;
         case NRB_OPT_USE_HARDWARE_RT: break;  // accepted, ignored: there is no OptiX path
         default: return fail(NRB_ERR_INVALID, "unknown option");
     }
@@ -573,6 +575,7 @@ int nrb_get_option(const nrb_renderer* r, int option) {
         case NRB_OPT_QUERY_KERNEL: return query_kernel();
         case NRB_OPT_TAIL_GRAPH: return r->tailMode;
         case NRB_OPT_DENOISE: return r->denoise ? 1 : 0;
+        case NRB_OPT_LITERAL_BOUNCE_TRACES: return r->literalBounceTraces ? 1 : 0;
         default: return 0;
     }
 }
@@ -813,6 +816,7 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     f.st = r->st;
     f.classicSlot = classicSlot;
     f.additionalEnabled = r->useAdditionalMesh ? 1 : 0;
+    f.literalBounceTraces = r->literalBounceTraces ? 1 : 0;
 
     cudaStream_t s = r->stream;
     if (r->profile) {

@@ -15,6 +15,7 @@ struct Frame {
     State st;
     int classicSlot;
     int additionalEnabled;
+    int literalBounceTraces;  // NRB_OPT_LITERAL_BOUNCE_TRACES
 };
 
 // Per-launch hook.  NRB_DEBUG=1 in the environment: synchronise + report after every launch.

@@ -387,6 +387,7 @@ __global__ void __launch_bounds__(kQueueThreads, kBounceCtasPerSm) k_bounce_begi
     float carried = 0.0f, tAny = 1e30f, tFwd = 1e30f, tBwd = 1e30f, baseOffset = 0.0f;
     MultiTrace tr;
     tr.ref = kTraceDone;
+    const bool literal = f.literalBounceTraces != 0;
     bool more = true;  // warp-uniform: the cursor has not run past the queue
     const int warpsTotal = gridDim.x * (kQueueThreads / 32);
     const int cap = max(1, min(32, (n + warpsTotal - 1) / warpsTotal));  // lanes a warp keeps busy
@@ -398,16 +399,27 @@ __global__ void __launch_bounds__(kQueueThreads, kBounceCtasPerSm) k_bounce_begi
             float entryT = 1e30f;
             if (stage != 0 && tr.done()) {
                 int next;  // 2 = inner ANY, 3 = re-entry, 5 = write
+                // Traces whose outcome is decided are not run (they still count as traced): the FORWARD re-entry
+                // trace starts beyond the BACKWARD exit of a ray on which the fused trace found no front face at
+                // all - its candidates are a subset of that trace's, so it finds nothing either; and the inner-shell
+                // trace only matters where it is nearer than the outer-shell hit.  NRB_OPT_LITERAL_BOUNCE_TRACES
+                // runs them all, as the reference does.
+                const bool wouldReenter = !(tr.best1 < 1e30f) && tr.best2 < 1e30f;  // valid in stage 1; stage 2 uses tFwd / tBwd
                 if (stage == 1) {
                     tAny = tr.best0; tFwd = tr.best1; tBwd = tr.best2;
                     nTrace += (carried > 0.0f ? 1u : 0u) + 1u + (tFwd >= 1e30f ? 1u : 0u);
-                    const int after = tFwd < 1e30f ? 5 : (tBwd < 1e30f ? 3 : 5);
+                    const int after = tFwd < 1e30f ? 5 : (tBwd < 1e30f ? (literal ? 3 : 5) : 5);
                     next = carried > 0.0f ? 2 : after;
+                    if (!literal) {
+                        if (next == 2 && !(tAny < 1e30f)) { next = after; ++nTrace; }  // nothing to be nearer than
+                        if (next == 5 && wouldReenter) ++nTrace;
+                    }
                     entryT = tFwd;
                     alive = true;
                 } else if (stage == 2) {
                     const float ht = tr.best0;
-                    const int after = tFwd < 1e30f ? 5 : (tBwd < 1e30f ? 3 : 5);
+                    const int after = tFwd < 1e30f ? 5 : (tBwd < 1e30f ? (literal ? 3 : 5) : 5);
+                    if (!literal && !(tFwd < 1e30f) && tBwd < 1e30f && !(ht < 1e30f && tAny < 1e30f && ht < tAny)) ++nTrace;
                     if (ht < 1e30f && tAny < 1e30f && ht < tAny) { next = 5; alive = false; }
                     else { next = after; alive = true; entryT = tFwd; }
                 } else {
@@ -416,7 +428,7 @@ __global__ void __launch_bounds__(kQueueThreads, kBounceCtasPerSm) k_bounce_begi
                     entryT = tr.best1;
                 }
                 if (next == 2) {
-                    tr.begin(tInner, 1, org, wi);
+                    tr.begin(tInner, 1, org, wi, literal ? 1e30f : tAny);
                     ++nTrace;
                     stage = 2;
                 } else if (next == 3) {

@@ -419,9 +419,10 @@ struct MultiTrace {
     __device__ __forceinline__ void relimit() {
         limit = fmaxf(fmaxf((want & 1) ? best0 : -1e30f, (want & 2) ? best1 : -1e30f), (want & 4) ? best2 : -1e30f);
     }
-    __device__ __forceinline__ void begin(const TraceTarget& m, int wanted, V3 org, V3 dir) {
-        best0 = best1 = best2 = 1e30f;
-        limit = 1e30f;
+    // tMax: only hits nearer than tMax are looked for (best stays tMax when there is none)
+    __device__ __forceinline__ void begin(const TraceTarget& m, int wanted, V3 org, V3 dir, float tMax = 1e30f) {
+        best0 = best1 = best2 = tMax;
+        limit = tMax;
         ref = kTraceDone;
         sp = 0;
         cur = -1;
@@ -429,7 +430,7 @@ struct MultiTrace {
         d = dir;
         const V3 inv = v3(1.0f / dir.x, 1.0f / dir.y, 1.0f / dir.z);
         float tn;
-        if (!slab_base(org, inv, m.bmin.x, m.bmin.y, m.bmin.z, m.bmax.x, m.bmax.y, m.bmax.z, tn) || tn > 1e30f) return;
+        if (!slab_base(org, inv, m.bmin.x, m.bmin.y, m.bmin.z, m.bmax.x, m.bmax.y, m.bmax.z, tn) || tn > tMax) return;
         rp = ray_pack(org, inv);
         nodes = m.nodes;
         tris = m.tris;

@@ -302,6 +302,10 @@ class RendererNeural:
         """Joint bilateral filter of the accumulated frame (reference src/denoiser.cuh) on the way to devicePixels()."""
         self._opt(K.OPT_DENOISE, int(v))
 
+    def set_literal_bounce_traces(self, v: bool):
+        """Parity hook: run every trace of the reference's bounce entry, also those whose outcome is decided."""
+        self._opt(K.OPT_LITERAL_BOUNCE_TRACES, int(v))
+
     def stages(self):
         """-> {kernel name: (total ms, launches)} accumulated since reset_stages()."""
         out, i = {}, 0

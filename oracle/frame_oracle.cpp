@@ -1274,7 +1274,7 @@ int orc_set_option(orc_renderer* r, int opt, int v) {
         case NRB_OPT_USE_CONSTANT_NEURAL_COLOR: r->useConstantNeuralColor = v != 0; break;
         case NRB_OPT_USE_DIRECT_ENV_COLOR: r->useDirectEnvColor = v != 0; break;
         case NRB_OPT_DENOISE: r->denoise = v != 0; break;
-        case NRB_OPT_CAPTURE: case NRB_OPT_USE_HARDWARE_RT: break;
+        case NRB_OPT_CAPTURE: case NRB_OPT_USE_HARDWARE_RT: case NRB_OPT_LITERAL_BOUNCE_TRACES: break;
         default: return fail(NRB_ERR_INVALID, "unknown option");
     }
     return 0;

@@ -172,6 +172,29 @@ def test_segment_tail_graph_matches_fixed_loop(oracle_lib):
     assert psnr8(frames[0], orc.read_pixels()) > 28.0, psnr8(frames[0], orc.read_pixels())
 
 
+@pytest.mark.parametrize("kind,delta", [("ico", 0.12), ("blobs", 0.3)])
+def test_decided_bounce_traces_are_skipped_without_changing_the_frame(oracle_lib, kind, delta):
+    """The bounce entry does not run traces whose outcome is decided (inner-shell trace beyond the outer-shell hit,
+    re-entry trace on a ray without any front face): same frame, radiance and counters as the literal sequence
+    (NRB_OPT_LITERAL_BOUNCE_TRACES), on a convex-ish shell and on two separate blobs whose rays do re-enter."""
+    scene = nrb.scenes.make_scene(kind, 4, additional=True, shell_delta=delta)
+    prod, _, eye = make_pair(scene, oracle_lib, 192, 128, spp=2, bounces=3, neural=True, weights=_weights())
+    prod.set_tail_graph(0)  # fixed loop: bit-reproducible network arithmetic
+    out = []
+    for literal in (True, False, True):
+        prod.set_literal_bounce_traces(literal)
+        prod.reset_samples()
+        prod.render(eye)
+        out.append((prod.read_pixels().copy(), prod.read_buffer("path_radiance").copy(), prod.counters()))
+    prod.set_literal_bounce_traces(False)
+    assert np.array_equal(out[0][0], out[2][0])  # the literal run is reproducible
+    assert np.array_equal(out[0][0], out[1][0])
+    assert np.array_equal(out[0][1], out[1][1])
+    for key in ("neural_queries", "path_vertices", "ray_segments"):
+        assert out[0][2][key] == out[1][2][key], (key, out[0][2][key], out[1][2][key])
+    assert out[0][2]["path_vertices"] > 1000
+
+
 def test_tiles_reassemble_full_frame(oracle_lib):
     """Multi-GPU partition (row bands, global RNG streams): the union of ranks' rows is the 1-GPU image bit for bit."""
     scene = nrb.scenes.make_scene("ico", 3)
