@@ -121,7 +121,8 @@ __device__ __forceinline__ void seg_exits_body(const Frame& f, int qin, bool dyn
     const int n = f.st.counts[qin];
     const int D = fp.inputDims;
     const int total = gridDim.x * blockDim.x;
-    dynamic = dynamic && n > (total >> 5) * 4;  // short queues: one ray per warp (queue_start)
+    // short queues: one ray per warp (queue_start); up to half a ray per lane: the (ray, trace) couples below
+    dynamic = dynamic && n > (total >> 5) * 4 && 2 * n > total;
     if (!dynamic && 2 * n <= total) {
         // sparse: one (ray, trace) task per lane, the couples of a queue spread over all warps
         const int warps = total >> 5, lane = threadIdx.x & 31;
