@@ -221,12 +221,17 @@ __device__ __forceinline__ void encode_tasks(const NetDev& net, const LevelInfo&
                                              float* stageBase) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int P = net.nPoints, D = net.inputDims, L = net.nLevels;
-    // the next tile of this level nobody has taken yet (warp-uniform), -1 when the level is finished
-    auto claim = [&]() {
+    // Tasks (tile * 4 + 32-row group) of this level are claimed from its cursor, a whole tile at a time in long
+    // launches and one group at a time in short ones, where the four groups of a tile should go to four warps.
+    const int nTasks = tiles * 4;
+    const int K = nTasks >= 8 * (static_cast<int>(gridDim.x) * (static_cast<int>(blockDim.x) >> 5) / L) ? 4 : 1;
+    int endTask = 0;
+    auto claim = [&]() {  // warp-uniform; -1 when the level is finished
         int t = 0;
-        if (lane == 0) t = atomicAdd(cursor, 1);
+        if (lane == 0) t = atomicAdd(cursor, K);
         t = __shfl_sync(0xffffffffu, t, 0);
-        return t < tiles ? t : -1;
+        endTask = t + K < nTasks ? t + K : nTasks;
+        return t < nTasks ? t : -1;
     };
     const int PF = P * F, PLF = PF * L, shN = net.shDegree * net.shDegree;
     const uint32_t tileBytes = static_cast<uint32_t>(ek) * kTileM * 2;
@@ -254,18 +259,15 @@ __device__ __forceinline__ void encode_tasks(const NetDev& net, const LevelInfo&
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
-    int tile = claim(), g = 0, it = 0;
-    if (tile >= 0) fetch(tile, 0, 0);
-    for (; tile >= 0; ++it) {
-        const int curTile = tile, curG = g;
-        // the task after this one: the next 32-row group of the tile, then the next tile of the level
-        if (++g == 4) {
-            g = 0;
-            tile = claim();
-        }
+    int task = claim(), it = 0;
+    if (task >= 0) fetch(task >> 2, task & 3, 0);
+    for (; task >= 0; ++it) {
+        const int curTile = task >> 2, curG = task & 3;
+        // the task after this one: the next of the claim, then a new claim
+        if (++task >= endTask) task = claim();
         const int slot = it & 1;
-        if (tile >= 0) {
-            fetch(tile, g, slot ^ 1);
+        if (task >= 0) {
+            fetch(task >> 2, task & 3, slot ^ 1);
             asm volatile("cp.async.wait_group 1;" ::: "memory");
         } else {
             asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -346,7 +348,7 @@ __global__ void __launch_bounds__(kEncThreads, 1)
     if (rowEnd <= rowBase) return;
     const int tiles = (rowEnd - rowBase + kTileM - 1) / kTileM;
     const int L = net.nLevels;
-    int* cursors = net.encCursor;  // [L] next unclaimed tile per level; zero at launch, reset by k_query_mlp
+    int* cursors = net.encCursor;  // [L] next unclaimed task per level; zero at launch, reset by k_query_mlp
     // (a static __shared__ variable would push the 227 KB dynamic allocation over the per-block limit)
     int& sNext = *reinterpret_cast<int*>(smem + smemBytes + (blockDim.x >> 5) * 2u * 32u * net.inputDims * 4u);
     int staged = -1;
@@ -378,7 +380,7 @@ __global__ void __launch_bounds__(kEncThreads, 1)
         // The levels do not cost the same (coarse levels gather a few shared cells, fine ones 24 random entries
         // per query): a CTA whose level is finished restages the table of the level furthest behind.
         if (threadIdx.x == 0) {
-            int best = -1, bestAt = tiles;
+            int best = -1, bestAt = tiles * 4;  // the cursors count tasks
             for (int l = 0; l < L; ++l) {
                 const int at = *reinterpret_cast<volatile int*>(cursors + l);
                 if (at < bestAt) { bestAt = at; best = l; }
