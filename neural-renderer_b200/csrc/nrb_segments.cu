@@ -371,7 +371,8 @@ __global__ void __launch_bounds__(kQueueThreads, 8) k_bounce_sample(const __grid
     }
 }
 
-// Ten resident CTAs per SM (48 registers) measured best: 8 / 10 / 12 / 16 -> 0.808 / 0.791 / 0.800 / 0.921 ms.
+// Ten resident CTAs per SM (48 registers) measured best: 8 / 10 / 12 / 16 -> 0.808 / 0.791 / 0.800 / 0.921 ms (v7);
+// 10 / 12 -> 0.543 / 0.572 ms with the decided traces skipped (v16).
 constexpr int kBounceCtasPerSm = 10;
 __global__ void __launch_bounds__(kQueueThreads, kBounceCtasPerSm) k_bounce_begin(const __grid_constant__ Frame f, int bounce, int qin,
                                                                 int qray) {
