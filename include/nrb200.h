@@ -219,7 +219,11 @@ typedef enum nrb_option {
                                          at the outer-shell distance it is compared with (and is skipped when there is
                                          none), and the FORWARD re-entry trace from beyond the BACKWARD exit is skipped
                                          when the first FORWARD trace found no front face along the WHOLE ray: its
-                                         candidates are a subset of that trace's. */
+                                         candidates are a subset of that trace's.  Also the segment exits: the outer-shell
+                                         BACKWARD trace of a ray that hits the inner shell stops at that hit (an exit
+                                         beyond it is only ever compared with it); the literal setting traces to the
+                                         end and so keeps the reference's exitT = 1e-8 fallback for rays that leak
+                                         through the outer shell (src/cuda_renderer_neural.cu:899-905). */
 } nrb_option;
 int nrb_set_option(nrb_renderer* r, int option, int value);
 int nrb_get_option(const nrb_renderer* r, int option);

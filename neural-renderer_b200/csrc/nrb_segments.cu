@@ -75,14 +75,27 @@ __device__ __forceinline__ void seg_exit_one(const Frame& f, int e, float* dst, 
         dir = f4v(f.st.segD[e]);
     }
     const V3 shifted = entry + dir * kSegEps;
-    // outer shell BACKWARD, then inner shell ANY: passes through ONE inlined copy of the traversal loop
+    // inner shell ANY, then outer shell BACKWARD: passes through ONE inlined copy of the traversal loop (k = 1 inner,
+    // k = 0 outer).  With both in this lane the outer trace only looks as far as the inner hit: the exit distance is
+    // used as a number only when the ray leaves the shell before it reaches the inner shell, otherwise only as
+    // "beyond the inner hit" (stored as 1e30).  What this cannot tell apart is a ray with an inner hit and NO back
+    // face of the outer shell at all - a leak through an edge of a closed shell - for which the reference falls back
+    // to exitT = 1e-8 (:899-905); NRB_OPT_LITERAL_BOUNCE_TRACES traces to the end, as the reference does.
     float tOuter = 1e30f, tInner = 1e30f;
-    const int k0 = pass < 0 ? 0 : pass, k1 = !valid ? -1 : (pass < 0 ? 1 : pass);
+    bool beyond = false;
+    const int k0 = !valid ? 2 : (pass < 0 ? 1 : pass), k1 = pass < 0 ? 0 : pass;
 #pragma unroll 1
-    for (int k = k0; k <= k1; ++k) {
+    for (int k = k0; k >= k1 && k < 2; --k) {
         const MeshDev& m = f.mesh[k == 0 ? NRB_SLOT_OUTER : NRB_SLOT_INNER];
-        const Hit h = trace_dyn_inline(target_of(m), k == 0 ? TRACE_BACKWARD : TRACE_ANY, shifted, dir);
-        if (k == 0) tOuter = h.t; else tInner = h.t;
+        float tMax = 1e30f;
+        if (k == 0 && pass < 0 && tInner < 1e30f && !f.literalBounceTraces) tMax = __uint_as_float(__float_as_uint(tInner) + 1u);
+        const Hit h = trace_dyn_inline(target_of(m), k == 0 ? TRACE_BACKWARD : TRACE_ANY, shifted, dir, tMax);
+        if (k == 0) {
+            beyond = tMax < 1e30f && !(h.t < tMax);
+            tOuter = beyond ? 1e30f : h.t;
+        } else {
+            tInner = h.t;
+        }
     }
     if (pass >= 0) {
         const float mine = pass == 0 ? tOuter : tInner;
@@ -90,7 +103,7 @@ __device__ __forceinline__ void seg_exit_one(const Frame& f, int e, float* dst, 
         if (pass == 0) tInner = other; else tOuter = other;
         if (!valid || pass != 0) return;  // the even lane of a couple writes
     }
-    const float exitT = tOuter < 1e30f ? tOuter : kSegEps;
+    const float exitT = tOuter < 1e30f ? tOuter : (beyond ? 1e30f : kSegEps);
     const bool hitInner = tInner < 1e30f;
     const float innerT = hitInner ? tInner : 1e30f;
     const bool innerFirst = hitInner && (innerT < exitT);

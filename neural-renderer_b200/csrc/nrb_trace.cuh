@@ -202,8 +202,9 @@ __device__ __forceinline__ TraceTarget pick_target(bool first, const TraceTarget
 constexpr int kTraceDone = static_cast<int>(0x80000000u);  // not a leaf ref: first < 2^26 (checked at upload)
 constexpr int kTracePop = static_cast<int>(0x80000001u);   // MultiTrace: the lane must pop its stack next
 
-__device__ __forceinline__ Hit trace_dyn_inline(const TraceTarget& m, int mode, V3 o, V3 d) {
-    Hit best{1e30f, 0.0f, 0.0f, 0u};
+// tMax: only hits nearer than tMax are looked for; best.t stays tMax when there is none.
+__device__ __forceinline__ Hit trace_dyn_inline(const TraceTarget& m, int mode, V3 o, V3 d, float tMax = 1e30f) {
+    Hit best{tMax, 0.0f, 0.0f, 0u};
     if (m.numTriangles <= 0) return best;
     const V3 inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
     float tn;
