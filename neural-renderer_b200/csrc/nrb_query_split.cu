@@ -379,13 +379,11 @@ __global__ void __launch_bounds__(kEncThreads, 1)
         __syncthreads();  // every warp has found this level's cursor past the end
         // The levels do not cost the same (coarse levels gather a few shared cells, fine ones 24 random entries
         // per query): a CTA whose level is finished restages the table of the level furthest behind.
-        if (threadIdx.x == 0) {
-            int best = -1, bestAt = tiles * 4;  // the cursors count tasks
-            for (int l = 0; l < L; ++l) {
-                const int at = *reinterpret_cast<volatile int*>(cursors + l);
-                if (at < bestAt) { bestAt = at; best = l; }
-            }
-            sNext = best;
+        if (threadIdx.x < 32) {  // one load per lane (L <= 16): the cursors arrive together, not one L2 round trip each
+            const int at = static_cast<int>(threadIdx.x) < L ? *reinterpret_cast<volatile int*>(cursors + threadIdx.x) : tiles * 4;
+            unsigned key = at < tiles * 4 ? static_cast<unsigned>(at) * 32u + threadIdx.x : 0xffffffffu;  // the cursors count tasks
+            key = __reduce_min_sync(0xffffffffu, key);
+            if (threadIdx.x == 0) sNext = key == 0xffffffffu ? -1 : static_cast<int>(key & 31u);
         }
         __syncthreads();
         level = sNext;
