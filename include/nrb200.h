@@ -5,7 +5,7 @@
  * (reference src/cuda_renderer_neural.h:84-124) fed by Scene/Mesh objects
  * (src/scene.h:44-71, src/mesh.h:45-78).  Every entry point below cites the reference
  * member it replaces; the source-compatible C++ class that forwards to these calls lives
- * in neural-renderer_b200/cpp/ (see INTEGRATION.md).
+ * in include/nrb200_renderer.hpp.
  *
  * Conventions: plain pointers and sizes only, no C++/torch types.  Every function that can
  * fail returns 0 on success and a negative nrb_status otherwise; nrb_last_error() returns a

@@ -37,6 +37,39 @@
 #define NRB_ENV_STRENGTH(env) ((env).strength())
 #endif
 
+// Per-kernel GPU timing, as in the reference (src/cuda_renderer_neural.h:17-66): only with -DPROFILE_KERNELS.
+// Same enumerators, names and struct; the values come from nrb_get_timings (NRB_OPT_PROFILE event pairs), with this
+// library's fused kernels attributed to the bucket of their dominant part (csrc/nrb_api.cu:timing_bucket).
+#ifdef PROFILE_KERNELS
+enum KernelId {
+    KID_primaryTrace, KID_bounceTrace, KID_shellTrace, KID_neuralForward, KID_additionalMeshPrimary,
+    KID_selectClosestPrimary, KID_initPathState, KID_sampleBounce, KID_earlyTermination, KID_additionalMeshBounce,
+    KID_selectClosestBounce, KID_integrateBounce, KID_finalize, KID_COUNT
+};
+static_assert(KID_COUNT == NRB_TIMING_BUCKETS, "KernelId buckets");
+
+struct KernelTimings {
+    double ms[KID_COUNT] = {};
+    int rayCount = 0;             // width * height * samplesPerPixel
+    uint64_t neuralRayCalls = 0;  // sum of active-ray counts across all neural forward passes
+
+    static const char* name(int kid) {
+        static const char* kNames[KID_COUNT] = {
+            "GT primary intersect", "GT bounce intersect", "Shell intersection", "Neural forward pass",
+            "Additional mesh (primary)", "Select closest (primary)", "Init path state", "Sample bounce dirs",
+            "Bounce early term.", "Additional mesh (bounce)", "Select closest (bounce)", "Integrate bounce",
+            "Finalize / lambert",
+        };
+        return (kid >= 0 && kid < KID_COUNT) ? kNames[kid] : "?";
+    }
+    double totalMs() const {
+        double t = 0.0;
+        for (int i = 0; i < KID_COUNT; ++i) t += ms[i];
+        return t;
+    }
+};
+#endif  // PROFILE_KERNELS
+
 class RendererNeural final {
  public:
     explicit RendererNeural(Scene& scene, const NeuralNetworkConfig* nnConfig = nullptr) : scene_(&scene) {
@@ -46,6 +79,9 @@ class RendererNeural final {
             cfg.base_resolution = nnConfig->base_resolution;
         }
         check(nrb_create(&cfg, -1, &r_), "nrb_create");
+#ifdef PROFILE_KERNELS
+        nrb_set_option(r_, NRB_OPT_PROFILE, 1);
+#endif
     }
     ~RendererNeural() { nrb_destroy(r_); }
     RendererNeural(const RendererNeural&) = delete;
@@ -99,9 +135,22 @@ class RendererNeural final {
     int width() const { return nrb_width(r_); }
     int height() const { return nrb_height(r_); }
 
-    // The scene is read again on the next render() (the reference uses per-mesh dirty flags,
-    // src/mesh.cu:91-222; callers that edit a mesh in place call this).
-    void markSceneDirty() { sceneUploaded_ = false; }
+#ifdef PROFILE_KERNELS
+    // The reference fills lastFrameTimings_ at the end of render() after a device synchronise (:2738-2751); here the
+    // events are read on demand.
+    const KernelTimings& lastFrameTimings() const {
+        uint64_t calls = 0;
+        check(nrb_get_timings(r_, lastFrameTimings_.ms, &lastFrameTimings_.rayCount, &calls), "nrb_get_timings");
+        lastFrameTimings_.neuralRayCalls = calls;
+        return lastFrameTimings_;
+    }
+#endif
+
+    // The reference re-uploads a mesh when one of its private dirty flags is set (src/mesh.cu:91-222).  The flags are
+    // not readable from outside, so a slot is uploaded again when what can be observed of it changed - triangle,
+    // vertex and node counts or the address of a host array (a reload, clear(), or rebuilt BVH moves them) - and
+    // callers that edit vertex data in place call markSceneDirty().
+    void markSceneDirty() { sceneUploaded_ = false; for (auto& s : slotSeen_) s = SlotSeen{}; }
     nrb_renderer* handle() const { return r_; }
 
  private:
@@ -112,12 +161,32 @@ class RendererNeural final {
         }
     }
 
+    struct SlotSeen {
+        const void* vertices = nullptr;
+        const void* indices = nullptr;
+        int triangles = -1, numVertices = -1, nodes = -1, materials = -1, textures = -1;
+        bool operator==(const SlotSeen& o) const {
+            return vertices == o.vertices && indices == o.indices && triangles == o.triangles && numVertices == o.numVertices &&
+                   nodes == o.nodes && materials == o.materials && textures == o.textures;
+        }
+    };
+    static SlotSeen observe(const Mesh& m) {
+        SlotSeen s;
+        s.vertices = m.vertices_.data(); s.indices = m.indices_.data();
+        s.triangles = m.numTriangles(); s.numVertices = m.numVertices(); s.nodes = m.nodeCount();
+        s.materials = static_cast<int>(m.materials_.size()); s.textures = m.textureCount();
+        return s;
+    }
+
     void uploadMesh(int slot, Mesh& mesh) {
+        if (mesh.numTriangles() > 0 && !mesh.hasBvh()) mesh.buildBvh();  // CPU SAH build of the reference; defines primitive ids
+        const SlotSeen now = observe(mesh);
+        if (sceneUploaded_ && now == slotSeen_[slot]) return;
+        slotSeen_[slot] = now;
         if (mesh.numTriangles() == 0) {
             check(nrb_update_mesh(r_, slot, nullptr), "nrb_update_mesh");
             return;
         }
-        if (!mesh.hasBvh()) mesh.buildBvh();  // CPU SAH build of the reference; defines primitive ids
         const auto& nodes = NRB_MESH_BVH_NODES(mesh);
         static_assert(sizeof(BvhNode) == sizeof(nrb_bvh_node), "BvhNode layout");
         static_assert(sizeof(Material) == sizeof(nrb_material), "Material layout");
@@ -154,11 +223,11 @@ class RendererNeural final {
         // global material can be edited between frames by the callers (evaluate.cu:181-209)
         check(nrb_set_global_material(r_, reinterpret_cast<const nrb_material*>(&scene_->globalMaterial())),
               "nrb_set_global_material");
-        if (sceneUploaded_) return;
         uploadMesh(NRB_MESH_ORIGINAL, scene_->originalMesh());
         uploadMesh(NRB_MESH_INNER_SHELL, scene_->innerShell());
         uploadMesh(NRB_MESH_OUTER_SHELL, scene_->outerShell());
         uploadMesh(NRB_MESH_ADDITIONAL, scene_->additionalMesh());
+        if (sceneUploaded_) return;
         EnvironmentMap& env = scene_->environment();
         if (env.isValid()) {
             check(nrb_update_env(r_, &NRB_ENV_PIXELS(env)[0].x, NRB_ENV_WIDTH(env), NRB_ENV_HEIGHT(env), NRB_ENV_STRENGTH(env)),
@@ -172,6 +241,10 @@ class RendererNeural final {
     Scene* scene_ = nullptr;
     nrb_renderer* r_ = nullptr;
     bool sceneUploaded_ = false;
+    SlotSeen slotSeen_[NRB_MESH_SLOT_COUNT];
+#ifdef PROFILE_KERNELS
+    mutable KernelTimings lastFrameTimings_;
+#endif
     bool useNeuralQuery_ = false, useHardwareRT_ = false, swapParamOrder_ = true;
     int samplesPerPixel_ = 1, bounceCount_ = 0, classicMeshIndex_ = 0;
     float envmapRotation_ = 0.0f;

@@ -7,6 +7,7 @@
 // before nrb_render returns (callers issue a plain cudaMemcpy from devicePixels() next,
 // src/evaluate.cu:266).  There is no CPU fallback anywhere in this file: every entry point that
 // needs a device fails with NRB_ERR_CUDA when none is usable.
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -83,12 +84,14 @@ struct MeshSlot {
     MeshDev view{};
     float boundsMin[3] = {0, 0, 0}, boundsMax[3] = {0, 0, 0};
     int depth = 0;
+    bool closed = false;  // closed, consistently oriented surface (computed for the outer shell only)
     void clear() {
         nodes.release(); tris.release(); vertices.release(); normals.release(); texcoords.release();
         indices.release(); materials.release(); materialMap.release(); materialIds.release(); textures.release();
         texPixels.clear();
         view = MeshDev{};
         depth = 0;
+        closed = false;
     }
 };
 
@@ -97,7 +100,7 @@ struct MeshSlot {
 struct nrb_renderer {
     int device = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t evStart = nullptr, evStop = nullptr, evJoin = nullptr;
+    cudaEvent_t evStart = nullptr, evStop = nullptr, evJoin = nullptr, evJoinIn = nullptr;
     // nrb_read_pixels_async: frame -> staging copy on `stream`, staging -> host on `copyStream`
     cudaStream_t copyStream = nullptr;
     cudaEvent_t evStaged = nullptr, evCopied = nullptr;
@@ -165,6 +168,8 @@ struct nrb_renderer {
     bool profPending = false;
     std::map<std::string, std::pair<double, uint64_t>> stages;  // name -> (total ms, launches)
     std::vector<std::string> stageOrder;
+    double lastBuckets[NRB_TIMING_BUCKETS] = {0};  // the last profiled frame in the reference's KernelId buckets
+    bool lastBucketsValid = false;
 };
 
 namespace {
@@ -237,6 +242,33 @@ int configure_network(nrb_renderer* r, const nrb_nn_config* c) {
     return NRB_OK;
 }
 
+// Is the mesh a closed, consistently oriented surface?  Vertices are welded by exact position; every directed edge
+// must occur once and its reverse once.  A ray that starts inside such a shell always has a back face ahead of it,
+// which is what lets k_seg_exits stop the outer-shell exit trace at the inner-shell hit; for any other
+// outer shell the exit trace runs to the end, exactly as the reference's does.
+bool closed_surface(const float* vertices, int nv, const uint32_t* indices, int nt) {
+    if (nt < 4) return false;
+    std::vector<uint32_t> order(nv), canon(nv);
+    for (int i = 0; i < nv; ++i) order[i] = static_cast<uint32_t>(i);
+    auto key = [&](uint32_t i) { return vertices + 3 * static_cast<size_t>(i); };
+    std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return std::memcmp(key(a), key(b), 12) < 0; });
+    for (int i = 0; i < nv; ++i)
+        canon[order[i]] = (i > 0 && std::memcmp(key(order[i]), key(order[i - 1]), 12) == 0) ? canon[order[i - 1]] : order[i];
+    std::vector<uint64_t> edges;
+    edges.reserve(3 * static_cast<size_t>(nt));
+    for (int t = 0; t < nt; ++t) {
+        const uint32_t v[3] = {canon[indices[3 * t]], canon[indices[3 * t + 1]], canon[indices[3 * t + 2]]};
+        if (v[0] == v[1] || v[1] == v[2] || v[2] == v[0]) return false;
+        for (int k = 0; k < 3; ++k) edges.push_back((static_cast<uint64_t>(v[k]) << 32) | v[(k + 1) % 3]);
+    }
+    std::sort(edges.begin(), edges.end());
+    for (size_t i = 1; i < edges.size(); ++i)
+        if (edges[i] == edges[i - 1]) return false;
+    for (uint64_t e : edges)
+        if (!std::binary_search(edges.begin(), edges.end(), (e << 32) | (e >> 32))) return false;
+    return true;
+}
+
 // ---- BVH re-layout ------------------------------------------------------------------------------
 int relayout_mesh(nrb_renderer* r, MeshSlot& m, const nrb_mesh_desc* d) {
     const int nn = d->num_nodes, nt = d->num_triangles;
@@ -259,11 +291,11 @@ int relayout_mesh(nrb_renderer* r, MeshSlot& m, const nrb_mesh_desc* d) {
     }
 
     auto check_leaf = [&](const nrb_bvh_node& n) {
-        return n.count >= 1 && n.count <= (1 << kLeafCountBits) && n.first >= 0 && n.first + n.count <= nt &&
-               n.first < (1 << (31 - kLeafCountBits));
+        return n.count >= 1 && n.first >= 0 && n.first + n.count <= nt && n.first + n.count <= (1 << (31 - kLeafCountBits));
     };
     std::vector<NodePair> pairs;
     MeshDev& v = m.view;
+    int extraDepth = 0;
     // intersectAabb pads every box by 1e-10 before the slab test (src/mesh_traversal.cuh:67-69); the
     // padded boxes are stored so the kernels skip 12 additions per node pair (same fp32 operations)
     const float kPad = 1e-10f;
@@ -273,10 +305,35 @@ int relayout_mesh(nrb_renderer* r, MeshSlot& m, const nrb_mesh_desc* d) {
         v.rootMin[k] = lo(src[0].bounds_min[k]);
         v.rootMax[k] = hi(src[0].bounds_max[k]);
     }
+    // A leaf reference holds at most 32 triangles.  The reference accepts any leaf size (src/mesh_traversal.cuh:155-185):
+    // a larger leaf becomes a chain of node pairs whose children all carry the LEAF'S box - the first 32 triangles on
+    // the left, the rest on the right.  Equal entry distances visit left first, so the triangles are still tested in
+    // ascending order; the only difference is that the box is compared with the current best hit again between blocks
+    // (a block is skipped only when the box lies entirely beyond a hit already found, which no triangle inside it
+    // could beat).
+    auto emit_leaf = [&](const nrb_bvh_node& n) -> int {
+        const int kMax = 1 << kLeafCountBits;
+        if (n.count <= kMax) return leaf_ref(n.first, n.count);
+        const float4 xy = make_float4(lo(n.bounds_min[0]), lo(n.bounds_min[1]), hi(n.bounds_max[0]), hi(n.bounds_max[1]));
+        const float2 z = make_float2(lo(n.bounds_min[2]), hi(n.bounds_max[2]));
+        const int head = static_cast<int>(pairs.size());
+        int chain = 0;
+        for (int first = n.first, left = n.count; left > kMax; first += kMax, left -= kMax, ++chain) {
+            const int rest = left - kMax;
+            NodePair p;
+            p.a = xy; p.b = xy; p.c = make_float4(z.x, z.y, z.x, z.y);
+            const int self = static_cast<int>(pairs.size());
+            const int rightRef = rest <= kMax ? leaf_ref(first + kMax, rest) : self + 1;
+            p.d = make_int4(leaf_ref(first, kMax), rightRef, kMax, rest <= kMax ? rest : 0);
+            pairs.push_back(p);
+        }
+        extraDepth = std::max(extraDepth, chain);
+        return head;
+    };
     int maxDepth = 1;
     if (src[0].is_leaf) {
         if (!check_leaf(src[0])) return fail(NRB_ERR_INVALID, "bad root leaf");
-        v.rootRef = leaf_ref(src[0].first, src[0].count);
+        v.rootRef = emit_leaf(src[0]);
     } else {
         // DFS pre-order numbering of inner nodes keeps a subtree's pairs adjacent in memory
         struct Item { int node, pair, depth; };
@@ -297,8 +354,8 @@ int relayout_mesh(nrb_renderer* r, MeshSlot& m, const nrb_mesh_desc* d) {
                 if (c <= 0 || c >= nn || seen[c]) return fail(NRB_ERR_INVALID, "bad child index in BVH");
                 seen[c] = 1;
                 if (src[c].is_leaf) {
-                    if (!check_leaf(src[c])) return fail(NRB_ERR_INVALID, "leaf range out of bounds (or > 32 triangles)");
-                    refs[k] = leaf_ref(src[c].first, src[c].count);
+                    if (!check_leaf(src[c])) return fail(NRB_ERR_INVALID, "leaf range out of bounds");
+                    refs[k] = emit_leaf(src[c]);
                 } else {
                     refs[k] = static_cast<int>(pairs.size());
                     pairs.emplace_back();
@@ -313,10 +370,11 @@ int relayout_mesh(nrb_renderer* r, MeshSlot& m, const nrb_mesh_desc* d) {
             p.a = make_float4(lo(L.bounds_min[0]), lo(L.bounds_min[1]), hi(L.bounds_max[0]), hi(L.bounds_max[1]));
             p.b = make_float4(lo(R.bounds_min[0]), lo(R.bounds_min[1]), hi(R.bounds_max[0]), hi(R.bounds_max[1]));
             p.c = make_float4(lo(L.bounds_min[2]), hi(L.bounds_max[2]), lo(R.bounds_min[2]), hi(R.bounds_max[2]));
-            p.d = make_int4(refs[0], refs[1], L.is_leaf ? L.count : 0, R.is_leaf ? R.count : 0);
+            p.d = make_int4(refs[0], refs[1], refs[0] < 0 ? L.count : 0, refs[1] < 0 ? R.count : 0);
         }
         v.rootRef = 0;
     }
+    maxDepth += extraDepth;
     if (maxDepth >= kTraceStack) return fail(NRB_ERR_INVALID, "BVH deeper than the traversal stack (64)");
     m.depth = maxDepth;
     NRB_CUDA(m.nodes.upload(pairs.data(), pairs.size() * sizeof(NodePair), r->stream));
@@ -360,9 +418,17 @@ int nrb_create(const nrb_nn_config* cfg, int device, nrb_renderer** out) {
     if (rc != NRB_OK) { delete r; return rc; }
     if (cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreate(&r->evStart) != cudaSuccess || cudaEventCreate(&r->evStop) != cudaSuccess ||
-        cudaEventCreateWithFlags(&r->evJoin, cudaEventDisableTiming) != cudaSuccess) {
+        cudaEventCreateWithFlags(&r->evJoin, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&r->evJoinIn, cudaEventDisableTiming) != cudaSuccess) {
         delete r;
         return fail(NRB_ERR_CUDA, "stream/event creation failed");
+    }
+    // function attributes are per device: opt every > 48 KB kernel in on THIS device (renderers may live on several GPUs)
+    init_frame_kernels();
+    init_query_kernels();
+    if (cudaGetLastError() != cudaSuccess) {
+        nrb_destroy(r);
+        return fail(NRB_ERR_CUDA, "kernel attribute setup failed");
     }
     // Material::defaultMaterial(), src/material.h:86-106
     MaterialDev& g = r->globalMaterial;
@@ -371,6 +437,13 @@ int nrb_create(const nrb_nn_config* cfg, int device, nrb_renderer** out) {
     g.clearcoat_gloss.value = 1.0f;
     g.emission_scale = 1.0f;
     g.ior = 1.5f;
+    {
+        // the reference zero-fills its parameter block at construction and renders with it until a checkpoint is
+        // loaded (:1691-1697, neuralReady needs only the network and an outer shell, :2258): same here
+        std::vector<uint16_t> zeros(r->gridParams + r->mlpParams, 0);
+        rc = nrb_load_weights(r, zeros.data(), zeros.size() * 2, 1);
+        if (rc != NRB_OK) { nrb_destroy(r); return rc; }
+    }
     *out = r;
     return NRB_OK;
 }
@@ -382,6 +455,7 @@ void nrb_destroy(nrb_renderer* r) {
     if (r->evStart) cudaEventDestroy(r->evStart);
     if (r->evStop) cudaEventDestroy(r->evStop);
     if (r->evJoin) cudaEventDestroy(r->evJoin);
+    if (r->evJoinIn) cudaEventDestroy(r->evJoinIn);
     if (r->gather.remotePixels) cudaIpcCloseMemHandle(r->gather.remotePixels);
     if (r->gather.remoteSync) cudaIpcCloseMemHandle(r->gather.remoteSync);
     if (r->copyStream) { cudaStreamSynchronize(r->copyStream); cudaStreamDestroy(r->copyStream); }
@@ -445,6 +519,7 @@ int nrb_update_mesh(nrb_renderer* r, int slot, const nrb_mesh_desc* d) {
     v.hasMeshMaterials = d->has_mesh_materials;
     std::memcpy(m.boundsMin, d->bounds_min, 12);
     std::memcpy(m.boundsMax, d->bounds_max, 12);
+    if (slot == NRB_MESH_OUTER_SHELL) m.closed = closed_surface(d->vertices, d->num_vertices, d->indices, d->num_triangles);
     return NRB_OK;
 }
 
@@ -550,7 +625,7 @@ int nrb_set_option(nrb_renderer* r, int option, int value) {
         case NRB_OPT_USE_DIRECT_ENV_COLOR: r->useDirectEnvColor = value != 0; break;
         case NRB_OPT_CAPTURE: r->capture = value; break;
         case NRB_OPT_PROFILE: r->profile = value; break;
-        case NRB_OPT_QUERY_KERNEL: set_query_kernel(value); break;
+        case NRB_OPT_QUERY_KERNEL: r->net.kernelChoice = value; break;
         case NRB_OPT_TAIL_GRAPH: r->tailMode = value < 0 ? 0 : (value > 2 ? 2 : value); break;
         case NRB_OPT_DENOISE: r->denoise = value != 0; break;
         case NRB_OPT_LITERAL_BOUNCE_TRACES: r->literalBounceTraces = value != 0; break;
@@ -572,7 +647,7 @@ int nrb_get_option(const nrb_renderer* r, int option) {
         case NRB_OPT_USE_DIRECT_ENV_COLOR: return r->useDirectEnvColor;
         case NRB_OPT_CAPTURE: return r->capture;
         case NRB_OPT_PROFILE: return r->profile;
-        case NRB_OPT_QUERY_KERNEL: return query_kernel();
+        case NRB_OPT_QUERY_KERNEL: return r->net.kernelChoice;
         case NRB_OPT_TAIL_GRAPH: return r->tailMode;
         case NRB_OPT_DENOISE: return r->denoise ? 1 : 0;
         case NRB_OPT_LITERAL_BOUNCE_TRACES: return r->literalBounceTraces ? 1 : 0;
@@ -697,15 +772,32 @@ int ensure_xt(nrb_renderer* r, size_t rows) {
     return NRB_OK;
 }
 
+// The reference's KernelId bucket (src/cuda_renderer_neural.h:17-34) a kernel of this library reports into.  Stages
+// are fused across the reference's buckets, so a kernel goes to the bucket of its dominant part (named in the list).
+int timing_bucket(const std::string& k) {
+    if (k == "k_gt_primary") return 0;                                   // KID_primaryTrace (+ init path state)
+    if (k == "k_gt_bounce") return 1;                                    // KID_bounceTrace (+ sample, integrate)
+    if (k == "k_bounce_begin") return 8;                                 // KID_earlyTermination (+ the shell entry of bounce rays)
+    if (k.rfind("k_query_", 0) == 0 || k.rfind("k_neural_query", 0) == 0) return 3;  // KID_neuralForward
+    if (k == "k_primary_finish") return 4;                               // KID_additionalMeshPrimary (+ select closest, init path state)
+    if (k == "k_bounce_sample") return 7;                                // KID_sampleBounce
+    if (k == "k_bounce_finish") return 11;                               // KID_integrateBounce (+ additional mesh, select closest)
+    if (k == "k_finalize" || k == "k_lambert" || k == "k_denoise" || k.rfind("k_gather", 0) == 0) return 12;  // KID_finalize
+    return 2;                                                            // KID_shellTrace: entry, exits, apply, segment tail
+}
+
 // Turn the event marks of the last profiled frame into per-kernel totals.
 int drain_profiler(nrb_renderer* r) {
     if (!r->profPending) return NRB_OK;
     r->profPending = false;
     NRB_CUDA(cudaStreamSynchronize(r->stream));
+    for (double& b : r->lastBuckets) b = 0.0;
+    r->lastBucketsValid = r->prof.marks > 0;
     for (int i = 0; i < r->prof.marks; ++i) {
         float ms = 0.0f;
         if (cudaEventElapsedTime(&ms, r->prof.ev[i], r->prof.ev[i + 1]) != cudaSuccess) continue;
         const std::string key(r->prof.name[i]);
+        r->lastBuckets[timing_bucket(key)] += ms;
         auto it = r->stages.find(key);
         if (it == r->stages.end()) {
             r->stageOrder.push_back(key);
@@ -817,6 +909,7 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     f.classicSlot = classicSlot;
     f.additionalEnabled = r->useAdditionalMesh ? 1 : 0;
     f.literalBounceTraces = r->literalBounceTraces ? 1 : 0;
+    f.literalSegExits = (r->literalBounceTraces || !outer.closed) ? 1 : 0;
 
     cudaStream_t s = r->stream;
     if (r->profile) {
@@ -827,6 +920,10 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
             r->prof.ready = true;
         }
     }
+    // symmetric join: whatever the caller enqueued on the legacy default stream since the last frame (an async copy or
+    // a kernel reading devicePixels()) finishes before this frame may overwrite the buffers
+    NRB_CUDA(cudaEventRecord(r->evJoinIn, cudaStreamLegacy));
+    NRB_CUDA(cudaStreamWaitEvent(s, r->evJoinIn, 0));
     NRB_CUDA(cudaMemsetAsync(r->st.stats, 0, 16 * sizeof(unsigned long long), s));
     NRB_CUDA(cudaEventRecord(r->evStart, s));
     if (r->gather.role == 1) {
@@ -842,7 +939,7 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     }
     const bool neural = r->useNeuralQuery && r->weightsLoaded && outer.view.numTriangles > 0;  // (:2258-2260)
     int launches;
-    if (neural) launches = launch_neural_frame(f, r->net, r->lambertView, s, (r->tailMode == 1 && getenv("NRB_DEBUG") == nullptr) ? &r->segTail : nullptr, r->tailMode == 2);
+    if (neural) launches = launch_neural_frame(f, r->net, r->lambertView, s, (r->tailMode == 1 && !debug_sync_enabled()) ? &r->segTail : nullptr, r->tailMode == 2);
     else launches = launch_gt_frame(f, r->lambertView, s);
     if (r->denoise && !r->lambertView) launches += launch_denoise(f, s);
     if (r->gather.role != 0) {
@@ -984,7 +1081,13 @@ int nrb_get_timings(nrb_renderer* r, double ms[NRB_TIMING_BUCKETS], int* ray_cou
     if (rc != NRB_OK) return rc;
     for (int i = 0; i < NRB_TIMING_BUCKETS; ++i) ms[i] = 0.0;
     float t = 0.0f;
-    if (r->lastLaunches > 0 && cudaEventElapsedTime(&t, r->evStart, r->evStop) == cudaSuccess) {
+    if (r->profile || r->profPending) {
+        // NRB_OPT_PROFILE (the reference's -DPROFILE_KERNELS): per-kernel events of the last frame, by bucket
+        rc = drain_profiler(r);
+        if (rc != NRB_OK) return rc;
+        if (r->lastBucketsValid)
+            for (int i = 0; i < NRB_TIMING_BUCKETS; ++i) ms[i] = r->lastBuckets[i];
+    } else if (r->lastLaunches > 0 && cudaEventElapsedTime(&t, r->evStart, r->evStop) == cudaSuccess) {
         // stages are fused across the reference's buckets; the frame total is attributed to the
         // traversal bucket of the active mode (KID_primaryTrace / KID_shellTrace)
         ms[r->lastNeural ? 2 : 0] = t;

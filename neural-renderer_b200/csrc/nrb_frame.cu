@@ -227,8 +227,24 @@ static thread_local StageProfiler* g_profiler = nullptr;
 void set_stage_profiler(StageProfiler* p) { g_profiler = p; }
 StageProfiler* get_stage_profiler() { return g_profiler; }
 
-void debug_check(const char* what, cudaStream_t s) {
+bool debug_sync_enabled() {
     static const bool on = getenv("NRB_DEBUG") != nullptr;
+    return on;
+}
+
+int sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        cached[dev] = (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0) ? n : 148;
+    }
+    return cached[dev];
+}
+
+void debug_check(const char* what, cudaStream_t s) {
+    const bool on = debug_sync_enabled();
     if (g_profiler && g_profiler->marks < StageProfiler::kMaxMarks) {
         StageProfiler& p = *g_profiler;
         p.name[p.marks] = what;

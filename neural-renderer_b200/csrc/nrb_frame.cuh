@@ -16,6 +16,9 @@ struct Frame {
     int classicSlot;
     int additionalEnabled;
     int literalBounceTraces;  // NRB_OPT_LITERAL_BOUNCE_TRACES
+    int literalSegExits;      // the option above, or an outer shell that is not a closed surface: k_seg_exits traces the
+                              // outer shell to the end, so the reference's exitT = 1e-8 fallback for rays that find no
+                              // back face (:899-905) is reproduced exactly
 };
 
 // Per-launch hook.  NRB_DEBUG=1 in the environment: synchronise + report after every launch.
@@ -32,6 +35,16 @@ struct StageProfiler {
 void set_stage_profiler(StageProfiler* p);
 StageProfiler* get_stage_profiler();
 void debug_check(const char* what, cudaStream_t s);
+bool debug_sync_enabled();   // NRB_DEBUG in the environment, read once per process
+// Multiprocessor count of the CURRENT device (cached per device ordinal): persistent grids are sized from it.
+int sm_count();
+// Per-device opt-in to > 48 KB of dynamic shared memory for every kernel that needs it.  Function attributes
+// belong to the device/context, so nrb_create runs these once for each device it is given (a process may hold
+// renderers on several GPUs).
+void init_frame_kernels();      // nrb_segments.cu
+void init_query_kernels();      // nrb_neural.cu (+ nrb_neural_tc.cu, nrb_query_split.cu)
+void init_query_tc_kernels();
+void init_query_split_kernels();
 #define NRB_LAUNCHED(what, s) ::nrb::debug_check(what, s)
 
 // Launchers implemented in nrb_frame.cu / nrb_neural.cu (all enqueue on `s`, none synchronises).

@@ -139,9 +139,9 @@ __device__ __forceinline__ uchar4 to_srgb8(V3 c) {
 }
 
 inline int queue_grid(int maxElems) {
-    // persistent-style grid: enough CTAs to fill 148 SMs x 8 resident CTAs, no more than needed
+    // persistent-style grid: enough CTAs to fill every SM with 8 resident CTAs, no more than needed
     const int need = (maxElems + kQueueThreads - 1) / kQueueThreads;
-    const int cap = 148 * 8;
+    const int cap = sm_count() * 8;
     return need < 1 ? 1 : (need < cap ? need : cap);
 }
 

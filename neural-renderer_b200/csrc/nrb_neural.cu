@@ -75,47 +75,40 @@ size_t neural_query_smem(const NetDev& net, int* warpsOut) {
     return p.warps > 0 ? p.total : 0;
 }
 
-static int g_queryKernel = 0;
-void set_query_kernel(int which) { g_queryKernel = which; }
-int query_kernel() { return g_queryKernel; }
+void init_query_kernels() {
+    cudaFuncSetAttribute(k_neural_query<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(k_neural_query<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    init_query_tc_kernels();
+    init_query_split_kernels();
+}
 
 int launch_neural_query(const NetDev& net, const float* in, size_t n, const int* dCount, __half* out,
                         cudaStream_t s) {
     if (n == 0) return 0;
-    const int which = g_queryKernel & 0xff;
+    const int which = net.kernelChoice & 0xff;
     // automatic choice: the split pays when a lane's encoder task carries enough gathers to amortise its
     // fixed cost (measured: 3 points x F4 -> 2.7x the fused kernel; 1 point x F2 -> 0.5x)
     const bool splitPays = net.nPoints * net.nFeatures >= 8;
     if ((which == 3 || (which == 0 && splitPays)) && net.xtRows > 0 && net.packedW && split_query_supported(net)) {
         NetDev tmp = net;
-        tmp.debug = g_queryKernel >> 8;
+        tmp.debug = net.kernelChoice >> 8;
         return launch_split_query(tmp, in, n, dCount, out, s);
     }
     if (which != 1 && neural_query_tc_supported(net)) {
         NetDev tmp = net;
-        tmp.debug = g_queryKernel >> 8;
+        tmp.debug = net.kernelChoice >> 8;
         return launch_neural_query_tc(tmp, in, n, dCount, out, s);
     }
     const SmemPlan p = plan_smem(net);
     if (p.warps <= 0) return -1;
     const int tiles = static_cast<int>((n + kRows - 1) / kRows);
     int grid = (tiles + p.warps - 1) / p.warps;
-    if (grid > 148) grid = 148;  // one persistent CTA per SM (weights stay resident in its smem)
+    if (grid > sm_count()) grid = sm_count();  // one persistent CTA per SM (weights stay resident in its smem)
     const int threads = p.warps * 32;
     if (net.width == 128) {
-        static bool attr = false;
-        if (!attr) {
-            cudaFuncSetAttribute(k_neural_query<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-            attr = true;
-        }
         k_neural_query<128><<<grid, threads, p.total, s>>>(net, in, static_cast<int>(n), dCount, out, p.ek, p.warps);
         NRB_LAUNCHED("k_neural_query", s);
     } else {
-        static bool attr = false;
-        if (!attr) {
-            cudaFuncSetAttribute(k_neural_query<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-            attr = true;
-        }
         k_neural_query<64><<<grid, threads, p.total, s>>>(net, in, static_cast<int>(n), dCount, out, p.ek, p.warps);
         NRB_LAUNCHED("k_neural_query", s);
     }

@@ -19,6 +19,8 @@ struct NetDev {
     int nPoints, nLevels, nFeatures, shDegree, width, nHidden;
     int inputDims;        // 3*nPoints (+3 when shDegree > 0)
     int encDims;          // nPoints*nLevels*nFeatures + shDegree^2
+    int kernelChoice;     // NRB_OPT_QUERY_KERNEL of the owning renderer: low byte 0 auto, 1 mma.sync, 2 fused tcgen05, 3 split;
+                          // higher bits = the experiment flags below
     int debug;            // experiments only: bit 0 = skip the table loads, bit 1 = skip the MLP,
                           // bit 2 = split encoder gathers from global memory, bit 3 = 1024-row chunks
     // split query (nrb_query_split.cu): weights pre-packed as UMMA operands, encoded-row scratch
@@ -52,8 +54,6 @@ size_t split_packed_bytes(const NetDev& net);
 size_t split_xt_bytes(const NetDev& net, size_t rows);           // rows rounded up to 128 inside
 int split_prepack(const NetDev& net, void* packedW, cudaStream_t s);
 int launch_split_query(const NetDev& net, const float* in, size_t n, const int* dCount, __half* out, cudaStream_t s);
-void set_query_kernel(int which);
-int query_kernel();
 // Bytes of dynamic shared memory the query kernel needs for this network (0 = unsupported shape).
 size_t neural_query_smem(const NetDev& net, int* warpsOut);
 

@@ -339,25 +339,20 @@ bool neural_query_tc_supported(const NetDev& net) {
     return plan_tc(net).total <= 227u * 1024u;
 }
 
+void init_query_tc_kernels() {
+    cudaFuncSetAttribute(k_neural_query_tc<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(k_neural_query_tc<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+}
+
 int launch_neural_query_tc(const NetDev& net, const float* in, size_t n, const int* dCount, __half* out,
                            cudaStream_t s) {
     if (n == 0) return 0;
     const TcPlan p = plan_tc(net);
     const int tiles = static_cast<int>((n + kTileM - 1) / kTileM);
-    const int grid = tiles < 148 ? tiles : 148;  // one persistent CTA per SM
+    const int grid = tiles < sm_count() ? tiles : sm_count();  // one persistent CTA per SM
     if (net.width == 128) {
-        static bool attr = false;
-        if (!attr) {
-            cudaFuncSetAttribute(k_neural_query_tc<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-            attr = true;
-        }
         k_neural_query_tc<128><<<grid, kMlpThreads + kEncThreads, p.total, s>>>(net, in, static_cast<int>(n), dCount, out, p);
     } else {
-        static bool attr = false;
-        if (!attr) {
-            cudaFuncSetAttribute(k_neural_query_tc<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-            attr = true;
-        }
         k_neural_query_tc<64><<<grid, kMlpThreads + kEncThreads, p.total, s>>>(net, in, static_cast<int>(n), dCount, out, p);
     }
     NRB_LAUNCHED("k_neural_query_tc", s);

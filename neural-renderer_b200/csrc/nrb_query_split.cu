@@ -82,7 +82,7 @@ SplitPlan make_plan(const NetDev& net) {
         if (bytes + p.encRing + 16u <= kSmemMax && bytes > best) best = static_cast<uint32_t>(bytes);
     }
     p.encSmem = best;
-    p.slices = net.nLevels > 0 ? (148 / net.nLevels > 0 ? 148 / net.nLevels : 1) : 1;
+    p.slices = net.nLevels > 0 ? (sm_count() / net.nLevels > 0 ? sm_count() / net.nLevels : 1) : 1;
     return p;
 }
 
@@ -613,7 +613,7 @@ __global__ void __launch_bounds__(kMlpThreads, 1)
 bool split_query_supported(const NetDev& net) {
     if (net.width != 64 && net.width != 128) return false;
     if (net.nFeatures != 2 && net.nFeatures != 4) return false;
-    if (net.nHidden < 1 || net.shDegree > 4 || net.nLevels < 1 || net.nLevels > 148) return false;
+    if (net.nHidden < 1 || net.shDegree > 4 || net.nLevels < 1 || net.nLevels > kMaxLevels) return false;
     if (((net.nPoints * net.nLevels * net.nFeatures) & 7) != 0) return false;
     const SplitPlan p = make_plan(net);
     return p.mlpSmem <= kSmemMax && p.encSmem + p.encRing <= kSmemMax;
@@ -632,18 +632,18 @@ int split_prepack(const NetDev& net, void* packedW, cudaStream_t s) {
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
+void init_query_split_kernels() {
+    cudaFuncSetAttribute(k_query_encode<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax));
+    cudaFuncSetAttribute(k_query_encode<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax));
+    cudaFuncSetAttribute(k_query_mlp<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax));
+    cudaFuncSetAttribute(k_query_mlp<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax));
+}
+
 int launch_split_query(const NetDev& net, const float* in, size_t n, const int* dCount, __half* out, cudaStream_t s) {
     if (n == 0) return 0;
     if (!net.packedW || !net.xt || net.xtRows < kTileM || !net.encCursor) return -1;
     const SplitPlan p = make_plan(net);
-    static bool attr = false;
-    if (!attr) {
-        cudaFuncSetAttribute(k_query_encode<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax));
-        cudaFuncSetAttribute(k_query_encode<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax));
-        cudaFuncSetAttribute(k_query_mlp<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax));
-        cudaFuncSetAttribute(k_query_mlp<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemMax));
-        attr = true;
-    }
+    const int sms = sm_count();
     int chunkRows = static_cast<int>(net.xtRows / kTileM * kTileM);
     if ((net.debug & 8) && chunkRows > 1024) chunkRows = 1024;  // tests: exercise the chunk walk on small batches
     int launches = 0;
@@ -652,7 +652,7 @@ int launch_split_query(const NetDev& net, const float* in, size_t n, const int* 
         const int tiles = static_cast<int>((rows + kTileM - 1) / kTileM);
         // one CTA per SM, never more than four tiles' worth of CTAs per level
         const int want = net.nLevels * ((tiles + 3) / 4);
-        const int egrid = want < 148 ? want : 148;
+        const int egrid = want < sms ? want : sms;
         unsigned char* xt = static_cast<unsigned char*>(net.xt);
         if (net.nFeatures == 4)
             k_query_encode<4><<<egrid, kEncThreads, p.encSmem + p.encRing + 16u, s>>>(net, in, static_cast<int>(n), dCount, static_cast<int>(base),
@@ -661,7 +661,7 @@ int launch_split_query(const NetDev& net, const float* in, size_t n, const int* 
             k_query_encode<2><<<egrid, kEncThreads, p.encSmem + p.encRing + 16u, s>>>(net, in, static_cast<int>(n), dCount, static_cast<int>(base),
                                                                     chunkRows, xt, p.ek, p.encSmem);
         NRB_LAUNCHED("k_query_encode", s);
-        const int mgrid = tiles < 148 ? tiles : 148;
+        const int mgrid = tiles < sms ? tiles : sms;
         if (net.width == 128)
             k_query_mlp<128><<<mgrid, kMlpThreads, p.mlpSmem, s>>>(net, static_cast<int>(n), dCount, static_cast<int>(base), chunkRows,
                                                                   xt, out, p);

@@ -88,7 +88,7 @@ __device__ __forceinline__ void seg_exit_one(const Frame& f, int e, float* dst, 
     for (int k = k0; k >= k1 && k < 2; --k) {
         const MeshDev& m = f.mesh[k == 0 ? NRB_SLOT_OUTER : NRB_SLOT_INNER];
         float tMax = 1e30f;
-        if (k == 0 && pass < 0 && tInner < 1e30f && !f.literalBounceTraces) tMax = __uint_as_float(__float_as_uint(tInner) + 1u);
+        if (k == 0 && pass < 0 && tInner < 1e30f && !f.literalSegExits) tMax = __uint_as_float(__float_as_uint(tInner) + 1u);
         const Hit h = trace_dyn_inline(target_of(m), k == 0 ? TRACE_BACKWARD : TRACE_ANY, shifted, dir, tMax);
         if (k == 0) {
             beyond = tMax < 1e30f && !(h.t < tMax);
@@ -600,7 +600,7 @@ static int seg_iteration(const Frame& f, const NetDev& net, int recIdx, int qin,
     const int qout = qin == 2 ? 3 : 2;
     // iteration 0 of a pass finds queue 3 empty (frame start / k_bounce_sample); the fixed loop resets per iteration
     if (!first) cudaMemsetAsync(f.st.counts + qout, 0, sizeof(int), s);
-    k_seg_exits<<<grid, kQueueThreads, 0, s>>>(f, qin, qin == 2 && grid > 148 ? 1 : 0);  // iteration 0 of a pass
+    k_seg_exits<<<grid, kQueueThreads, 0, s>>>(f, qin, qin == 2 && grid > sm_count() ? 1 : 0);  // iteration 0 of a pass
     NRB_LAUNCHED("k_seg_exits", s);
     int launches = 1 + launch_neural_query(net, f.st.netIn, static_cast<size_t>(f.fp.nElems), f.st.counts + qin, f.st.netOut, s);
     k_seg_apply<<<grid, kQueueThreads, 0, s>>>(f, qin, qout, recIdx);
@@ -652,9 +652,9 @@ static bool build_tail(SegTail& t, const Frame& f, const NetDev& net, int recIdx
     cudaGraph_t body = cp.conditional.phGraph_out[0];
     if (cudaStreamBeginCaptureToGraph(t.capture, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed) != cudaSuccess) return false;
     const Frame* df = static_cast<const Frame*>(t.dFrame);
-    k_seg_exits_tail<<<148, kQueueThreads, 0, t.capture>>>(df, ctl);
+    k_seg_exits_tail<<<sm_count(), kQueueThreads, 0, t.capture>>>(df, ctl);
     const int q = launch_neural_query(net, f.st.netIn, static_cast<size_t>(f.fp.nElems), &ctl->curCount, f.st.netOut, t.capture);
-    k_seg_apply_tail<<<148, kQueueThreads, 0, t.capture>>>(df, ctl);
+    k_seg_apply_tail<<<sm_count(), kQueueThreads, 0, t.capture>>>(df, ctl);
     k_seg_tail_next<<<1, 1, 0, t.capture>>>(ctl, counts, h);
     cudaGraph_t done = nullptr;
     if (cudaStreamEndCapture(t.capture, &done) != cudaSuccess || q < 0) return false;
@@ -676,8 +676,6 @@ static bool prepare_tail(SegTail& t, const Frame& f, const NetDev& net, cudaStre
     put(&f.st.netOut, sizeof(void*));
     put(&f.st.counts, sizeof(void*));
     put(&f.fp.nElems, sizeof(int));
-    int kernelChoice = query_kernel();
-    put(&kernelChoice, sizeof(int));
     if (n > sizeof(key)) { t.failed = true; return false; }
     if (t.exec[0] && t.exec[1] && n == t.keyBytes && std::memcmp(key, t.key, n) == 0) return true;
     StageProfiler* prof = get_stage_profiler();  // no per-launch events inside a capture
@@ -791,18 +789,17 @@ static size_t seg_tail_smem(const NetDev& net, int* warpsOut, int* ekOut) {
     return wbytes + per * warps;
 }
 
+void init_frame_kernels() {
+    cudaFuncSetAttribute(k_seg_tail<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(k_seg_tail<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+}
+
 static bool launch_seg_tail(const Frame& f, const NetDev& net, int recIdx, cudaStream_t s) {
     int warps = 0, ek = 0;
     const size_t smem = seg_tail_smem(net, &warps, &ek);
     if (smem == 0) return false;
-    static bool attr = false;
-    if (!attr) {
-        cudaFuncSetAttribute(k_seg_tail<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        cudaFuncSetAttribute(k_seg_tail<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        attr = true;
-    }
-    if (net.width == 128) k_seg_tail<128><<<148, 512, smem, s>>>(f, net, recIdx, ek, warps);
-    else k_seg_tail<64><<<148, 512, smem, s>>>(f, net, recIdx, ek, warps);
+    if (net.width == 128) k_seg_tail<128><<<sm_count(), 512, smem, s>>>(f, net, recIdx, ek, warps);
+    else k_seg_tail<64><<<sm_count(), 512, smem, s>>>(f, net, recIdx, ek, warps);
     NRB_LAUNCHED("k_seg_tail", s);
     return true;
 }
@@ -820,7 +817,7 @@ static int run_segments(const Frame& f, const NetDev& net, int recIdx, cudaStrea
     }
     int qin = 3;
     for (int it = 1; it < kMaxSegIters; ++it) {
-        launches += seg_iteration(f, net, recIdx, qin, 148, s, false);
+        launches += seg_iteration(f, net, recIdx, qin, sm_count(), s, false);
         qin = qin == 2 ? 3 : 2;
     }
     return launches;
@@ -850,7 +847,8 @@ int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStr
         NRB_LAUNCHED("k_bounce_sample", s);
         {
             const int need = (fp.nElems + kQueueThreads - 1) / kQueueThreads;
-            const int g = need < 148 * kBounceCtasPerSm ? (need < 1 ? 1 : need) : 148 * kBounceCtasPerSm;
+            const int cap = sm_count() * kBounceCtasPerSm;
+            const int g = need < cap ? (need < 1 ? 1 : need) : cap;
             k_bounce_begin<<<g, kQueueThreads, 0, s>>>(f, b, 0, 1);
         }
         NRB_LAUNCHED("k_bounce_begin", s);

@@ -194,9 +194,26 @@ def checker_texture(size: int = 64, seed: int = 3):
     return np.clip(img * 255.0, 0, 255).astype(np.uint8)
 
 
+def param_textures(size: int = 32, seed: int = 5):
+    """Two seeded 3-channel 8-bit textures: [0] a channel-packed parameter map (G = roughness, B = metallic, the glTF
+    packing) and [1] a tangent-space normal map (mostly +z with a seeded tilt)."""
+    rng = np.random.RandomState(seed)
+    packed = np.zeros((size, size, 3), np.float32)
+    y, x = np.mgrid[0:size, 0:size]
+    packed[..., 0] = 1.0
+    packed[..., 1] = 0.15 + 0.7 * (((x // 4) + (y // 4)) % 2) + 0.05 * rng.standard_normal((size, size))
+    packed[..., 2] = 0.9 * ((x // 8) % 2) + 0.05 * rng.standard_normal((size, size))
+    tilt = 0.35 * rng.standard_normal((size, size, 2))
+    n = np.concatenate([tilt, np.ones((size, size, 1))], -1)
+    n /= np.linalg.norm(n, axis=-1, keepdims=True)
+    to8 = lambda a: np.clip(a * 255.0, 0, 255).astype(np.uint8)
+    return to8(packed), to8(0.5 * (n + 1.0))
+
+
 def make_scene(kind: str = "ico", subdivisions: int = 4, shells: bool = True, env: bool = True,
-               additional: bool = False, shell_delta: float = 0.12, textured: bool = False,
-               env_size=(512, 256), roughness: float = 0.5, metallic: float = 0.0, specular: float = 0.5):
+               additional: bool = False, shell_delta: float = 0.12, textured=False,
+               env_size=(512, 256), roughness: float = 0.5, metallic: float = 0.0, specular: float = 0.5,
+               material: dict = None, open_outer: float = 0.0):
     """Synthetic scene in the reference's Scene layout: a displaced icosphere (or the
     reference's UV sphere) as original mesh, +-shell_delta icosphere hulls as inner/outer shells, an
     optional ground quad as the additional mesh and a seeded equirect environment."""
@@ -225,12 +242,28 @@ def make_scene(kind: str = "ico", subdivisions: int = 4, shells: bool = True, en
         uv = np.concatenate([uv, uv]).astype(np.float32)
         idx = np.concatenate([idx, idx + np.uint32(nv)]).astype(np.uint32)
     extra = {}
+    mat_kw = dict(base_color=(0.8, 0.8, 0.8), roughness=roughness, metallic=metallic, specular=specular)
+    extras_direct = {}
+    if material:
+        mat_kw.update({k: v for k, v in material.items() if k not in ("ior", "specular_transmission")})
+        extras_direct = {k: v for k, v in material.items() if k in ("ior", "specular_transmission")}
     if textured:
-        m = K.Material.from_config(base_color=(0.8, 0.8, 0.8), roughness=roughness, metallic=metallic, specular=specular)
+        m = K.Material.from_config(**mat_kw)
         m.base_color.textured = 1
         m.base_color.texture_id = 0
+        textures = [(checker_texture(), False)]
+        nearest = False
+        if textured == "packed":
+            # everything resolveMaterial / computeHitData can read from textures (src/mesh_intersection.cuh:109-152,
+            # 168-238, 244-337): base colour, channel-packed roughness (G) / metallic (B), a normal map, nearest filtering
+            packed, nmap = param_textures()
+            textures += [(packed, False), (nmap, False)]
+            m.roughness.textured, m.roughness.texture_id, m.roughness.channel = 1, 1, 1
+            m.metallic.textured, m.metallic.texture_id, m.metallic.channel = 1, 1, 2
+            m.normal.textured, m.normal.texture_id = 1, 2
+            nearest = True
         extra = dict(materials=[m], material_map=np.array([0], np.uint32), material_ids=np.array([0], np.int32),
-                     textures=[(checker_texture(), False)], has_mesh_materials=True)
+                     textures=textures, has_mesh_materials=True, texture_nearest=nearest)
     scene = Scene(original_mesh=mesh_from(v, idx, normals=n, texcoords=uv, **extra))
     if shells:
         hv, hidx = icosphere(3)
@@ -241,14 +274,23 @@ def make_scene(kind: str = "ico", subdivisions: int = 4, shells: bool = True, en
             scene.outer_shell = mesh_from(two(1.0 + shell_delta), hidx2)
         else:
             scene.inner_shell = mesh_from((hv * np.float32(1.0 - shell_delta)).astype(np.float32), hidx)
+            if open_outer > 0.0:
+                # an OPEN outer shell: a cap on the side away from the default camera is removed, so camera rays through
+                # the middle enter the shell, reach the inner shell and have NO outer back face anywhere ahead - the
+                # exitT = 1e-8 fallback of traceSegmentExitsKernel (src/cuda_renderer_neural.cu:899-905)
+                c = hv[hidx].mean(1)
+                c /= np.linalg.norm(c, axis=1, keepdims=True)
+                d0 = np.array([2.0, 1.2, 2.0]) / np.linalg.norm([2.0, 1.2, 2.0])
+                hidx = hidx[(c @ d0) > -(1.0 - open_outer)]
             scene.outer_shell = mesh_from((hv * np.float32(1.0 + shell_delta)).astype(np.float32), hidx)
     if additional:
         gv, gidx = ground_quad()
         scene.additional_mesh = mesh_from(gv, gidx)
     if env:
         scene.env_pixels = sky_env(*env_size)
-    scene.global_material = K.Material.from_config(base_color=(0.8, 0.8, 0.8), roughness=roughness, metallic=metallic,
-                                                   specular=specular)
+    scene.global_material = K.Material.from_config(**mat_kw)
+    for k, v in extras_direct.items():
+        setattr(scene.global_material, k, v)
     return scene
 
 
