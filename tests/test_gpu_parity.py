@@ -145,6 +145,34 @@ def test_neural_frame_parity(oracle_lib, spp, bounces, additional):
     assert abs(ca["neural_queries"] - cb["neural_queries"]) <= 0.01 * cb["neural_queries"] + 2
 
 
+@pytest.mark.parametrize("neural", [False, True], ids=["gt", "neural"])
+def test_benchmarked_configuration_parity(oracle_lib, neural):
+    """The configuration bench.py times (BASELINE configs 2 and 3): 1920x1080, spp 1, 3 bounces, displaced icosphere of
+    327 680 triangles in its +-12 % shells, 2048x1024 environment, reference network - against the oracle on all host
+    cores (~10 s per frame).  Ground truth: primary hit buffers bit-exact, frame within one step of 255 on >= 99.99 % of
+    the pixels.  Neural: north_star's bars - mean FLIP <= 0.005 - and PSNR >= 45 dB."""
+    scene = nrb.scenes.make_scene("ico", 7, shells=True, env=True, env_size=(2048, 1024))
+    prod, orc, eye = make_pair(scene, oracle_lib, 1920, 1080, spp=1, bounces=3, neural=neural,
+                               weights=_weights() if neural else None)
+    prod.render(eye)
+    orc.render(eye)
+    ia, ib = prod.read_pixels(), orc.read_pixels()
+    d = np.abs(ia.astype(int) - ib.astype(int)).max(axis=2)
+    p, flip = psnr8(ia, ib), float(nrb.metrics.flip_ldr(ib, ia))
+    fa, fb = prod.read_buffer("hit_flags"), orc.read_buffer("hit_flags")
+    print(f"1080p {'neural' if neural else 'gt'}: psnr {p:.2f} dB, flip {flip:.5f}, within one step {np.mean(d <= 1):.6f}, "
+          f"hit-flag mismatch {np.mean(fa != fb):.2e}")
+    if neural:
+        assert np.mean(fa != fb) < 1e-3
+        assert p >= 45.0 and flip <= 0.005, (p, flip)
+        ca, cb = prod.counters(), orc.counters()
+        assert abs(ca["neural_queries"] - cb["neural_queries"]) <= 0.002 * cb["neural_queries"]
+    else:
+        for name in ("hit_flags", "hit_positions", "hit_normals", "hit_colors", "hit_material_params"):
+            assert np.array_equal(prod.read_buffer(name), orc.read_buffer(name)), name
+        assert p >= 60.0 and np.mean(d <= 1) >= 0.9999 and flip <= 0.001, (p, np.mean(d <= 1), flip)
+
+
 def test_segment_tail_graph_matches_fixed_loop(oracle_lib):
     """Two shell components in line with the camera: rays that pass the first one re-enter the shell, so
     iterations >= 1 of the segment loop carry rays.  The device-driven WHILE graph must give the

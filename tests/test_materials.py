@@ -3,9 +3,10 @@ the host when oracle/_ref is present): every Disney lobe (src/disney_brdf.cuh:88
 resolveMaterial / computeHitData (src/mesh_intersection.cuh:109-152, 168-238, 244-337), a leaking outer shell
 (src/cuda_renderer_neural.cu:899-905), oversized BVH leaves, renderers on two devices in one process.
 
-Bars: primary hit buffers bit-exact (ids decide them); the 8-bit frame within 1 step of 255 on >= 99.5 % of the pixels
-and >= 45 dB PSNR - bounce directions go through sinf / cosf / powf / logf, which differ by an ulp or two between
-CUDA and glibc, and a path whose bounce ray grazes an edge may resolve differently (observed: 48-70 dB).
+Bars: primary hit buffers bit-exact (ids decide them); the 8-bit frame within 1 step of 255 on >= 99.99 % of the pixels
+and >= 60 dB PSNR - bounce directions go through sinf / cosf / powf / logf, which differ by an ulp or two between
+CUDA and glibc, and a path whose bounce ray grazes an edge may resolve differently (observed on B200: seven of nine
+frames identical to the last bit, the other two 91 and 96 dB with no pixel off by more than one step).
 """
 import numpy as np
 import pytest
@@ -25,7 +26,7 @@ MATERIALS = {
 }
 
 
-def _frame_bars(prod, orc, eye, exact_hits=True, psnr_floor=45.0, step_frac=0.995):
+def _frame_bars(prod, orc, eye, exact_hits=True, psnr_floor=60.0, step_frac=0.9999):
     prod.render(eye)
     orc.render(eye)
     if exact_hits:
