@@ -44,3 +44,25 @@ def ref_build_bvh(vertices, indices):
     dll.ref_build_bvh(v.ctypes.data_as(C.c_void_p), C.c_int(len(v)), idx.ctypes.data_as(C.c_void_p),
                       C.c_int(len(idx)), nodes.ctypes.data_as(C.c_void_p), C.byref(n), bmin, bmax)
     return nodes[: n.value].copy(), idx, np.array(bmin, np.float32), np.array(bmax, np.float32)
+
+
+def ref_extbvh_trace(vertices, indices, origins, directions, threads=0, reps=1, tmin=0.0):
+    """ext/bvh's own CPU traversal (bvh::v2::Bvh::intersect + PrecomputedTri, the configuration of
+    ext/bvh/test/benchmark.cpp) -> dict(prim = source triangle id or 0xffffffff, t, uv, normal, build_ms, trace_ms, threads)."""
+    dll = C.CDLL(REFBVH_LIB)
+    v = np.ascontiguousarray(vertices, np.float32)
+    idx = np.ascontiguousarray(indices, np.uint32)
+    o = np.ascontiguousarray(origins, np.float32)
+    d = np.ascontiguousarray(directions, np.float32)
+    n = len(o)
+    prim, t = np.zeros(n, np.uint32), np.zeros(n, np.float32)
+    uv, nrm = np.zeros((n, 2), np.float32), np.zeros((n, 3), np.float32)
+    bms, tms, used = C.c_double(0), C.c_double(0), C.c_int(0)
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    dll.ref_extbvh_trace(vp(v), C.c_int(len(v)), vp(idx), C.c_int(len(idx)), vp(o), vp(d), C.c_size_t(n), C.c_int(threads),
+                         C.c_int(reps), C.c_float(tmin), vp(prim), vp(t), vp(uv), vp(nrm), C.byref(bms), C.byref(tms), C.byref(used))
+    return dict(prim=prim, t=t, uv=uv, normal=nrm, build_ms=bms.value, trace_ms=tms.value, threads=used.value)
+
+
+def have_refbvh():
+    return os.path.exists(REFBVH_LIB)

@@ -73,3 +73,17 @@ def peer_rank_main(conn, rank, world, width, height, frames, neural):
         r.close()
     except Exception as e:  # pragma: no cover
         conn.send(f"error: {e!r}")
+
+
+def primary_rays(width, height, radius=1.0):
+    """Pixel-centre pinhole rays of the default camera (generatePrimaryRay, src/mesh_traversal.cuh:40-55, without jitter)."""
+    eye, basis = nrb.scenes.default_camera(radius)
+    x, y = np.meshgrid(np.arange(width, dtype=np.float32), np.arange(height, dtype=np.float32))
+    u = (x + 0.5) / width * 2.0 - 1.0
+    v = (1.0 - (y + 0.5) / height) * 2.0 - 1.0
+    th = np.float32(np.tan(basis.fov_y * 0.5))
+    d = (basis.forward[None, None, :] + basis.right[None, None, :] * (u * (width / height) * th)[..., None]
+         + basis.up[None, None, :] * (v * th)[..., None])
+    d = (d / np.linalg.norm(d, axis=-1, keepdims=True)).astype(np.float32).reshape(-1, 3)
+    o = np.broadcast_to(np.asarray(eye, np.float32), d.shape).copy()
+    return o, d
