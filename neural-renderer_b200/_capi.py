@@ -146,7 +146,7 @@ class Lib:
             "build_bvh": ([vp, i, vp, i, vp, P(i), vp], i),
             "build_bvh_gpu": ([vp, i, vp, i, vp, P(i), vp, i, i, P(C.c_float)], i), "build_bvh_gpu_error": ([], C.c_char_p), "abi_version": ([], i),
             "get_stage": ([vp, i, P(C.c_char_p), P(C.c_double), P(C.c_uint64)], i), "reset_stages": ([vp], i),
-            "set_threads": ([vp, i], i), "set_row_range": ([vp, i, i], i), "backend": ([], C.c_char_p),
+            "set_threads": ([vp, i], i), "set_row_range": ([vp, i, i], i), "set_row_sample": ([vp, i, i, i], i), "backend": ([], C.c_char_p),
         }
         for name, (args, res) in table.items():
             if self.has(name):

@@ -179,9 +179,14 @@ def build_bvh_gpu(vertices, indices, max_leaf: int = 4, device: int = -1):
     return nodes[: n.value].copy(), idx, prim, ms.value
 
 
-def mesh_from(vertices, indices, normals=None, texcoords=None, gpu_bvh: bool = False, **kw):
+def mesh_from(vertices, indices, normals=None, texcoords=None, gpu_bvh: bool = False, builder=None, **kw):
+    """builder: (vertices, indices) -> (nodes, leaf-ordered indices, ...); default = the host SAH builder of libnrb200.
+    Callers that must not load libnrb200 (bench.py's reference arm) pass the reference's own Mesh::buildBvh."""
     from .renderer import MeshData
-    nodes, idx, _ = build_bvh_gpu(vertices, indices)[:3] if gpu_bvh else build_bvh(vertices, indices)
+    if builder is not None:
+        nodes, idx = builder(vertices, indices)[:2]
+    else:
+        nodes, idx, _ = build_bvh_gpu(vertices, indices)[:3] if gpu_bvh else build_bvh(vertices, indices)
     return MeshData(vertices=vertices, indices=idx, nodes=nodes, normals=normals, texcoords=texcoords, **kw)
 
 
@@ -213,7 +218,7 @@ def param_textures(size: int = 32, seed: int = 5):
 def make_scene(kind: str = "ico", subdivisions: int = 4, shells: bool = True, env: bool = True,
                additional: bool = False, shell_delta: float = 0.12, textured=False,
                env_size=(512, 256), roughness: float = 0.5, metallic: float = 0.0, specular: float = 0.5,
-               material: dict = None, open_outer: float = 0.0):
+               material: dict = None, open_outer: float = 0.0, builder=None):
     """Synthetic scene in the reference's Scene layout: a displaced icosphere (or the
     reference's UV sphere) as original mesh, +-shell_delta icosphere hulls as inner/outer shells, an
     optional ground quad as the additional mesh and a seeded equirect environment."""
@@ -264,16 +269,16 @@ def make_scene(kind: str = "ico", subdivisions: int = 4, shells: bool = True, en
             nearest = True
         extra = dict(materials=[m], material_map=np.array([0], np.uint32), material_ids=np.array([0], np.int32),
                      textures=textures, has_mesh_materials=True, texture_nearest=nearest)
-    scene = Scene(original_mesh=mesh_from(v, idx, normals=n, texcoords=uv, **extra))
+    scene = Scene(original_mesh=mesh_from(v, idx, normals=n, texcoords=uv, builder=builder, **extra))
     if shells:
         hv, hidx = icosphere(3)
         if blobs:
             two = lambda r: np.concatenate([hv * np.float32(0.3 * r) + d * np.float32(0.9), hv * np.float32(0.6 * r) - d * np.float32(0.6)]).astype(np.float32)
             hidx2 = np.concatenate([hidx, hidx + np.uint32(len(hv))]).astype(np.uint32)
-            scene.inner_shell = mesh_from(two(1.0 - shell_delta), hidx2)
-            scene.outer_shell = mesh_from(two(1.0 + shell_delta), hidx2)
+            scene.inner_shell = mesh_from(two(1.0 - shell_delta), hidx2, builder=builder)
+            scene.outer_shell = mesh_from(two(1.0 + shell_delta), hidx2, builder=builder)
         else:
-            scene.inner_shell = mesh_from((hv * np.float32(1.0 - shell_delta)).astype(np.float32), hidx)
+            scene.inner_shell = mesh_from((hv * np.float32(1.0 - shell_delta)).astype(np.float32), hidx, builder=builder)
             if open_outer > 0.0:
                 # an OPEN outer shell: a cap on the side away from the default camera is removed, so camera rays through
                 # the middle enter the shell, reach the inner shell and have NO outer back face anywhere ahead - the
@@ -282,10 +287,10 @@ def make_scene(kind: str = "ico", subdivisions: int = 4, shells: bool = True, en
                 c /= np.linalg.norm(c, axis=1, keepdims=True)
                 d0 = np.array([2.0, 1.2, 2.0]) / np.linalg.norm([2.0, 1.2, 2.0])
                 hidx = hidx[(c @ d0) > -(1.0 - open_outer)]
-            scene.outer_shell = mesh_from((hv * np.float32(1.0 + shell_delta)).astype(np.float32), hidx)
+            scene.outer_shell = mesh_from((hv * np.float32(1.0 + shell_delta)).astype(np.float32), hidx, builder=builder)
     if additional:
         gv, gidx = ground_quad()
-        scene.additional_mesh = mesh_from(gv, gidx)
+        scene.additional_mesh = mesh_from(gv, gidx, builder=builder)
     if env:
         scene.env_pixels = sky_env(*env_size)
     scene.global_material = K.Material.from_config(**mat_kw)

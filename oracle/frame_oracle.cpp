@@ -268,6 +268,8 @@ struct orc_renderer {
 
     // (oracle only) restrict every per-pixel loop to rows [rowBegin,rowEnd) for bounded timing.
     int rowBegin = 0, rowEnd = 1 << 30;
+    // (oracle only) of those rows, visit bands of rowBand rows, every rowStride-th band: a uniform sample of the frame
+    int rowBand = 1, rowStride = 1;
     Pool pool;
     uint64_t counters[4] = {0, 0, 0, 0};  // [1] ray segments traced, [2] neural queries, [3] path vertices
 
@@ -309,9 +311,19 @@ struct orc_renderer {
     template <class F>
     void forPixels(const RenderParams& p, F body) {
         int y0 = std::max(0, rowBegin), y1 = std::min(p.height, rowEnd);
-        pool.run(y1 - y0, [&](int a, int b) {
-            for (int y = y0 + a; y < y0 + b; ++y)
-                for (int x = 0; x < p.width; ++x) body(x, y);
+        if (rowStride <= 1) {
+            pool.run(y1 - y0, [&](int a, int b) {
+                for (int y = y0 + a; y < y0 + b; ++y)
+                    for (int x = 0; x < p.width; ++x) body(x, y);
+            });
+            return;
+        }
+        std::vector<int> rows;
+        for (int y = y0; y < y1; ++y)
+            if (((y - y0) / rowBand) % rowStride == 0) rows.push_back(y);
+        pool.run(static_cast<int>(rows.size()), [&](int a, int b) {
+            for (int k = a; k < b; ++k)
+                for (int x = 0; x < p.width; ++x) body(x, rows[k]);
         });
     }
     void traceNeuralSegmentsForRays(bool useCameraRays, const float* rayOrigins, const float* rayDirs,
@@ -378,7 +390,7 @@ void orc_renderer::traceNeuralSegmentsForRays(bool useCameraRays, const float* r
     if (outHitMaterialParams) std::fill(outHitMaterialParams, outHitMaterialParams + elementCount * 3, 0.0f);
     if (outHitDistances) std::fill(outHitDistances, outHitDistances + elementCount, 0.0f);
     // Rows outside [rowBegin,rowEnd) are never visited by the bounded-sample loops.
-    if (rowBegin > 0 || rowEnd < params.height) std::fill(rayActiveFlags.begin(), rayActiveFlags.end(), 0);
+    if (rowBegin > 0 || rowEnd < params.height || rowStride > 1) std::fill(rayActiveFlags.begin(), rayActiveFlags.end(), 0);
 
     float* entryPositions = currentEntryPos.data();
     float* entryT = outerExitT.data();  // the reference passes outerExitT_ as entryT (:1881)
@@ -1173,6 +1185,17 @@ int orc_set_row_range(orc_renderer* r, int y0, int y1) {
     r->rowBegin = y0;
     r->rowEnd = y1;
     return 0;
+}
+
+// Visit bands of `band` rows, every `stride`-th band of the row range; returns the number of rows a frame of the
+// given height then covers.
+int orc_set_row_sample(orc_renderer* r, int band, int stride, int height) {
+    r->rowBand = band < 1 ? 1 : band;
+    r->rowStride = stride < 1 ? 1 : stride;
+    int y0 = std::max(0, r->rowBegin), y1 = std::min(height, r->rowEnd), n = 0;
+    for (int y = y0; y < y1; ++y)
+        if (r->rowStride <= 1 || ((y - y0) / r->rowBand) % r->rowStride == 0) ++n;
+    return n;
 }
 
 int orc_update_mesh(orc_renderer* r, int slot, const nrb_mesh_desc* d) {
