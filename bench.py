@@ -380,13 +380,15 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(steps, body):
+    def timed(steps, body, finish=None):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.time()
         e0.record(torch.cuda.current_stream())
         for _ in range(steps):
             body()
+        if finish:
+            finish()  # e2e: the frame read-backs run on the renderer's copy stream; wait for the last of them
         e1.record(torch.cuda.current_stream())  # render() joins its stream into the legacy default stream
         barrier()
         ms = e0.elapsed_time(e1)
@@ -435,7 +437,7 @@ def main():
     counters = r.counters()
     for _ in range(2):
         step_e2e()
-    ms_e2e, _, _ = timed(a.steps, step_e2e)
+    ms_e2e, _, _ = timed(a.steps, step_e2e, finish=r.sync)
 
     # second pass with per-launch events -> per-kernel times
     r.set_profile(True)

@@ -244,7 +244,9 @@ int nrb_set_tile(nrb_renderer* r, int band_rows, int rank, int world);
 /* RendererNeural::render(const Vec3& camPos) (src/cuda_renderer_neural.cu:2085-2755).
  * Returns after the work has been enqueued and joined to the legacy default stream, so a
  * following cudaMemcpy from nrb_device_pixels() is ordered after the frame (the reference's
- * callers rely on this, evaluate.cu:266). */
+ * callers rely on this, evaluate.cu:266).  The join is symmetric: the frame also waits for whatever the
+ * caller enqueued on the legacy default stream before the call (an async copy or a kernel still reading the
+ * previous frame), so devicePixels() is never overwritten under a reader. */
 int nrb_render(nrb_renderer* r, const float cam_pos[3]);
 /* RendererNeural::devicePixels(): uchar4 RGBA, row-major, width*height (device pointer). */
 void* nrb_device_pixels(const nrb_renderer* r);
@@ -252,9 +254,9 @@ void* nrb_device_pixels(const nrb_renderer* r);
 int nrb_read_pixels(nrb_renderer* r, void* rgba, size_t bytes);
 /* (new) Non-blocking variant for callers that stream frames: returns once the copy is enqueued on
  * a second stream, so the transfer of this frame overlaps the kernels of the next nrb_render.
- * rgba should be pinned; it is valid after nrb_sync() (or once the legacy default stream, which
- * the copy is joined to like nrb_render, has drained).  One transfer in flight per renderer: a
- * second call waits on the device for the first. */
+ * rgba should be pinned; it is valid after nrb_sync() (the copy runs on the renderer's copy stream and is NOT joined
+ * to the legacy default stream, or the next frame - which orders itself behind that stream - would wait for the PCIe
+ * transfer).  One transfer in flight per renderer: a second call waits on the device for the first. */
 int nrb_read_pixels_async(nrb_renderer* r, void* rgba, size_t bytes);
 /* (new) Multi-GPU frame gather fused into the frame, over peer memory instead of a collective: the root
  * rank (one process per GPU) exports its frame buffer, the others attach and from then on their finalize

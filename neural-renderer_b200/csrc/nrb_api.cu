@@ -998,7 +998,9 @@ int nrb_read_pixels_async(nrb_renderer* r, void* rgba, size_t bytes) {
     NRB_CUDA(cudaStreamWaitEvent(r->copyStream, r->evStaged, 0));
     NRB_CUDA(cudaMemcpyAsync(rgba, r->pixelsStaged.p, bytes, cudaMemcpyDeviceToHost, r->copyStream));
     NRB_CUDA(cudaEventRecord(r->evCopied, r->copyStream));
-    NRB_CUDA(cudaStreamWaitEvent(cudaStreamLegacy, r->evCopied, 0));  // same join rule as nrb_render
+    // NOT joined into the legacy default stream: nrb_render orders itself behind that stream (the caller's reads of
+    // devicePixels()), and a transfer joined there would serialise the next frame behind this PCIe copy.  The copy
+    // reads the staging buffer, never the frame buffer, so the next frame is free to start; nrb_sync() waits for it.
     r->copyPending = true;
     return NRB_OK;
 }
