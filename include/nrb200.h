@@ -133,8 +133,11 @@ typedef enum nrb_trace_mode {
     NRB_TRACE_FORWARD_ONLY = 1,
     NRB_TRACE_BACKWARD_ONLY = 2,
     NRB_TRACE_ALL_MODES = 3,  /* (new, parity hook) one fused pass: out.t/u/v = ANY/FORWARD/BACKWARD distances */
-    NRB_TRACE_ALL_MODES_UNION = 4 /* (new, parity hook) the same through the bounce entry's resumable engine,
+    NRB_TRACE_ALL_MODES_UNION = 4, /* (new, parity hook) the same through the bounce entry's resumable engine,
                                      which prunes by the union of the live modes */
+    NRB_TRACE_DYN_ANY = 5,         /* (new, parity hooks) modes 0..2 through the run-time-mode traversal loop of the */
+    NRB_TRACE_DYN_FORWARD = 6,     /* segment stages (k_seg_exits, k_seg_apply), which skips subtrees whose normal    */
+    NRB_TRACE_DYN_BACKWARD = 7     /* cone rules the facing mode out: same {t,u,v,prim} as modes 0..2                  */
 } nrb_trace_mode;
 
 /* = PreliminaryHitInfo, reference src/hit_info.h:7-13.  t == 1e30f means no hit. */

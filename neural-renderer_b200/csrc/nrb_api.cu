@@ -270,7 +270,84 @@ bool closed_surface(const float* vertices, int nv, const uint32_t* indices, int 
 }
 
 // ---- BVH re-layout ------------------------------------------------------------------------------
-int relayout_mesh(nrb_renderer* r, MeshSlot& m, const nrb_mesh_desc* d) {
+// Normal cones of every node's subtree (nrb_scene.cuh: cone word).  Axis = the quantised mean normal of the subtree's
+// triangles, threshold from the EXACT minimum of axis . n over those triangles (double precision, the fp32 normals the
+// kernels' facing test uses), widened by the margins described below.  O(triangles x depth); shells only.
+std::vector<uint32_t> node_cones(const nrb_bvh_node* src, int nn, const std::vector<TriBlock>& tris) {
+    std::vector<uint32_t> cone(nn, kNoCone);
+    struct D3 { double x, y, z; };
+    std::vector<D3> sum(nn, D3{0, 0, 0});
+    auto normal = [&](int t, D3& n) {
+        n = D3{tris[t].p.w, tris[t].q.w, tris[t].r.w};
+        const double l = std::sqrt(n.x * n.x + n.y * n.y + n.z * n.z);
+        if (!(l > 0.5) || !std::isfinite(l)) return false;  // degenerate triangle: its normal is 0 or NaN, it can never be hit
+        n = D3{n.x / l, n.y / l, n.z / l};
+        return true;
+    };
+    // post-order over the tree (children have larger indices than their parent in every builder we accept? not
+    // guaranteed: use an explicit order)
+    std::vector<int> order;
+    order.reserve(nn);
+    {
+        std::vector<int> todo{0};
+        while (!todo.empty()) {
+            const int i = todo.back();
+            todo.pop_back();
+            order.push_back(i);
+            if (!src[i].is_leaf) { todo.push_back(src[i].left); todo.push_back(src[i].right); }
+        }
+    }
+    for (auto it = order.rbegin(); it != order.rend(); ++it) {
+        const int i = *it;
+        if (src[i].is_leaf) {
+            for (int t = src[i].first; t < src[i].first + src[i].count; ++t) {
+                D3 n;
+                if (normal(t, n)) { sum[i].x += n.x; sum[i].y += n.y; sum[i].z += n.z; }
+            }
+        } else {
+            const D3 &a = sum[src[i].left], &b = sum[src[i].right];
+            sum[i] = D3{a.x + b.x, a.y + b.y, a.z + b.z};
+        }
+    }
+    std::vector<int> stack;
+    for (int i = 0; i < nn; ++i) {
+        const D3 s = sum[i];
+        const double l = std::sqrt(s.x * s.x + s.y * s.y + s.z * s.z);
+        if (!(l > 1e-9)) continue;
+        const int qx = static_cast<int>(std::lround(s.x / l * 127.0)), qy = static_cast<int>(std::lround(s.y / l * 127.0)),
+                  qz = static_cast<int>(std::lround(s.z / l * 127.0));
+        const double ax = qx / 127.0, ay = qy / 127.0, az = qz / 127.0, al = std::sqrt(ax * ax + ay * ay + az * az);
+        if (!(al > 0.5)) continue;
+        double minDot = 1.0;
+        stack.assign(1, i);
+        while (!stack.empty()) {
+            const int k = stack.back();
+            stack.pop_back();
+            if (src[k].is_leaf) {
+                for (int t = src[k].first; t < src[k].first + src[k].count; ++t) {
+                    D3 n;
+                    if (normal(t, n)) minDot = std::min(minDot, (ax * n.x + ay * n.y + az * n.z) / al);
+                }
+            } else {
+                stack.push_back(src[k].left);
+                stack.push_back(src[k].right);
+            }
+        }
+        // every normal is within theta of the unit axis; n . d >= eps for all of them once axis . d >= sin(theta + asin eps).
+        // eps = 1e-5 keeps the sign of the kernels' fp32 facing dot (rounding ~ 4e-7); the kernel tests the UNnormalised
+        // quantised axis against s * |d|, so s carries |axis|, the fp32 error of that dot and of |d| (4e-6), is rounded
+        // up to the next 1/255 and given one more step.
+        const double theta = std::acos(std::max(-1.0, std::min(1.0, minDot))) + std::asin(1e-5);
+        if (!(theta < 1.5707)) continue;
+        const int sq = static_cast<int>(std::ceil((std::sin(theta) * al + 4e-6) * 255.0)) + 1;
+        if (sq >= 255) continue;
+        cone[i] = (static_cast<uint32_t>(qx) & 0xffu) | ((static_cast<uint32_t>(qy) & 0xffu) << 8) |
+                  ((static_cast<uint32_t>(qz) & 0xffu) << 16) | (static_cast<uint32_t>(sq) << 24);
+    }
+    return cone;
+}
+
+int relayout_mesh(nrb_renderer* r, MeshSlot& m, const nrb_mesh_desc* d, bool withCones) {
     const int nn = d->num_nodes, nt = d->num_triangles;
     const nrb_bvh_node* src = d->nodes;
     if (!src || nn <= 0 || !d->vertices || !d->indices) return fail(NRB_ERR_INVALID, "mesh without nodes/vertices/indices");
@@ -296,6 +373,27 @@ int relayout_mesh(nrb_renderer* r, MeshSlot& m, const nrb_mesh_desc* d) {
     std::vector<NodePair> pairs;
     MeshDev& v = m.view;
     int extraDepth = 0;
+    // node indices are validated below before they are followed; the cone pass needs a well-formed tree, so it runs
+    // only after a first structural check
+    std::vector<uint32_t> cones;
+    if (withCones) {
+        bool ok = true;
+        std::vector<char> seenNode(nn, 0);
+        std::vector<int> todo{0};
+        seenNode[0] = 1;
+        while (ok && !todo.empty()) {
+            const int i = todo.back();
+            todo.pop_back();
+            if (src[i].is_leaf) { ok = check_leaf(src[i]); continue; }
+            for (int c : {src[i].left, src[i].right}) {
+                if (c <= 0 || c >= nn || seenNode[c]) { ok = false; break; }
+                seenNode[c] = 1;
+                todo.push_back(c);
+            }
+        }
+        if (ok) cones = node_cones(src, nn, tris);
+    }
+    auto cone_of = [&](int node) { return cones.empty() ? kNoCone : cones[node]; };
     // intersectAabb pads every box by 1e-10 before the slab test (src/mesh_traversal.cuh:67-69); the
     // padded boxes are stored so the kernels skip 12 additions per node pair (same fp32 operations)
     const float kPad = 1e-10f;
@@ -324,7 +422,7 @@ int relayout_mesh(nrb_renderer* r, MeshSlot& m, const nrb_mesh_desc* d) {
             p.a = xy; p.b = xy; p.c = make_float4(z.x, z.y, z.x, z.y);
             const int self = static_cast<int>(pairs.size());
             const int rightRef = rest <= kMax ? leaf_ref(first + kMax, rest) : self + 1;
-            p.d = make_int4(leaf_ref(first, kMax), rightRef, kMax, rest <= kMax ? rest : 0);
+            p.d = make_int4(leaf_ref(first, kMax), rightRef, static_cast<int>(kNoCone), static_cast<int>(kNoCone));
             pairs.push_back(p);
         }
         extraDepth = std::max(extraDepth, chain);
@@ -370,7 +468,7 @@ int relayout_mesh(nrb_renderer* r, MeshSlot& m, const nrb_mesh_desc* d) {
             p.a = make_float4(lo(L.bounds_min[0]), lo(L.bounds_min[1]), hi(L.bounds_max[0]), hi(L.bounds_max[1]));
             p.b = make_float4(lo(R.bounds_min[0]), lo(R.bounds_min[1]), hi(R.bounds_max[0]), hi(R.bounds_max[1]));
             p.c = make_float4(lo(L.bounds_min[2]), hi(L.bounds_max[2]), lo(R.bounds_min[2]), hi(R.bounds_max[2]));
-            p.d = make_int4(refs[0], refs[1], refs[0] < 0 ? L.count : 0, refs[1] < 0 ? R.count : 0);
+            p.d = make_int4(refs[0], refs[1], static_cast<int>(cone_of(kids[0])), static_cast<int>(cone_of(kids[1])));
         }
         v.rootRef = 0;
     }
@@ -474,7 +572,7 @@ int nrb_update_mesh(nrb_renderer* r, int slot, const nrb_mesh_desc* d) {
     MeshSlot& m = r->mesh[slot];
     m.clear();
     if (!d || d->num_triangles <= 0) return NRB_OK;
-    int rc = relayout_mesh(r, m, d);
+    int rc = relayout_mesh(r, m, d, slot == NRB_MESH_INNER_SHELL || slot == NRB_MESH_OUTER_SHELL);
     if (rc != NRB_OK) { m.clear(); return rc; }
     MeshDev& v = m.view;
     cudaStream_t s = r->stream;
@@ -1187,7 +1285,7 @@ int nrb_read_buffer(nrb_renderer* r, const char* name, void* dst, size_t bytes) 
 
 int nrb_trace_rays(nrb_renderer* r, int slot, int mode, const float* d_origins, const float* d_directions, size_t n,
                    nrb_hit* d_out) {
-    if (!r || slot < 0 || slot >= NRB_MESH_SLOT_COUNT || mode < 0 || mode > 4) return fail(NRB_ERR_INVALID, "bad argument");
+    if (!r || slot < 0 || slot >= NRB_MESH_SLOT_COUNT || mode < 0 || mode > 7) return fail(NRB_ERR_INVALID, "bad argument");
     if (n >= (1ull << 31)) return fail(NRB_ERR_INVALID, "too many rays for one call");
     NRB_CUDA(cudaSetDevice(r->device));
     if (!r->scratchC.p) {

@@ -208,6 +208,9 @@ __global__ void __launch_bounds__(128) k_trace_rays(const __grid_constant__ Mesh
                 else tr.step_pop();
             }
             h = Hit{tr.best0, tr.best1, tr.best2, 0u};
+        } else if (mode >= 5) {  // parity hook: the run-time-mode loop of the segment stages (cone culling included)
+            h = trace_dyn_inline(target_of(m), mode - 5, ld3(o, i), ld3(d, i));
+            if (h.t >= 1e30f) h = Hit{1e30f, 0.0f, 0.0f, 0u};
         } else {
             h = trace_mode<true>(m, mode, ld3(o, i), ld3(d, i), &st);
             if (h.t >= 1e30f) h = Hit{1e30f, 0.0f, 0.0f, 0u};

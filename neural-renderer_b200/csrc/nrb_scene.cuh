@@ -24,8 +24,32 @@ struct __align__(16) NodePair {
     float4 a;  // lmin.x lmin.y lmax.x lmax.y
     float4 b;  // rmin.x rmin.y rmax.x rmax.y
     float4 c;  // lmin.z lmax.z rmin.z rmax.z
-    int4 d;    // leftRef rightRef leftCount rightCount
+    int4 d;    // leftRef rightRef leftCone rightCone
 };
+
+// Normal cone of a child's subtree, one 32-bit word: axis as three snorm8 (x | y << 8 | z << 16, value / 127) and a
+// threshold s as unorm8 (<< 24, value / 255; 255 = no cone).  Built at upload (nrb_api.cu:relayout_mesh) such that
+//   dot(axis, d) >=  s * |d|  implies  n . d > 0 for EVERY triangle normal n of the subtree (all back-facing: a
+//                                       FORWARD_ONLY query rejects each of them, src/mesh_traversal.cuh:166-169),
+//   dot(axis, d) <= -s * |d|  implies  n . d < 0 for every one (all front-facing: BACKWARD_ONLY rejects them all),
+// with margins that cover the 8-bit quantisation and fp32 rounding of both dot products.  Skipping such a subtree for
+// that mode removes only triangles its facing test would have skipped, so results are unchanged; what it buys is
+// that a FORWARD query along a ray that LEAVES a closed shell stops visiting everything the ray pierces.
+constexpr uint32_t kNoCone = 0xff000000u;
+__host__ __device__ __forceinline__ float cone_dot(uint32_t cone, float dx, float dy, float dz) {
+    const float k = 1.0f / 127.0f;
+    const float ax = static_cast<float>(static_cast<signed char>(cone & 0xffu)) * k;
+    const float ay = static_cast<float>(static_cast<signed char>((cone >> 8) & 0xffu)) * k;
+    const float az = static_cast<float>(static_cast<signed char>((cone >> 16) & 0xffu)) * k;
+    return ax * dx + ay * dy + az * dz;
+}
+__host__ __device__ __forceinline__ float cone_threshold(uint32_t cone) { return static_cast<float>(cone >> 24) * (1.0f / 255.0f); }
+// bit 0: no triangle of the subtree can pass a FORWARD_ONLY facing test along d; bit 1: none can pass BACKWARD_ONLY
+__host__ __device__ __forceinline__ int cone_culls(uint32_t cone, float dx, float dy, float dz, float dlen) {
+    if ((cone >> 24) == 0xffu) return 0;
+    const float c = cone_dot(cone, dx, dy, dz), s = cone_threshold(cone) * dlen;
+    return (c >= s ? 1 : 0) | (c <= -s ? 2 : 0);
+}
 static_assert(sizeof(NodePair) == 64, "NodePair");
 
 struct __align__(16) TriBlock {

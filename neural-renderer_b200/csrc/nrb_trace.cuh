@@ -215,6 +215,9 @@ __device__ __forceinline__ Hit trace_dyn_inline(const TraceTarget& m, int mode, 
     int ref = m.rootRef;
     const NodePair* __restrict__ nodes = m.nodes;
     const TriBlock* __restrict__ tris = m.tris;
+    // facing modes skip subtrees whose normal cone says every triangle fails the facing test (nrb_scene.cuh)
+    const int coneBit = mode == TRACE_FORWARD ? 1 : (mode == TRACE_BACKWARD ? 2 : 0);
+    const float dlen = coneBit ? sqrtf(dot(d, d)) : 0.0f;
     // pop: skip entries whose box entry distance is now beyond the best hit
     auto pop = [&]() {
         int next = kTraceDone;
@@ -233,6 +236,10 @@ __device__ __forceinline__ Hit trace_dyn_inline(const TraceTarget& m, int mode, 
             slab_pair(rp, a, b, c, hl, ln, hr, rn);
             hl = hl && !(ln > best.t);
             hr = hr && !(rn > best.t);
+            if (coneBit) {
+                hl = hl && !(cone_culls(static_cast<uint32_t>(k.z), d.x, d.y, d.z, dlen) & coneBit);
+                hr = hr && !(cone_culls(static_cast<uint32_t>(k.w), d.x, d.y, d.z, dlen) & coneBit);
+            }
             if (hl && hr) {
                 const bool rightFirst = rn < ln;
                 if (sp < kTraceStack) stack[sp++] = make_int2(rightFirst ? k.x : k.y, __float_as_int(rightFirst ? ln : rn));
@@ -399,7 +406,11 @@ __device__ __noinline__ static void trace_multi(TraceTarget m, int want, V3 o, V
 // of letting them idle until the warp's longest ray ends.
 //
 // Pruning here is by the UNION of the live modes: a box is entered while its entry distance is not beyond
-// `limit` = the largest best-t among the wanted modes (1e30 while one of them has no hit yet).  trace_multi
+// `limit` = the largest best-t among the wanted modes (1e30 while one of them has no hit yet).
+// (Round 2 experiment, removed: the nodes' normal cones - see trace_dyn_inline - as a second pruning rule for the
+// FORWARD / BACKWARD members of the set.  Parity-green, but k_bounce_begin went from 0.543 to 0.624 ms: a bounce ray
+// starts INSIDE the shell, where it lies inside the boxes of all coarse nodes - whose cones are too wide to cull -
+// so the 36 node pairs per vertex are visited for every mode, and the cone decode only added instructions.)  trace_multi
 // above tracks, per node, exactly which modes' own traversals would enter it (three compares per box, a
 // mode set per stack entry); the union visits a superset of those nodes, and a mode m can gain a hit from
 // the extra ones only through a triangle whose computed t is below best_m although its leaf box was entered

@@ -287,6 +287,31 @@ def test_fused_three_mode_traversal_is_exact(oracle_lib):
             assert np.allclose(union[key], ref["t"], rtol=1e-5, atol=0)
 
 
+def test_normal_cone_culling_changes_nothing(oracle_lib):
+    """The shells' node pairs carry normal cones (csrc/nrb_scene.cuh): facing-mode traversals skip subtrees in which
+    every triangle would fail the facing test.  The run-time-mode loop of the segment stages (parity hook modes 5-7)
+    must return exactly what the reference traversal returns - ids included - on convex and on non-convex shells,
+    from inside and outside, along axis-parallel and unnormalised directions."""
+    for kind, sub in (("ico", 3), ("blobs", 3)):
+        scene = nrb.scenes.make_scene(kind, sub, additional=True, env=False, shell_delta=0.3 if kind == "blobs" else 0.12)
+        # a bumpy (non-convex) outer shell: cones of coarse nodes are wide, of fine nodes narrow
+        hv, hidx = nrb.scenes.icosphere(4)
+        scene.outer_shell = nrb.scenes.mesh_from(nrb.scenes.displace(hv * np.float32(1.3), 0.25, seed=9), hidx) if kind == "ico" else scene.outer_shell
+        prod, orc, eye = make_pair(scene, oracle_lib, 8, 8)
+        o, d = random_rays(30000, seed=99)
+        o[:12000] *= 0.35            # origins inside the shells
+        d[:3000] *= np.float32(2.5)  # unnormalised directions
+        d[3000:3006] = np.eye(3, dtype=np.float32).repeat(2, 0) * np.array([1, -1, 1, -1, 1, -1], np.float32)[:, None]
+        for slot in (nrb.SLOT_OUTER, nrb.SLOT_INNER):
+            for mode in (0, 1, 2):
+                a, b = prod.trace_rays(slot, 5 + mode, o, d), orc.trace_rays(slot, mode, o, d)
+                assert np.array_equal(a["t"], b["t"]), (kind, slot, mode)
+                hit = b["t"] < 1e30
+                assert np.array_equal(a["prim"][hit], b["prim"][hit]) and hit.sum() > 500, (kind, slot, mode)
+        prod.close()
+        orc.close()
+
+
 def test_async_read_back_is_the_frame():
     """nrb_read_pixels_async (second stream, staged copy): frames streamed back while the next one renders are
     the frames a blocking read returns."""
