@@ -215,6 +215,11 @@ typedef enum nrb_option {
                                          reference ships but never launches), guided by the sample-0 primary-hit
                                          normal and albedo; accumulation itself is untouched.  Single-GPU frames only
                                          (nrb_set_tile world 1): the 11x11 window would need rows of other ranks. */
+    NRB_OPT_PATH_TAIL = 15,           /* (new) bounces >= 2 run as ONE kernel (a warp carries up to 16 surviving paths through sample ->
+                                         shell entry -> segment loop -> integrate, bounce after bounce) while the previous frames entered
+                                         bounce 2 with at most `value` paths (default 49152; 0 = always the per-stage kernels).  Needs
+                                         NRB_OPT_TAIL_GRAPH = 2.  The network then runs on the mma.sync tile: outputs equal the
+                                         tcgen05 kernels' within fp16 tolerance. */
     NRB_OPT_LITERAL_BOUNCE_TRACES = 14 /* (new, parity hook) 1: the bounce entry runs every trace of
                                          checkBounceEarlyTermination / traceOuterShellEntryFromRays
                                          (src/cuda_renderer_neural.cu:503-553, 773-852) literally.  0 (default): traces

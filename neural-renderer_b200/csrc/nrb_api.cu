@@ -128,6 +128,8 @@ struct nrb_renderer {
     DevBuf grid, mlp, packedW, xt, encCur;
     SegTail segTail;
     int tailMode = 2;  // NRB_OPT_TAIL_GRAPH: 0 fixed loop, 1 conditional WHILE graph, 2 fused tail kernel
+    int pathTailBelow = 49152;  // NRB_OPT_PATH_TAIL: bounces >= 2 run as one kernel while they start with at most this many paths
+    int* pathFeedback = nullptr;  // mapped host memory: [0] paths that entered bounce 2 in the last finished frame
     bool denoise = false;
     bool literalBounceTraces = false;
     size_t gridParams = 0, mlpParams = 0;
@@ -521,6 +523,12 @@ int nrb_create(const nrb_nn_config* cfg, int device, nrb_renderer** out) {
         delete r;
         return fail(NRB_ERR_CUDA, "stream/event creation failed");
     }
+    if (cudaHostAlloc(reinterpret_cast<void**>(&r->pathFeedback), 4 * sizeof(int), cudaHostAllocMapped) == cudaSuccess) {
+        r->pathFeedback[0] = -1;
+    } else {
+        r->pathFeedback = nullptr;
+        cudaGetLastError();
+    }
     // function attributes are per device: opt every > 48 KB kernel in on THIS device (renderers may live on several GPUs)
     init_frame_kernels();
     init_query_kernels();
@@ -562,6 +570,7 @@ void nrb_destroy(nrb_renderer* r) {
     if (r->prof.ready)
         for (int i = 0; i <= StageProfiler::kMaxMarks; ++i) cudaEventDestroy(r->prof.ev[i]);
     if (r->stream) cudaStreamDestroy(r->stream);
+    if (r->pathFeedback) cudaFreeHost(r->pathFeedback);
     delete r;
 }
 
@@ -727,6 +736,10 @@ int nrb_set_option(nrb_renderer* r, int option, int value) {
         case NRB_OPT_TAIL_GRAPH: r->tailMode = value < 0 ? 0 : (value > 2 ? 2 : value); break;
         case NRB_OPT_DENOISE: r->denoise = value != 0; break;
         case NRB_OPT_LITERAL_BOUNCE_TRACES: r->literalBounceTraces = value != 0; break;
+        case NRB_OPT_PATH_TAIL:
+            r->pathTailBelow = value < 0 ? 0 : value;
+            if (r->pathFeedback) r->pathFeedback[0] = -1;
+            break;
         case NRB_OPT_USE_HARDWARE_RT: break;  // accepted, ignored: there is no OptiX path
         default: return fail(NRB_ERR_INVALID, "unknown option");
     }
@@ -749,6 +762,7 @@ int nrb_get_option(const nrb_renderer* r, int option) {
         case NRB_OPT_TAIL_GRAPH: return r->tailMode;
         case NRB_OPT_DENOISE: return r->denoise ? 1 : 0;
         case NRB_OPT_LITERAL_BOUNCE_TRACES: return r->literalBounceTraces ? 1 : 0;
+        case NRB_OPT_PATH_TAIL: return r->pathTailBelow;
         default: return 0;
     }
 }
@@ -1037,7 +1051,8 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     }
     const bool neural = r->useNeuralQuery && r->weightsLoaded && outer.view.numTriangles > 0;  // (:2258-2260)
     int launches;
-    if (neural) launches = launch_neural_frame(f, r->net, r->lambertView, s, (r->tailMode == 1 && !debug_sync_enabled()) ? &r->segTail : nullptr, r->tailMode == 2);
+    if (neural) launches = launch_neural_frame(f, r->net, r->lambertView, s, (r->tailMode == 1 && !debug_sync_enabled()) ? &r->segTail : nullptr, r->tailMode == 2,
+                                               r->pathFeedback, r->tailMode == 2 ? r->pathTailBelow : 0);
     else launches = launch_gt_frame(f, r->lambertView, s);
     if (r->denoise && !r->lambertView) launches += launch_denoise(f, s);
     if (r->gather.role != 0) {

@@ -19,15 +19,19 @@ namespace nrb {
 
 // ---------------------------------------------------------------------------------------------
 
-__global__ void __launch_bounds__(kTileThreads) k_gt_primary(const __grid_constant__ Frame f) {
+__global__ void __launch_bounds__(kTileThreads, 10) k_gt_primary(const __grid_constant__ Frame f) {
     const FrameParams& fp = f.fp;
-    const ElemId id = tile_elem(fp);
+    const int total = tile_count(fp);
+    unsigned int nRays = 0;
+    for (int tile = next_tile(f.st.counts + 10, total); tile >= 0; tile = next_tile(f.st.counts + 10, total)) {
+    const ElemId id = tile_elem_at(fp, tile);
     bool active = false;
     if (id.valid) {
+        ++nRays;
         uint32_t rng = rng_seed(id.pixel, fp.sampleOffset, id.s);
         const V3 dir = primary_direction(fp, id.x, id.gy, rng);
         V3 pos = v3s(0.0f), nrm = v3s(0.0f), alb = v3s(0.0f), mp;
-        const bool hit = hit_record<TRACE_FORWARD>(f, f.classicSlot, fp.camPos, dir, pos, nrm, alb, mp);
+        const bool hit = hit_record<TRACE_FORWARD, true>(f, f.classicSlot, fp.camPos, dir, pos, nrm, alb, mp);
         rec_store(f.st.rec[0], id.e, pos, hit ? 1 : 0, nrm, 0.0f, alb, mp);
         V3 L = v3s(0.0f);
         if (!hit) L = fp.useDirectEnvColor ? fp.directEnvColor : env_clamped(f.env, dir, fp.maxRadiance);
@@ -36,7 +40,8 @@ __global__ void __launch_bounds__(kTileThreads) k_gt_primary(const __grid_consta
         active = hit && fp.maxBounces > 0;
     }
     queue_push(f.st.queue[0], f.st.counts + 0, active, id.e);
-    stat_flush(f.st.stats + 0, id.valid ? 1u : 0u);
+    }
+    stat_flush(f.st.stats + 0, nRays);
 }
 
 __global__ void __launch_bounds__(kQueueThreads) k_gt_bounce(const __grid_constant__ Frame f, int bounce, int qin,
@@ -63,7 +68,7 @@ __global__ void __launch_bounds__(kQueueThreads) k_gt_bounce(const __grid_consta
             if (sample_vertex(f, id, f4v(P), f4v(N), f4v(C), v3(C.w, M.x, M.y), bounce == 1, prev, org, wi, weight,
                               pdf)) {
                 V3 pos, nrm, alb, mp;
-                const bool hit = hit_record<TRACE_ANY>(f, f.classicSlot, org, wi, pos, nrm, alb, mp);
+                const bool hit = hit_record<TRACE_ANY, true>(f, f.classicSlot, org, wi, pos, nrm, alb, mp);
                 ++nTrace;
                 V3 T = f4v(f.st.T[e]), L = v3s(0.0f);
                 bool touchedL;
@@ -330,8 +335,11 @@ int launch_gt_frame(const Frame& f, bool lambert, cudaStream_t s) {
     const FrameParams& fp = f.fp;
     int launches = 0;
     cudaMemsetAsync(f.st.counts, 0, 16 * sizeof(int), s);
-    const dim3 grid((fp.width + 31) / 32, (fp.localHeight + 3) / 4, fp.spp);
-    k_gt_primary<<<grid, kTileThreads, 0, s>>>(f);
+    {
+        const int tiles = ((fp.width + 7) / 8) * ((fp.localHeight + 3) / 4) * fp.spp;
+        const int need = (tiles + 3) / 4, cap = sm_count() * 10;
+        k_gt_primary<<<need < cap ? need : cap, kTileThreads, 0, s>>>(f);
+    }
     NRB_LAUNCHED("k_gt_primary", s);
     ++launches;
     if (lambert) return launches + launch_lambert(f, s);

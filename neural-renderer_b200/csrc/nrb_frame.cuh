@@ -67,7 +67,8 @@ struct SegTail {
     void release();
     ~SegTail() { release(); }
 };
-int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStream_t s, SegTail* tail, bool fusedTail);
+int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStream_t s, SegTail* tail, bool fusedTail,
+                        int* hostFeedback, int pathTailBelow);
 int launch_finalize(const Frame& f, cudaStream_t s);
 int launch_lambert(const Frame& f, cudaStream_t s);
 int launch_denoise(const Frame& f, cudaStream_t s);

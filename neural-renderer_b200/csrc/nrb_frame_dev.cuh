@@ -29,6 +29,33 @@ __device__ __forceinline__ ElemId tile_elem(const FrameParams& fp) {
     return id;
 }
 
+// The same 8x4 tiles handed out one per warp from a device cursor (persistent grids: the resident warps of every SM
+// stay busy until the frame's last tile, and tiles of sky pixels cost no CTA launch).  tile < 0: none left.
+__device__ __forceinline__ int tile_count(const FrameParams& fp) {
+    return ((fp.width + 7) >> 3) * ((fp.localHeight + 3) >> 2) * fp.spp;
+}
+__device__ __forceinline__ int next_tile(int* cursor, int total) {
+    int t = 0;
+    if ((threadIdx.x & 31) == 0) t = atomicAdd(cursor, 1);
+    t = __shfl_sync(0xffffffffu, t, 0);
+    return t < total ? t : -1;
+}
+__device__ __forceinline__ ElemId tile_elem_at(const FrameParams& fp, int tile) {
+    const int lane = threadIdx.x & 31;
+    const int tx = (fp.width + 7) >> 3, ty = (fp.localHeight + 3) >> 2;
+    ElemId id;
+    id.s = tile / (tx * ty);
+    const int r = tile - id.s * (tx * ty);
+    const int by = r / tx, bx = r - by * tx;
+    id.x = bx * 8 + (lane & 7);
+    const int ly = by * 4 + (lane >> 3);
+    id.valid = id.x < fp.width && ly < fp.localHeight;
+    id.gy = global_row(fp, ly);
+    id.pixel = id.gy * fp.width + id.x;
+    id.e = ly * fp.width + id.x + id.s * fp.localPixels;
+    return id;
+}
+
 __device__ __forceinline__ ElemId queue_elem(const FrameParams& fp, int e) {
     ElemId id;
     id.e = e;
@@ -69,10 +96,12 @@ __device__ __forceinline__ V3 global_mparams(const MaterialDev& g) {
 
 // Trace one mesh and build the reference's hit record (the tail shared by :244-296, :556-618,
 // :1128-1188, :1235-1302).
-template <int MODE>
+template <int MODE, bool INLINE = false>
 __device__ __forceinline__ bool hit_record(const Frame& f, int slot, V3 o, V3 d, V3& pos, V3& nrm, V3& alb, V3& mp) {
     const MeshDev& m = f.mesh[slot];
-    const Hit h = trace_dyn(target_of(m), MODE, o, d);
+    // INLINE: kernels whose only traversal this is (ground-truth primary / bounce) inline the loop - a called copy
+    // moves the global-memory descriptor to a uniform register before every load
+    const Hit h = INLINE ? trace_dyn_inline(target_of(m), MODE, o, d) : trace_dyn(target_of(m), MODE, o, d);
     if (h.t >= 1e30f) {
         mp = global_mparams(f.gmat);
         return false;

@@ -358,9 +358,14 @@ constexpr int kRefillBelow = 22;  // 28 measured slower after the trace pruning 
 
 // sampleBounceDirectionsKernel (:357-499) on the live-path queue: fully convergent apart from the
 // three-way lobe choice.  A path the reference deactivates here is marked by pdf = -1.
-__global__ void __launch_bounds__(kQueueThreads, 8) k_bounce_sample(const __grid_constant__ Frame f, int bounce, int qin) {
+__global__ void __launch_bounds__(kQueueThreads, 8) k_bounce_sample(const __grid_constant__ Frame f, int bounce, int qin,
+                                                                    int* hostFeedback) {
     const FrameParams& fp = f.fp;
     const int n = f.st.counts[qin];
+    if (hostFeedback && blockIdx.x == 0 && threadIdx.x == 0) {  // how many paths enter this bounce: the host's hint for the next frames
+        hostFeedback[0] = n;
+        __threadfence_system();
+    }
     const SurfRec& cur = f.st.rec[bounce == 1 ? 0 : 1];
     for (int i = queue_start(n); i < n; i += gridDim.x * blockDim.x) {
         const int e = f.st.queue[qin][i];
@@ -774,6 +779,147 @@ __global__ void __launch_bounds__(512, 1)
     }
 }
 
+// ---- every bounce after the first as ONE launch --------------------------------------------------------
+// On the bench scene bounce 1 carries 780 K path vertices, bounce 2 three thousand and bounce 3 about fifty, and
+// each of those bounces still cost eight dependent launches whose time was the latency of a handful of warps
+// (~0.1 ms per bounce).  Paths are independent of each other, so nothing needs a
+// grid-wide step between their bounces: a warp takes up to 16 of the surviving paths - spread one per warp while
+// there are fewer paths than warps - and carries them through
+//   sample (sampleBounceDirections :357-499) -> early termination + shell entry (:503-553, :773-852)
+//   -> segment loop (exits, network, apply, re-entry; :858-1123, :1456-1524) -> hybrid mesh + integrate (:1235-1450, :621-675)
+// bounce after bounce until each has ended.  The network runs as the warp-autonomous mma.sync tile against weights
+// the CTA loads once (as in k_seg_tail); the traversals are the exact per-mode trace_multi / trace_dyn loops.  Same
+// results as the per-stage kernels up to the order of the fp32 sums inside the network (fp16 tolerance).
+// The host launches it instead of the per-bounce stages when the previous frames entered bounce 2 with few paths
+// (the count travels back through mapped host memory, no synchronisation); it is correct for any count.
+template <int WIDTH>
+__global__ void __launch_bounds__(512, 1)
+    k_path_tail(const __grid_constant__ Frame f, const __grid_constant__ NetDev net, int firstBounce, int ek, int warps,
+                int* hostFeedback) {
+    using namespace qwarp;
+    const FrameParams& fp = f.fp;
+    const int n = f.st.counts[0];
+    if (blockIdx.x == 0 && threadIdx.x == 0 && hostFeedback) {
+        hostFeedback[0] = n;
+        __threadfence_system();
+    }
+    const int totalWarps = gridDim.x * warps;
+    int per = (n + totalWarps - 1) / totalWarps;  // paths per warp trip: one while the paths are fewer than the warps
+    per = per < 1 ? 1 : (per > kRows ? kRows : per);
+    if (n == 0 || blockIdx.x * warps * per >= n) return;
+    extern __shared__ __align__(16) unsigned char tailSmem[];
+    const int H = net.nHidden;
+    const int ld0 = ek + 8, ldw = WIDTH + 8, ldA = (ek > WIDTH ? ek : WIDTH) + 8;
+    __half* w0 = reinterpret_cast<__half*>(tailSmem);
+    __half* wh = w0 + WIDTH * ld0;
+    __half* wl = wh + (H - 1) * WIDTH * ldw;
+    unsigned char* perWarp = reinterpret_cast<unsigned char*>(wl + 16 * ldw);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    preload_weights<WIDTH>(net, ek, w0, wh, wl);
+    __syncthreads();
+    if (warp >= warps) return;
+    const size_t perWarpBytes = static_cast<size_t>(kRows) * ldA * 2 + static_cast<size_t>(kRows) * 16 * 4 + kRows * 16 * 2;
+    __half* act = reinterpret_cast<__half*>(perWarp + warp * perWarpBytes);
+    float* inp = reinterpret_cast<float*>(act + kRows * ldA);
+    __half* outRows = reinterpret_cast<__half*>(inp + kRows * 16);
+    const TraceTarget tOuter = target_of(f.mesh[NRB_SLOT_OUTER]), tInner = target_of(f.mesh[NRB_SLOT_INNER]);
+    const bool literal = f.literalBounceTraces != 0;
+    const bool useAdd = f.additionalEnabled && f.mesh[NRB_SLOT_ADDITIONAL].numTriangles > 0;
+    const SurfRec& rec = f.st.rec[1];
+    unsigned int nTrace = 0, nQuery = 0, nVert = 0;
+    const unsigned full = 0xffffffffu;
+    for (int base = (blockIdx.x * warps + warp) * per; base < n; base += totalWarps * per) {
+        bool alive = lane < per && base + lane < n;
+        const int e = alive ? f.st.queue[0][base + lane] : 0;
+        const ElemId id = queue_elem(fp, e);
+        for (int b = firstBounce; b <= fp.maxBounces && __any_sync(full, alive); ++b) {
+            // ---- sample + early termination + shell entry
+            V3 org = v3s(0.0f), wi = v3(0.0f, 0.0f, 1.0f), weight = v3s(0.0f);
+            bool enters = false;
+            if (alive) {
+                const SurfRec& cur = f.st.rec[b == 1 ? 0 : 1];
+                const float4 P = cur.P[e], N = cur.N[e], C = cur.C[e];
+                const float2 M = cur.M[e];
+                const V3 prev = b == 1 ? v3s(0.0f) : f4v(f.st.prevD[e]);
+                float pdf = 0.0f;
+                ++nVert;
+                alive = sample_vertex(f, id, f4v(P), f4v(N), f4v(C), v3(C.w, M.x, M.y), b == 1, prev, org, wi, weight, pdf);
+                if (alive) {
+                    const float carried = N.w;
+                    float tAny, tFwd, tBwd;
+                    trace_multi(tOuter, (carried > 0.0f ? 1 : 0) | 2 | 4, org, wi, tAny, tFwd, tBwd);
+                    nTrace += (carried > 0.0f ? 2u : 0u) + 1u + (tFwd >= 1e30f ? 1u : 0u);
+                    if (carried > 0.0f && (literal || tAny < 1e30f)) {
+                        const Hit hi = trace_dyn(tInner, TRACE_ANY, org, wi);
+                        if (hi.t < 1e30f && tAny < 1e30f && hi.t < tAny) alive = false;
+                    }
+                    float entryT = tFwd, baseOffset = 0.0f;
+                    V3 entryOrigin = org;
+                    if (alive && !(tFwd < 1e30f) && tBwd < 1e30f) {
+                        ++nTrace;
+                        if (literal) {  // restart beyond the exit and look for a front face again (:806-838)
+                            baseOffset = tBwd + kSegEps;
+                            entryOrigin = org + wi * baseOffset;
+                            entryT = trace_dyn(tOuter, TRACE_FORWARD, entryOrigin, wi).t;
+                        }
+                    }
+                    if (alive) {
+                        rec_clear(rec, e);
+                        if (entryT < 1e30f) {
+                            const V3 p = entryOrigin + wi * entryT;
+                            f.st.segE[e] = make_float4(p.x, p.y, p.z, baseOffset + entryT);
+                            f.st.segD[e] = make_float4(wi.x, wi.y, wi.z, 0.0f);
+                            enters = true;
+                        }
+                    }
+                }
+            }
+            // ---- segment loop of the rays that entered the shell
+            for (int it = 0; it < kMaxSegIters && __any_sync(full, enters); ++it) {
+                if (lane < kRows)
+                    for (int c = 0; c < 16; ++c) inp[lane * 16 + c] = 0.0f;
+                if (enters) {
+                    seg_exit_one(f, e, inp + lane * 16);
+                    ++nQuery;
+                }
+                __syncwarp();
+                query_tile<WIDTH>(net, ek, w0, wh, wl, act, inp, outRows, 16, kRows);
+                if (enters) enters = seg_apply_one(f, e, *reinterpret_cast<const uint4*>(outRows + lane * 16), rec, nTrace);
+                __syncwarp();
+            }
+            // ---- hybrid mesh, throughput / radiance, Russian roulette
+            if (alive) {
+                bool hit = __float_as_int(rec.P[e].w) != 0;
+                if (useAdd) {
+                    V3 pos, nrm, alb, mp;
+                    const bool addHit = hit_record<TRACE_ANY>(f, NRB_SLOT_ADDITIONAL, org, wi, pos, nrm, alb, mp);
+                    ++nTrace;
+                    select_closer(rec, e, addHit, org, pos, nrm, alb, mp, hit);
+                }
+                V3 T = f4v(f.st.T[e]), L = v3s(0.0f);
+                bool touchedL;
+                if (!hit) L = f4v(f.st.L[e]);
+                alive = integrate_vertex(f, id, b, hit, wi, weight, T, L, touchedL);
+                if (touchedL) f.st.L[e] = make_float4(L.x, L.y, L.z, 0.0f);
+                if (alive) {
+                    f.st.T[e] = make_float4(T.x, T.y, T.z, 0.0f);
+                    f.st.prevD[e] = make_float4(wi.x, wi.y, wi.z, 0.0f);
+                }
+            }
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        nTrace += __shfl_xor_sync(full, nTrace, o);
+        nQuery += __shfl_xor_sync(full, nQuery, o);
+        nVert += __shfl_xor_sync(full, nVert, o);
+    }
+    if (lane == 0 && (nTrace | nQuery | nVert)) {
+        atomicAdd(f.st.stats + 0, static_cast<unsigned long long>(nTrace) + 2ull * nQuery);
+        atomicAdd(f.st.stats + 1, static_cast<unsigned long long>(nQuery));
+        atomicAdd(f.st.stats + 2, static_cast<unsigned long long>(nVert));
+    }
+}
+
 // Shared-memory plan of k_seg_tail (weights + per-warp tiles); 0 warps = shape not supported by the mma.sync tile.
 static size_t seg_tail_smem(const NetDev& net, int* warpsOut, int* ekOut) {
     int w = 0;
@@ -792,6 +938,19 @@ static size_t seg_tail_smem(const NetDev& net, int* warpsOut, int* ekOut) {
 void init_frame_kernels() {
     cudaFuncSetAttribute(k_seg_tail<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     cudaFuncSetAttribute(k_seg_tail<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(k_path_tail<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(k_path_tail<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+}
+
+// Bounces firstBounce..maxBounces in one launch (see k_path_tail).
+static bool launch_path_tail(const Frame& f, const NetDev& net, int firstBounce, int* hostFeedback, cudaStream_t s) {
+    int warps = 0, ek = 0;
+    const size_t smem = seg_tail_smem(net, &warps, &ek);
+    if (smem == 0) return false;
+    if (net.width == 128) k_path_tail<128><<<sm_count(), 512, smem, s>>>(f, net, firstBounce, ek, warps, hostFeedback);
+    else k_path_tail<64><<<sm_count(), 512, smem, s>>>(f, net, firstBounce, ek, warps, hostFeedback);
+    NRB_LAUNCHED("k_path_tail", s);
+    return true;
 }
 
 static bool launch_seg_tail(const Frame& f, const NetDev& net, int recIdx, cudaStream_t s) {
@@ -823,7 +982,8 @@ static int run_segments(const Frame& f, const NetDev& net, int recIdx, cudaStrea
     return launches;
 }
 
-int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStream_t s, SegTail* tail, bool fusedTail) {
+int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStream_t s, SegTail* tail, bool fusedTail,
+                        int* hostFeedback, int pathTailBelow) {
     const FrameParams& fp = f.fp;
     int launches = 0;
     if (fusedTail) tail = nullptr;  // the fused tail kernel needs no graph
@@ -841,9 +1001,19 @@ int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStr
     if (lambert) return launches + launch_lambert(f, s);
     const int grid = queue_grid(fp.nElems);
     for (int b = 1; b <= fp.maxBounces; ++b) {
+        // Few paths survive the first bounce: the rest of the frame is then one launch.  The decision uses the count
+        // the last finished frame reported (hostFeedback, mapped host memory; -1 = not known yet); the kernel is correct
+        // for any count, the per-stage kernels below are merely faster for large ones.
+        if (b >= 2 && pathTailBelow > 0 && hostFeedback) {
+            const int last = *reinterpret_cast<volatile int*>(hostFeedback);
+            if ((last < 0 || last <= pathTailBelow) && launch_path_tail(f, net, b, hostFeedback, s)) {
+                ++launches;
+                break;
+            }
+        }
         // path queue 0 -> ray queue 1 (+ segment queue 2) -> path queue 0
         // (k_bounce_sample resets the counters of the bounce: queues 1-3 and the two work cursors)
-        k_bounce_sample<<<grid, kQueueThreads, 0, s>>>(f, b, 0);
+        k_bounce_sample<<<grid, kQueueThreads, 0, s>>>(f, b, 0, b == 2 ? hostFeedback : nullptr);
         NRB_LAUNCHED("k_bounce_sample", s);
         {
             const int need = (fp.nElems + kQueueThreads - 1) / kQueueThreads;
