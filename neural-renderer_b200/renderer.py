@@ -306,6 +306,11 @@ class RendererNeural:
         """Parity hook: run every trace of the reference's bounce entry, also those whose outcome is decided."""
         self._opt(K.OPT_LITERAL_BOUNCE_TRACES, int(v))
 
+    def set_path_tail(self, max_paths: int):
+        """Bounces >= 2 as one kernel while the previous frames entered bounce 2 with at most `max_paths` paths
+        (default 49152; 0 = always the per-stage kernels)."""
+        self._opt(K.OPT_PATH_TAIL, int(max_paths))
+
     def stages(self):
         """-> {kernel name: (total ms, launches)} accumulated since reset_stages()."""
         out, i = {}, 0

@@ -287,6 +287,35 @@ def test_fused_three_mode_traversal_is_exact(oracle_lib):
             assert np.allclose(union[key], ref["t"], rtol=1e-5, atol=0)
 
 
+@pytest.mark.parametrize("kind,additional", [("ico", True), ("blobs", False)])
+def test_path_tail_kernel_matches_per_stage_bounces(oracle_lib, kind, additional):
+    """NRB_OPT_PATH_TAIL: bounces >= 2 in ONE launch (a warp carries the surviving paths through sample -> entry ->
+    segments -> integrate).  Same paths, same counters; radiance equal to the per-stage kernels up to the fp32
+    summation order inside the network (mma.sync tile vs tcgen05), and both against the oracle."""
+    scene = nrb.scenes.make_scene(kind, 3, additional=additional, shell_delta=0.3 if kind == "blobs" else 0.12,
+                                  material=dict(metallic=0.6, roughness=0.3))  # glossy: more paths survive to bounces 2..4
+    prod, orc, eye = make_pair(scene, oracle_lib, 192, 128, spp=2, bounces=4, neural=True, weights=_weights())
+    out = []
+    for below in (0, 1 << 30, 0):
+        prod.set_path_tail(below)
+        prod.reset_samples()
+        prod.render(eye)
+        prod.render(eye)  # the second frame of a setting has the feedback of the first
+        out.append((prod.read_pixels().copy(), prod.read_buffer("path_radiance").copy(), prod.counters()))
+    prod.set_path_tail(49152)
+    assert np.array_equal(out[0][0], out[2][0])
+    assert out[1][2]["kernels"] < out[0][2]["kernels"] - 10, (out[0][2], out[1][2])
+    for key in ("path_vertices", "neural_queries"):
+        assert abs(out[0][2][key] - out[1][2][key]) <= 0.002 * out[0][2][key] + 2, (key, out[0][2], out[1][2])
+    assert out[0][2]["path_vertices"] > 2000
+    d = np.abs(out[0][0].astype(int) - out[1][0].astype(int)).max(axis=2)
+    print(f"path tail vs per-stage: psnr {psnr8(out[0][0], out[1][0]):.2f} dB, pixels differing {np.mean(d > 0):.5f}, counters {out[1][2]}")
+    assert psnr8(out[0][0], out[1][0]) > 45.0 and np.mean(d > 1) < 0.005
+    orc.render(eye)
+    orc.render(eye)
+    assert psnr8(out[1][0], orc.read_pixels()) > 30.0
+
+
 def test_normal_cone_culling_changes_nothing(oracle_lib):
     """The shells' node pairs carry normal cones (csrc/nrb_scene.cuh): facing-mode traversals skip subtrees in which
     every triangle would fail the facing test.  The run-time-mode loop of the segment stages (parity hook modes 5-7)
