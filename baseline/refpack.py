@@ -160,6 +160,26 @@ def scene_with_reference_bvh(scene, bvh):
     return s
 
 
+def tcnn_time(net: dict, weights, n: int, reps: int = 10):
+    """Device time of tiny-cuda-nn's inference_mixed_precision on n seeded uniform queries -> timing dict."""
+    exe = os.path.join(BIN, "tcnn_query")
+    d = dict(log2_hashmap_size=14, base_resolution=16, n_points=3, n_levels=8, n_features=4, per_level_scale=2.0,
+             sh_degree=4, mlp_width=128, n_hidden=4)
+    d.update(net)
+    with tempfile.TemporaryDirectory(prefix="nrb_tcnn_") as tmp:
+        wp = os.path.join(tmp, "w.bin")
+        np.ascontiguousarray(weights).view(np.uint16).tofile(wp)
+        args = [exe, d["log2_hashmap_size"], d["base_resolution"], d["n_levels"], d["n_features"], d["per_level_scale"],
+                d["n_points"], d["sh_degree"], d["mlp_width"], d["n_hidden"], wp, 1, "@rand", n, "@none", reps]
+        res = subprocess.run([str(a) for a in args], capture_output=True, text=True, timeout=1800)
+    if res.returncode != 0:
+        raise RuntimeError(f"tcnn_query failed ({res.returncode}): {res.stdout[-1000:]} {res.stderr[-1000:]}")
+    for line in res.stdout.splitlines():
+        if line.startswith("{"):
+            return json.loads(line)
+    return None
+
+
 def tcnn_query(net: dict, weights, inputs, swap_order=True, time_reps=0):
     """tiny-cuda-nn inference_mixed_precision on `inputs` [n, input_dims] fp32 -> ([n,16] fp16, timing dict or None).
     net keys as scenes.network_sizes: log2_hashmap_size, base_resolution, n_points, n_levels, n_features,

@@ -21,7 +21,8 @@ def main():
     ap.add_argument("--kernel", type=int, default=0)
     ap.add_argument("--log2", type=int, nargs="+", default=[18, 20, 22])
     ap.add_argument("--dist", default="uniform", choices=["uniform", "coherent"])
-    ap.add_argument("--shape", default="ref", choices=["ref", "w64"])
+    ap.add_argument("--shape", default="ref", choices=["ref", "w64", "w128"])
+    ap.add_argument("--tcnn", action="store_true", help="also time tiny-cuda-nn (baseline/_ref/tcnn_query) on the same shape and batch")
     ap.add_argument("--reps", type=int, default=10)
     a = ap.parse_args()
     import torch
@@ -31,14 +32,16 @@ def main():
         flops = 2 * (112 * 128 + 3 * 128 * 128 + 128 * 16)
         gathered, hbm = 3 * 8 * 8 * 8, 36 + 16
     else:
+        W = 64 if a.shape == "w64" else 128
         cfg = nrb.NNConfig(log2_hashmap_size=19, base_resolution=16, n_points=1, n_levels=16, n_features_per_level=2,
-                           per_level_scale=1.5, sh_degree=-1, mlp_width=64, n_hidden_layers=2)
+                           per_level_scale=1.5, sh_degree=-1, mlp_width=W, n_hidden_layers=2)
         net = dict(log2_hashmap_size=19, base_resolution=16, n_points=1, n_levels=16, n_features=2, per_level_scale=1.5,
-                   sh_degree=0, mlp_width=64, n_hidden=2)
-        flops = 2 * (32 * 64 + 64 * 64 + 64 * 16)
+                   sh_degree=0, mlp_width=W, n_hidden=2)
+        flops = 2 * (32 * W + W * W + W * 16)
         gathered, hbm = 16 * 8 * 4, 12 + 16
     r = nrb.RendererNeural(nrb.Scene(), nn_config=cfg)
-    r.load_weights(nrb.scenes.make_weights(**net))
+    weights = nrb.scenes.make_weights(**net)
+    r.load_weights(weights)
     r.set_query_kernel(a.kernel)
     D = r.input_dims()
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {"bf16_tflops": 1590.0, "hbm_gbs": 6650.0}
@@ -67,7 +70,14 @@ def main():
         r.sync()
         ms = e0.elapsed_time(e1) / a.reps
         qps = n / (ms * 1e-3)
-        print(json.dumps({"queries": n, "kernel": a.kernel, "dist": a.dist, "shape": a.shape, "ms": round(ms, 4),
+        extra = {}
+        if a.tcnn:
+            from baseline import refpack
+            if refpack.have("tcnn_query"):
+                t = refpack.tcnn_time(net, weights, n, reps=a.reps)
+                extra = {"tcnn_ms": round(t["ms_per_call"], 4), "tcnn_Gqueries_per_s": round(t["gqueries_per_s"], 3),
+                         "speedup_vs_tcnn": round(t["ms_per_call"] / ms, 2)}
+        print(json.dumps({**extra, "queries": n, "kernel": a.kernel, "dist": a.dist, "shape": a.shape, "ms": round(ms, 4),
                           "Gqueries_per_s": round(qps / 1e9, 3), "tensor_TFLOPs": round(qps * flops / 1e12, 1),
                           "tensor_frac_of_measured_burst": round(qps * flops / 1e12 / peaks["bf16_tflops"], 4),
                           "hbm_GBs": round(qps * hbm / 1e9, 1), "hbm_frac": round(qps * hbm / 1e9 / peaks["hbm_gbs"], 4),
