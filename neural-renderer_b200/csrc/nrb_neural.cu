@@ -94,7 +94,12 @@ int launch_neural_query(const NetDev& net, const float* in, size_t n, const int*
         tmp.debug = net.kernelChoice >> 8;
         return launch_split_query(tmp, in, n, dCount, out, s);
     }
-    if (which != 1 && neural_query_tc_supported(net)) {
+    // shapes whose tables do not fit shared memory are bound by L2 gathers (BASELINE config 5: 16 levels x 2^19 entries,
+    // 512 B gathered against 14-45 KFLOP per query): the warp-autonomous mma.sync kernel keeps many more independent
+    // gather streams in flight than the warp-specialised tcgen05 kernel and is the faster of the two there
+    // (2^22 queries, width 64 / 128: 2.85 / 2.32 G queries/s against 2.06 / 1.98; tiny-cuda-nn 2.30 / 1.51)
+    const bool gatherBound = which == 0 && !splitPays && plan_smem(net).warps > 0;
+    if (which != 1 && !gatherBound && neural_query_tc_supported(net)) {
         NetDev tmp = net;
         tmp.debug = net.kernelChoice >> 8;
         return launch_neural_query_tc(tmp, in, n, dCount, out, s);
