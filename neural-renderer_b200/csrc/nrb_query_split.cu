@@ -646,6 +646,10 @@ int launch_split_query(const NetDev& net, const float* in, size_t n, const int* 
     const int sms = sm_count();
     int chunkRows = static_cast<int>(net.xtRows / kTileM * kTileM);
     if ((net.debug & 8) && chunkRows > 1024) chunkRows = 1024;  // tests: exercise the chunk walk on small batches
+    {
+        const int lg = (net.debug >> 8) & 31;  // experiments: NRB_OPT_QUERY_KERNEL = 3 | (log2 rows << 16) walks the batch in smaller chunks
+        if (lg >= 10 && chunkRows > (1 << lg)) chunkRows = 1 << lg;
+    }
     int launches = 0;
     for (size_t base = 0; base < n; base += chunkRows) {
         const size_t rows = n - base < static_cast<size_t>(chunkRows) ? n - base : chunkRows;

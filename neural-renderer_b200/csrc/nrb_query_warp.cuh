@@ -156,5 +156,92 @@ __device__ __forceinline__ void query_tile(const NetDev& net, int ek, const __ha
     __syncwarp();
 }
 
+// The same tile with the layer weights read straight from global memory (row-major [out][in] fp16, the checkpoint's
+// layout) instead of a shared-memory copy: a thread's B fragment of mma.m16n8k16 (row.col) is two 32-bit words of
+// one weight row, W[n0 + lane / 4][k0 + 2 * (lane % 4) + {0, 1}] and the same at k + 8.  For kernels in which a few
+// warps evaluate a few tiles (k_path_tail): no 170 KB preload per CTA, and the shared-memory carve-out stays small,
+// so the L1 keeps the BVH nodes the same warps traverse.  Same products, same fp32 summation order as query_tile.
+template <int WIDTH>
+__device__ __forceinline__ void query_tile_gmem(const NetDev& net, int ek, __half* act, const float* inp, __half* out,
+                                                size_t outStride, int validRows, int encodeRows = kRows) {
+    const int E = net.encDims, H = net.nHidden;
+    const int ldA = (ek > WIDTH ? ek : WIDTH) + 8;
+    const int lane = threadIdx.x & 31;
+    const int PL = net.nPoints * net.nLevels, F = net.nFeatures;
+    const int shBase = PL * F, shN = net.shDegree * net.shDegree;
+    // only the first encodeRows rows carry queries (a warp that holds one or two paths): the other rows of the tile
+    // are not encoded - rows are independent in the products, whatever they hold never reaches a valid output
+    for (int it = lane; it < encodeRows * PL; it += 32) {
+        const int pl = it / encodeRows, r = it - pl * encodeRows;
+        const int p = pl / net.nLevels, level = pl - p * net.nLevels;
+        const float* x = inp + r * 16 + 3 * p;
+        __half* dst = act + r * ldA + pl * F;
+        if (F == 4) encode_item<4>(net, level, x, dst);
+        else encode_item<2>(net, level, x, dst);
+    }
+    if (lane < kRows) {
+        __half* dst = act + lane * ldA + shBase;
+        if (shN > 0) encode_sh(net.shDegree, inp + lane * 16 + 3 * net.nPoints, dst);
+        for (int c = E; c < ek; ++c) act[lane * ldA + c] = __float2half_rn(0.0f);
+    }
+    __syncwarp();
+    const uint32_t aBase = smem_u32(act) + ((lane & 15) * ldA + (lane >> 4) * 8) * 2;
+    const int bn = lane >> 2, bk = (lane & 3) * 2;
+    const __half* W = net.mlp;
+    int K = ek, Kreal = E;  // layer 0: K padded to 16 in the tile, the weight rows hold E columns
+    for (int layer = 0; layer < H; ++layer) {
+        float acc[WIDTH / 8][4];
+#pragma unroll
+        for (int j = 0; j < WIDTH / 8; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.0f;
+        for (int k0 = 0; k0 < K; k0 += 16) {
+            uint32_t a0, a1, a2, a3;
+            ldsm_x4(aBase + k0 * 2, a0, a1, a2, a3);
+            const int c0 = k0 + bk, c1 = k0 + 8 + bk;
+#pragma unroll
+            for (int j = 0; j < WIDTH / 8; ++j) {
+                const __half* row = W + static_cast<size_t>(j * 8 + bn) * Kreal;
+                const uint32_t b0 = c0 < Kreal ? __ldg(reinterpret_cast<const uint32_t*>(row + c0)) : 0u;
+                const uint32_t b1 = c1 < Kreal ? __ldg(reinterpret_cast<const uint32_t*>(row + c1)) : 0u;
+                mma16816(acc[j], a0, a1, a2, a3, b0, b1);
+            }
+        }
+        __syncwarp();
+        const int r0 = lane >> 2, cc = (lane & 3) * 2;
+#pragma unroll
+        for (int j = 0; j < WIDTH / 8; ++j) {
+            *reinterpret_cast<uint32_t*>(act + r0 * ldA + j * 8 + cc) = leaky_pack2(acc[j][0], acc[j][1]);
+            *reinterpret_cast<uint32_t*>(act + (r0 + 8) * ldA + j * 8 + cc) = leaky_pack2(acc[j][2], acc[j][3]);
+        }
+        __syncwarp();
+        W += static_cast<size_t>(WIDTH) * Kreal;
+        K = WIDTH;
+        Kreal = WIDTH;
+    }
+    {
+        float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+        for (int k0 = 0; k0 < WIDTH; k0 += 16) {
+            uint32_t a0, a1, a2, a3;
+            ldsm_x4(aBase + k0 * 2, a0, a1, a2, a3);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const __half* row = W + static_cast<size_t>(j * 8 + bn) * WIDTH;
+                const uint32_t b0 = __ldg(reinterpret_cast<const uint32_t*>(row + k0 + bk));
+                const uint32_t b1 = __ldg(reinterpret_cast<const uint32_t*>(row + k0 + 8 + bk));
+                mma16816(acc[j], a0, a1, a2, a3, b0, b1);
+            }
+        }
+        const int r0 = lane >> 2, cc = (lane & 3) * 2;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            if (r0 < validRows)
+                *reinterpret_cast<__half2*>(out + static_cast<size_t>(r0) * outStride + j * 8 + cc) = __floats2half2_rn(acc[j][0], acc[j][1]);
+            if (r0 + 8 < validRows)
+                *reinterpret_cast<__half2*>(out + static_cast<size_t>(r0 + 8) * outStride + j * 8 + cc) = __floats2half2_rn(acc[j][2], acc[j][3]);
+        }
+    }
+    __syncwarp();
+}
+
+
 }  // namespace qwarp
 }  // namespace nrb

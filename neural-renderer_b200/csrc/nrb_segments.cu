@@ -787,15 +787,19 @@ __global__ void __launch_bounds__(512, 1)
 // there are fewer paths than warps - and carries them through
 //   sample (sampleBounceDirections :357-499) -> early termination + shell entry (:503-553, :773-852)
 //   -> segment loop (exits, network, apply, re-entry; :858-1123, :1456-1524) -> hybrid mesh + integrate (:1235-1450, :621-675)
-// bounce after bounce until each has ended.  The network runs as the warp-autonomous mma.sync tile against weights
-// the CTA loads once (as in k_seg_tail); the traversals are the exact per-mode trace_multi / trace_dyn loops.  Same
-// results as the per-stage kernels up to the order of the fp32 sums inside the network (fp16 tolerance).
+// bounce after bounce until each has ended.  The network runs as the warp-autonomous mma.sync tile with its weights
+// read straight from global memory (query_tile_gmem: a few tiles per warp do not repay a 170 KB preload per CTA, and
+// without that shared-memory carve-out the L1 keeps the shells' BVH nodes - with it every node fetch of these few,
+// latency-bound warps went to L2); the traversals are the exact per-mode trace_multi / trace_dyn loops.  Same results
+// as the per-stage kernels up to the order of the fp32 sums inside the network (fp16 tolerance).
 // The host launches it instead of the per-bounce stages when the previous frames entered bounce 2 with few paths
 // (the count travels back through mapped host memory, no synchronisation); it is correct for any count.
+constexpr int kPathTailWarps = 8;
 template <int WIDTH>
-__global__ void __launch_bounds__(512, 1)
-    k_path_tail(const __grid_constant__ Frame f, const __grid_constant__ NetDev net, int firstBounce, int ek, int warps,
+__global__ void __launch_bounds__(kPathTailWarps * 32, 2)
+    k_path_tail(const __grid_constant__ Frame f, const __grid_constant__ NetDev net, int firstBounce, int ek,
                 int* hostFeedback) {
+    constexpr int warps = kPathTailWarps;
     using namespace qwarp;
     const FrameParams& fp = f.fp;
     const int n = f.st.counts[0];
@@ -808,18 +812,10 @@ __global__ void __launch_bounds__(512, 1)
     per = per < 1 ? 1 : (per > kRows ? kRows : per);
     if (n == 0 || blockIdx.x * warps * per >= n) return;
     extern __shared__ __align__(16) unsigned char tailSmem[];
-    const int H = net.nHidden;
-    const int ld0 = ek + 8, ldw = WIDTH + 8, ldA = (ek > WIDTH ? ek : WIDTH) + 8;
-    __half* w0 = reinterpret_cast<__half*>(tailSmem);
-    __half* wh = w0 + WIDTH * ld0;
-    __half* wl = wh + (H - 1) * WIDTH * ldw;
-    unsigned char* perWarp = reinterpret_cast<unsigned char*>(wl + 16 * ldw);
+    const int ldA = (ek > WIDTH ? ek : WIDTH) + 8;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    preload_weights<WIDTH>(net, ek, w0, wh, wl);
-    __syncthreads();
-    if (warp >= warps) return;
     const size_t perWarpBytes = static_cast<size_t>(kRows) * ldA * 2 + static_cast<size_t>(kRows) * 16 * 4 + kRows * 16 * 2;
-    __half* act = reinterpret_cast<__half*>(perWarp + warp * perWarpBytes);
+    __half* act = reinterpret_cast<__half*>(tailSmem + warp * perWarpBytes);
     float* inp = reinterpret_cast<float*>(act + kRows * ldA);
     __half* outRows = reinterpret_cast<__half*>(inp + kRows * 16);
     const TraceTarget tOuter = target_of(f.mesh[NRB_SLOT_OUTER]), tInner = target_of(f.mesh[NRB_SLOT_INNER]);
@@ -828,9 +824,13 @@ __global__ void __launch_bounds__(512, 1)
     const SurfRec& rec = f.st.rec[1];
     unsigned int nTrace = 0, nQuery = 0, nVert = 0;
     const unsigned full = 0xffffffffu;
+    // path j of a trip lives on lane 2j (tile row j); the odd lane beside it is its partner in the segment exits, where
+    // the two traces of a segment (outer and inner shell) run side by side instead of one after the other
+    const int row = lane >> 1;
+    const bool even = (lane & 1) == 0;
     for (int base = (blockIdx.x * warps + warp) * per; base < n; base += totalWarps * per) {
-        bool alive = lane < per && base + lane < n;
-        const int e = alive ? f.st.queue[0][base + lane] : 0;
+        bool alive = even && row < per && base + row < n;
+        const int e = alive ? f.st.queue[0][base + row] : 0;
         const ElemId id = queue_elem(fp, e);
         for (int b = firstBounce; b <= fp.maxBounces && __any_sync(full, alive); ++b) {
             // ---- sample + early termination + shell entry
@@ -878,13 +878,16 @@ __global__ void __launch_bounds__(512, 1)
             for (int it = 0; it < kMaxSegIters && __any_sync(full, enters); ++it) {
                 if (lane < kRows)
                     for (int c = 0; c < 16; ++c) inp[lane * 16 + c] = 0.0f;
-                if (enters) {
-                    seg_exit_one(f, e, inp + lane * 16);
-                    ++nQuery;
+                __syncwarp();
+                {
+                    const int eP = __shfl_sync(full, e, lane & ~1);
+                    const bool entP = __shfl_sync(full, enters ? 1 : 0, lane & ~1) != 0;
+                    seg_exit_one(f, eP, inp + row * 16, lane & 1, entP);
+                    if (enters) ++nQuery;
                 }
                 __syncwarp();
-                query_tile<WIDTH>(net, ek, w0, wh, wl, act, inp, outRows, 16, kRows);
-                if (enters) enters = seg_apply_one(f, e, *reinterpret_cast<const uint4*>(outRows + lane * 16), rec, nTrace);
+                query_tile_gmem<WIDTH>(net, ek, act, inp, outRows, 16, kRows, per);
+                if (enters) enters = seg_apply_one(f, e, *reinterpret_cast<const uint4*>(outRows + row * 16), rec, nTrace);
                 __syncwarp();
             }
             // ---- hybrid mesh, throughput / radiance, Russian roulette
@@ -938,17 +941,20 @@ static size_t seg_tail_smem(const NetDev& net, int* warpsOut, int* ekOut) {
 void init_frame_kernels() {
     cudaFuncSetAttribute(k_seg_tail<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     cudaFuncSetAttribute(k_seg_tail<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    cudaFuncSetAttribute(k_path_tail<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    cudaFuncSetAttribute(k_path_tail<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(k_path_tail<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    cudaFuncSetAttribute(k_path_tail<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
 }
 
 // Bounces firstBounce..maxBounces in one launch (see k_path_tail).
 static bool launch_path_tail(const Frame& f, const NetDev& net, int firstBounce, int* hostFeedback, cudaStream_t s) {
     int warps = 0, ek = 0;
-    const size_t smem = seg_tail_smem(net, &warps, &ek);
-    if (smem == 0) return false;
-    if (net.width == 128) k_path_tail<128><<<sm_count(), 512, smem, s>>>(f, net, firstBounce, ek, warps, hostFeedback);
-    else k_path_tail<64><<<sm_count(), 512, smem, s>>>(f, net, firstBounce, ek, warps, hostFeedback);
+    if (seg_tail_smem(net, &warps, &ek) == 0) return false;  // shapes the mma.sync tile supports
+    const int ldA = (ek > net.width ? ek : net.width) + 8;
+    const size_t smem = static_cast<size_t>(kPathTailWarps) * (qwarp::kRows * ldA * 2 + qwarp::kRows * 16 * 4 + qwarp::kRows * 16 * 2);
+    if (smem > 64 * 1024) return false;
+    const int grid = sm_count() * 2;
+    if (net.width == 128) k_path_tail<128><<<grid, kPathTailWarps * 32, smem, s>>>(f, net, firstBounce, ek, hostFeedback);
+    else k_path_tail<64><<<grid, kPathTailWarps * 32, smem, s>>>(f, net, firstBounce, ek, hostFeedback);
     NRB_LAUNCHED("k_path_tail", s);
     return true;
 }

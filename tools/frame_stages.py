@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--subdiv", type=int, default=7)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--tag", default="")
+    ap.add_argument("--query-kernel", type=int, default=0)
     a = ap.parse_args()
     nrb = importlib.import_module("neural-renderer_b200")
     scene = nrb.scenes.make_scene("ico", a.subdiv, shells=True, env=True, env_size=(2048, 1024))
@@ -37,6 +38,8 @@ def main():
     if a.mode == "neural":
         r.load_weights(nrb.scenes.make_weights())
         r.set_use_neural_query(True)
+        if a.query_kernel:
+            r.set_query_kernel(a.query_kernel)
     for _ in range(5):
         r.render(eye)
     r.sync()
