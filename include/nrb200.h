@@ -297,6 +297,10 @@ int nrb_reset_stages(nrb_renderer* r);
  * [2] neural queries, [3] path vertices shaded. */
 int nrb_get_counters(nrb_renderer* r, uint64_t out[4]);
 
+/* (new) traversal work of the last nrb_trace_rays_host call (modes 0..2): [0] rays, [1] node pairs fetched (64 B each),
+ * [2] triangle blocks fetched (48 B each) - the counts behind the algorithmic bytes per ray of SURVEY.md 8d. */
+int nrb_get_trace_stats(nrb_renderer* r, uint64_t out[3]);
+
 /* (new, parity/debug) copy one of the renderer's per-element buffers to the host, in the
  * reference's layout (src/cuda_renderer_neural.h:160-214).  Needs NRB_OPT_CAPTURE = 1
  * before the frame.  Names: "hit_positions", "hit_normals", "hit_colors",

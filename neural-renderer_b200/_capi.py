@@ -138,7 +138,7 @@ class Lib:
             "reset_samples": ([vp], i), "set_tile": ([vp, i, i, i], i), "render": ([vp, P(f)], i),
             "device_pixels": ([vp], vp), "read_pixels": ([vp, vp, sz], i), "read_pixels_async": ([vp, vp, sz], i), "width": ([vp], i), "height": ([vp], i),
             "accum_sample_count": ([vp], C.c_uint32), "get_timings": ([vp, P(C.c_double), P(i), P(C.c_uint64)], i),
-            "get_counters": ([vp, P(C.c_uint64)], i), "read_buffer": ([vp, C.c_char_p, vp, sz], i),
+            "get_counters": ([vp, P(C.c_uint64)], i), "get_trace_stats": ([vp, P(C.c_uint64)], i), "read_buffer": ([vp, C.c_char_p, vp, sz], i),
             "trace_rays": ([vp, i, i, vp, vp, sz, vp], i), "trace_rays_host": ([vp, i, i, vp, vp, sz, vp], i),
             "neural_query": ([vp, vp, sz, vp], i), "neural_query_host": ([vp, vp, sz, vp], i),
             "input_dims": ([vp], i), "output_dims": ([vp], i), "sync": ([vp], i), "stream": ([vp], vp),

@@ -1233,6 +1233,14 @@ int nrb_reset_stages(nrb_renderer* r) {
     return rc;
 }
 
+int nrb_get_trace_stats(nrb_renderer* r, uint64_t out[3]) {
+    if (!r || !out) return fail(NRB_ERR_INVALID, "null argument");
+    out[0] = r->lastStats[0];  // rays of the last nrb_trace_rays_host call
+    out[1] = r->lastStats[3];  // node pairs fetched
+    out[2] = r->lastStats[4];  // triangle blocks fetched
+    return NRB_OK;
+}
+
 int nrb_get_counters(nrb_renderer* r, uint64_t out[4]) {
     if (!r || !out) return fail(NRB_ERR_INVALID, "null argument");
     int rc = fetch_stats(r);

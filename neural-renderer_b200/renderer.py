@@ -373,6 +373,12 @@ class RendererNeural:
         self.lib.check(self.lib.fn("get_counters")(self._h, c), "get_counters")
         return dict(kernels=c[0], ray_segments=c[1], neural_queries=c[2], path_vertices=c[3])
 
+    def trace_stats(self):
+        """Work of the last trace_rays call: rays, node pairs (64 B) and triangle blocks (48 B) fetched."""
+        c = (C.c_uint64 * 3)()
+        self.lib.check(self.lib.fn("get_trace_stats")(self._h, c), "get_trace_stats")
+        return dict(rays=c[0], node_pairs=c[1], triangles=c[2])
+
     def trace_rays(self, slot: int, mode: int, origins: np.ndarray, directions: np.ndarray) -> np.ndarray:
         o = np.ascontiguousarray(origins, np.float32)
         d = np.ascontiguousarray(directions, np.float32)
