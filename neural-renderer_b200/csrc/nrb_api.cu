@@ -524,7 +524,7 @@ int nrb_create(const nrb_nn_config* cfg, int device, nrb_renderer** out) {
         return fail(NRB_ERR_CUDA, "stream/event creation failed");
     }
     if (cudaHostAlloc(reinterpret_cast<void**>(&r->pathFeedback), 4 * sizeof(int), cudaHostAllocMapped) == cudaSuccess) {
-        r->pathFeedback[0] = -1;
+        r->pathFeedback[0] = r->pathFeedback[1] = -1;
     } else {
         r->pathFeedback = nullptr;
         cudaGetLastError();
@@ -738,7 +738,7 @@ int nrb_set_option(nrb_renderer* r, int option, int value) {
         case NRB_OPT_LITERAL_BOUNCE_TRACES: r->literalBounceTraces = value != 0; break;
         case NRB_OPT_PATH_TAIL:
             r->pathTailBelow = value < 0 ? 0 : value;
-            if (r->pathFeedback) r->pathFeedback[0] = -1;
+            if (r->pathFeedback) r->pathFeedback[0] = r->pathFeedback[1] = -1;
             break;
         case NRB_OPT_USE_HARDWARE_RT: break;  // accepted, ignored: there is no OptiX path
         default: return fail(NRB_ERR_INVALID, "unknown option");
@@ -1053,7 +1053,7 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     int launches;
     if (neural) launches = launch_neural_frame(f, r->net, r->lambertView, s, (r->tailMode == 1 && !debug_sync_enabled()) ? &r->segTail : nullptr, r->tailMode == 2,
                                                r->pathFeedback, r->tailMode == 2 ? r->pathTailBelow : 0);
-    else launches = launch_gt_frame(f, r->lambertView, s);
+    else launches = launch_gt_frame(f, r->lambertView, s, r->pathFeedback, r->pathTailBelow);
     if (r->denoise && !r->lambertView) launches += launch_denoise(f, s);
     if (r->gather.role != 0) {
         ++r->gather.frames;

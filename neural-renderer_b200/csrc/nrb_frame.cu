@@ -45,9 +45,13 @@ __global__ void __launch_bounds__(kTileThreads, 10) k_gt_primary(const __grid_co
 }
 
 __global__ void __launch_bounds__(kQueueThreads) k_gt_bounce(const __grid_constant__ Frame f, int bounce, int qin,
-                                                             int qout) {
+                                                             int qout, int* hostFeedback) {
     const FrameParams& fp = f.fp;
     const int n = f.st.counts[qin];
+    if (hostFeedback && blockIdx.x == 0 && threadIdx.x == 0) {  // paths entering this bounce: the host's hint for the next frames
+        hostFeedback[1] = n;
+        __threadfence_system();
+    }
     const SurfRec& cur = f.st.rec[bounce == 1 ? 0 : 1];
     const SurfRec& nxt = f.st.rec[1];
     unsigned int nTrace = 0, nVert = 0;
@@ -83,6 +87,55 @@ __global__ void __launch_bounds__(kQueueThreads) k_gt_bounce(const __grid_consta
             }
         }
         queue_push(f.st.queue[qout], f.st.counts + qout, alive, e);
+    }
+    stat_flush(f.st.stats + 0, nTrace);
+    stat_flush(f.st.stats + 2, nVert);
+}
+
+// Every ground-truth bounce after the first in ONE launch (the counterpart of k_path_tail): the few paths that survive
+// bounce 1 are spread one per warp while they are fewer than the warps, and each is carried through sample -> trace ->
+// integrate, bounce after bounce, with its vertex record in registers.  Same arithmetic as k_gt_bounce, so frames are
+// bit-identical; what goes away is a kernel boundary (and its latency floor of ~0.1 ms) per bounce.
+__global__ void __launch_bounds__(kQueueThreads) k_gt_tail(const __grid_constant__ Frame f, int firstBounce, int qin,
+                                                           int* hostFeedback) {
+    const FrameParams& fp = f.fp;
+    const int n = f.st.counts[qin];
+    if (hostFeedback && blockIdx.x == 0 && threadIdx.x == 0) {
+        hostFeedback[1] = n;
+        __threadfence_system();
+    }
+    const int lane = threadIdx.x & 31;
+    const int totalWarps = (gridDim.x * blockDim.x) >> 5, gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int per = (n + totalWarps - 1) / totalWarps;
+    per = per < 1 ? 1 : (per > 32 ? 32 : per);
+    unsigned int nTrace = 0, nVert = 0;
+    for (int base = gw * per; base < n; base += totalWarps * per) {
+        if (lane >= per || base + lane >= n) continue;
+        const int e = f.st.queue[qin][base + lane];
+        const ElemId id = queue_elem(fp, e);
+        const SurfRec& cur = f.st.rec[firstBounce == 1 ? 0 : 1];
+        const float4 P = cur.P[e], N = cur.N[e], C = cur.C[e];
+        const float2 M = cur.M[e];
+        V3 pos = f4v(P), nrm = f4v(N), alb = f4v(C), mp = v3(C.w, M.x, M.y);
+        V3 prev = firstBounce == 1 ? v3s(0.0f) : f4v(f.st.prevD[e]);
+        V3 T = f4v(f.st.T[e]);
+        for (int b = firstBounce; b <= fp.maxBounces; ++b) {
+            V3 org, wi, weight;
+            float pdf;
+            ++nVert;
+            if (!sample_vertex(f, id, pos, nrm, alb, mp, b == 1, prev, org, wi, weight, pdf)) break;
+            V3 hp, hn, ha, hm;
+            const bool hit = hit_record<TRACE_ANY, true>(f, f.classicSlot, org, wi, hp, hn, ha, hm);
+            ++nTrace;
+            V3 L = v3s(0.0f);
+            bool touchedL;
+            if (!hit) L = f4v(f.st.L[e]);
+            const bool alive = integrate_vertex(f, id, b, hit, wi, weight, T, L, touchedL);
+            if (touchedL) f.st.L[e] = make_float4(L.x, L.y, L.z, 0.0f);
+            if (!alive) break;
+            pos = hp; nrm = hn; alb = ha; mp = hm;
+            prev = wi;
+        }
     }
     stat_flush(f.st.stats + 0, nTrace);
     stat_flush(f.st.stats + 2, nVert);
@@ -331,7 +384,7 @@ int launch_lambert(const Frame& f, cudaStream_t s) {
     return 1;
 }
 
-int launch_gt_frame(const Frame& f, bool lambert, cudaStream_t s) {
+int launch_gt_frame(const Frame& f, bool lambert, cudaStream_t s, int* hostFeedback, int pathTailBelow) {
     const FrameParams& fp = f.fp;
     int launches = 0;
     cudaMemsetAsync(f.st.counts, 0, 16 * sizeof(int), s);
@@ -346,8 +399,17 @@ int launch_gt_frame(const Frame& f, bool lambert, cudaStream_t s) {
     int qin = 0;
     for (int b = 1; b <= fp.maxBounces; ++b) {
         const int qout = qin ^ 1;
+        if (b >= 2 && pathTailBelow > 0 && hostFeedback) {  // few paths left: the rest of the frame is one launch (see k_path_tail)
+            const int last = reinterpret_cast<volatile int*>(hostFeedback)[1];
+            if (last < 0 || last <= pathTailBelow) {
+                k_gt_tail<<<sm_count() * 8, kQueueThreads, 0, s>>>(f, b, qin, hostFeedback);
+                NRB_LAUNCHED("k_gt_tail", s);
+                ++launches;
+                break;
+            }
+        }
         cudaMemsetAsync(f.st.counts + qout, 0, sizeof(int), s);
-        k_gt_bounce<<<queue_grid(fp.nElems), kQueueThreads, 0, s>>>(f, b, qin, qout);
+        k_gt_bounce<<<queue_grid(fp.nElems), kQueueThreads, 0, s>>>(f, b, qin, qout, b == 2 ? hostFeedback : nullptr);
         NRB_LAUNCHED("k_gt_bounce", s);
         ++launches;
         qin = qout;

@@ -316,6 +316,26 @@ def test_path_tail_kernel_matches_per_stage_bounces(oracle_lib, kind, additional
     assert psnr8(out[1][0], orc.read_pixels()) > 30.0
 
 
+def test_gt_tail_kernel_is_bit_identical(oracle_lib):
+    """Ground-truth mode: bounces >= 2 as one launch (k_gt_tail) - same arithmetic per path, so the frame, the radiance
+    buffer and the counters equal the per-bounce launches exactly."""
+    scene = nrb.scenes.make_scene("ico", 4, additional=False, material=dict(metallic=0.8, roughness=0.25))
+    prod, orc, eye = make_pair(scene, oracle_lib, 192, 128, spp=2, bounces=5)
+    out = []
+    for below in (0, 1 << 30):
+        prod.set_path_tail(below)
+        prod.reset_samples()
+        prod.render(eye)
+        prod.render(eye)
+        out.append((prod.read_pixels().copy(), prod.read_buffer("path_radiance").copy(), prod.counters()))
+    prod.set_path_tail(49152)
+    assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1])
+    assert out[1][2]["kernels"] < out[0][2]["kernels"]
+    for key in ("path_vertices", "ray_segments"):
+        assert out[0][2][key] == out[1][2][key], (key, out[0][2], out[1][2])
+    assert out[0][2]["path_vertices"] > 10000
+
+
 def test_normal_cone_culling_changes_nothing(oracle_lib):
     """The shells' node pairs carry normal cones (csrc/nrb_scene.cuh): facing-mode traversals skip subtrees in which
     every triangle would fail the facing test.  The run-time-mode loop of the segment stages (parity hook modes 5-7)
