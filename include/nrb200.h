@@ -220,6 +220,9 @@ typedef enum nrb_option {
                                          bounce 2 with at most `value` paths (default 49152; 0 = always the per-stage kernels).  Needs
                                          NRB_OPT_TAIL_GRAPH = 2.  The network then runs on the mma.sync tile: outputs equal the
                                          tcgen05 kernels' within fp16 tolerance. */
+    NRB_OPT_TILE_ORDER = 16,          /* (new) 1 (default): the ground-truth primary pass hands its 8x4 tiles out most-expensive-first,
+                                         ordered by the clocks an earlier frame of the same camera measured per tile; 0: row-major.
+                                         Scheduling only: every pixel is computed by the same arithmetic either way. */
     NRB_OPT_LITERAL_BOUNCE_TRACES = 14 /* (new, parity hook) 1: the bounce entry runs every trace of
                                          checkBounceEarlyTermination / traceOuterShellEntryFromRays
                                          (src/cuda_renderer_neural.cu:503-553, 773-852) literally.  0 (default): traces

@@ -154,6 +154,11 @@ struct nrb_renderer {
     std::vector<DevBuf> pool;
     State st{};
     DevBuf accum, pixels, pixelsStaged;
+    // primary-pass tile order (ground-truth mode): costs of a frame, ids sorted by them, sort scratch
+    DevBuf tileCost, tileCostSorted, tileIds, tileOrder, tileSortTemp;
+    int tileCount = 0;
+    int tileOrderState = 0;  // 0 none, 2 order valid, 3 order usable but to be re-sorted from this frame's costs (camera moved)
+    bool tileOrderOn = true; // NRB_OPT_TILE_ORDER
     size_t stateElems = 0, accumPixels = 0, pixelCount = 0;
     int localHeight = 0;
 
@@ -736,6 +741,7 @@ int nrb_set_option(nrb_renderer* r, int option, int value) {
         case NRB_OPT_TAIL_GRAPH: r->tailMode = value < 0 ? 0 : (value > 2 ? 2 : value); break;
         case NRB_OPT_DENOISE: r->denoise = value != 0; break;
         case NRB_OPT_LITERAL_BOUNCE_TRACES: r->literalBounceTraces = value != 0; break;
+        case NRB_OPT_TILE_ORDER: r->tileOrderOn = value != 0; r->tileOrderState = 0; break;
         case NRB_OPT_PATH_TAIL:
             r->pathTailBelow = value < 0 ? 0 : value;
             if (r->pathFeedback) r->pathFeedback[0] = r->pathFeedback[1] = -1;
@@ -763,6 +769,7 @@ int nrb_get_option(const nrb_renderer* r, int option) {
         case NRB_OPT_DENOISE: return r->denoise ? 1 : 0;
         case NRB_OPT_LITERAL_BOUNCE_TRACES: return r->literalBounceTraces ? 1 : 0;
         case NRB_OPT_PATH_TAIL: return r->pathTailBelow;
+        case NRB_OPT_TILE_ORDER: return r->tileOrderOn ? 1 : 0;
         default: return 0;
     }
 }
@@ -852,6 +859,18 @@ int ensure_state(nrb_renderer* r, size_t nElems, size_t localPixels, size_t fram
         NRB_CUDA(r->pixels.alloc(framePixels * sizeof(uchar4)));
         NRB_CUDA(cudaMemsetAsync(r->pixels.p, 0, r->pixels.bytes, r->stream));
         r->pixelCount = framePixels;
+    }
+    {
+        const int tiles = static_cast<int>(((r->width + 7) / 8) * ((r->localHeight + 3) / 4)) * (nElems && localPixels ? static_cast<int>(nElems / localPixels) : 1);
+        if (tiles != r->tileCount) {
+            NRB_CUDA(r->tileCost.alloc(sizeof(unsigned int) * tiles));
+            NRB_CUDA(r->tileCostSorted.alloc(sizeof(unsigned int) * tiles));
+            NRB_CUDA(r->tileIds.alloc(sizeof(int) * tiles));
+            NRB_CUDA(r->tileOrder.alloc(sizeof(int) * tiles));
+            NRB_CUDA(r->tileSortTemp.alloc(tile_sort_temp_bytes(tiles)));
+            r->tileCount = tiles;
+            r->tileOrderState = 0;
+        }
     }
     r->st.accum = r->accum.as<float>();
     r->st.pixels = r->gather.role == 2 ? static_cast<uchar4*>(r->gather.remotePixels) : r->pixels.as<uchar4>();
@@ -977,6 +996,7 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
         r->envmapRotation != r->lastEnvmapRotation || r->useAdditionalMesh != r->lastUseAdditionalMesh) {
         rc = nrb_reset_samples(r);
         if (rc != NRB_OK) return rc;
+        if (r->tileOrderState == 2) r->tileOrderState = 3;  // keep the old order (still a permutation), re-sort after this frame
     }
     r->lastUseNeuralQuery = r->useNeuralQuery; r->lastLambertView = r->lambertView; r->lastBounceCount = maxBounces;
     r->lastSamplesPerPixel = spp; r->lastClassicMeshIndex = r->classicMeshIndex; r->lastEnvmapRotation = r->envmapRotation;
@@ -1018,6 +1038,8 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     f.env = EnvDev{r->envPixels.as<float>(), r->envW, r->envH, r->envmapRotation, r->envStrength};
     f.gmat = r->globalMaterial;
     f.st = r->st;
+    f.st.tileOrder = nullptr;
+    f.st.tileCost = nullptr;
     f.classicSlot = classicSlot;
     f.additionalEnabled = r->useAdditionalMesh ? 1 : 0;
     f.literalBounceTraces = r->literalBounceTraces ? 1 : 0;
@@ -1053,7 +1075,21 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     int launches;
     if (neural) launches = launch_neural_frame(f, r->net, r->lambertView, s, (r->tailMode == 1 && !debug_sync_enabled()) ? &r->segTail : nullptr, r->tailMode == 2,
                                                r->pathFeedback, r->tailMode == 2 ? r->pathTailBelow : 0);
-    else launches = launch_gt_frame(f, r->lambertView, s, r->pathFeedback, r->pathTailBelow);
+    else {
+        // primary tiles most-expensive-first, from the clocks an earlier frame of this camera measured (see k_gt_primary)
+        const bool order = r->tileOrderOn && r->tileCount > 0;
+        if (order) {
+            f.st.tileCost = r->tileOrderState == 2 ? nullptr : r->tileCost.as<unsigned int>();
+            f.st.tileOrder = r->tileOrderState >= 2 ? r->tileOrder.as<int>() : nullptr;
+        }
+        launches = launch_gt_frame(f, r->lambertView, s, r->pathFeedback, r->pathTailBelow);
+        if (order && r->tileOrderState != 2) {
+            if (launch_tile_sort(r->tileCost.as<unsigned int>(), r->tileCostSorted.as<unsigned int>(), r->tileIds.as<int>(),
+                                 r->tileOrder.as<int>(), r->tileCount, r->tileSortTemp.p, r->tileSortTemp.bytes, s) == 0)
+                r->tileOrderState = 2;
+            launches += 2;
+        }
+    }
     if (r->denoise && !r->lambertView) launches += launch_denoise(f, s);
     if (r->gather.role != 0) {
         ++r->gather.frames;

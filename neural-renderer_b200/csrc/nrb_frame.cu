@@ -15,6 +15,8 @@
 #include <cstdio>
 #include <cstdlib>
 
+#include <cub/device/device_radix_sort.cuh>
+
 namespace nrb {
 
 // ---------------------------------------------------------------------------------------------
@@ -23,7 +25,13 @@ __global__ void __launch_bounds__(kTileThreads, 10) k_gt_primary(const __grid_co
     const FrameParams& fp = f.fp;
     const int total = tile_count(fp);
     unsigned int nRays = 0;
-    for (int tile = next_tile(f.st.counts + 10, total); tile >= 0; tile = next_tile(f.st.counts + 10, total)) {
+    // Tiles are handed out most-expensive-first (longest processing time first): the cost of a primary tile - silhouette
+    // tiles walk hundreds of leaves, sky tiles none - is a property of the camera, so the clocks measured in one frame
+    // order the next ones.  With the natural order the launch ended on a few silhouette warps while the SMs were busy
+    // 54 % of its duration on average (ncu, profiles/r2_*).
+    for (int slot = next_tile(f.st.counts + 10, total); slot >= 0; slot = next_tile(f.st.counts + 10, total)) {
+    const int tile = f.st.tileOrder ? f.st.tileOrder[slot] : slot;
+    const long long t0 = clock64();
     const ElemId id = tile_elem_at(fp, tile);
     bool active = false;
     if (id.valid) {
@@ -40,8 +48,29 @@ __global__ void __launch_bounds__(kTileThreads, 10) k_gt_primary(const __grid_co
         active = hit && fp.maxBounces > 0;
     }
     queue_push(f.st.queue[0], f.st.counts + 0, active, id.e);
+    if (f.st.tileCost && (threadIdx.x & 31) == 0) {
+        const long long dt = clock64() - t0;
+        f.st.tileCost[tile] = dt > 0xffffffffll ? 0xffffffffu : static_cast<unsigned int>(dt);
+    }
     }
     stat_flush(f.st.stats + 0, nRays);
+}
+
+// tile ids sorted by descending cost (CUB radix sort, a library primitive); temp storage is grown on demand
+__global__ void k_iota(int* v, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) v[i] = i;
+}
+size_t tile_sort_temp_bytes(int n) {
+    size_t bytes = 0;
+    cub::DeviceRadixSort::SortPairsDescending(nullptr, bytes, static_cast<const unsigned int*>(nullptr), static_cast<unsigned int*>(nullptr),
+                                              static_cast<const int*>(nullptr), static_cast<int*>(nullptr), n);
+    return bytes;
+}
+int launch_tile_sort(const unsigned int* cost, unsigned int* costSorted, int* ids, int* order, int n, void* temp, size_t tempBytes,
+                     cudaStream_t s) {
+    k_iota<<<(n + 255) / 256, 256, 0, s>>>(ids, n);
+    return cub::DeviceRadixSort::SortPairsDescending(temp, tempBytes, cost, costSorted, ids, order, n, 0, 32, s) == cudaSuccess ? 0 : -1;
 }
 
 __global__ void __launch_bounds__(kQueueThreads) k_gt_bounce(const __grid_constant__ Frame f, int bounce, int qin,

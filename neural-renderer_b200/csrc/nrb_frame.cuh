@@ -69,6 +69,9 @@ struct SegTail {
 };
 int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStream_t s, SegTail* tail, bool fusedTail,
                         int* hostFeedback, int pathTailBelow);
+size_t tile_sort_temp_bytes(int n);
+int launch_tile_sort(const unsigned int* cost, unsigned int* costSorted, int* ids, int* order, int n, void* temp, size_t tempBytes,
+                     cudaStream_t s);
 int launch_finalize(const Frame& f, cudaStream_t s);
 int launch_lambert(const Frame& f, cudaStream_t s);
 int launch_denoise(const Frame& f, cudaStream_t s);

@@ -38,6 +38,8 @@ struct State {
     float2* segI;       // innerEnterT, innerHit flag (int bits)
     int* queue[4];      // 0/1: path queues (ping-pong), 2/3: segment queues (ping-pong)
     int* counts;        // [0..3] queue counts, [4..] scratch; cleared by the host per stage
+    const int* tileOrder;   // primary-pass 8x4 tiles, most expensive first (from tileCost of an earlier frame), or null
+    unsigned int* tileCost; // clocks each tile's warp spent in the primary pass of this frame
     unsigned long long* stats;  // [0] ray segments traced, [1] neural queries, [2] path vertices,
                                 // [3] node pairs fetched, [4] triangles fetched
     float* netIn;       // [slot][inputDims] fp32, slot = position in the segment queue

@@ -306,6 +306,10 @@ class RendererNeural:
         """Parity hook: run every trace of the reference's bounce entry, also those whose outcome is decided."""
         self._opt(K.OPT_LITERAL_BOUNCE_TRACES, int(v))
 
+    def set_tile_order(self, on: bool):
+        """Ground-truth primary pass: tiles most-expensive-first from an earlier frame's per-tile clocks (default on)."""
+        self._opt(K.OPT_TILE_ORDER, int(on))
+
     def set_path_tail(self, max_paths: int):
         """Bounces >= 2 as one kernel while the previous frames entered bounce 2 with at most `max_paths` paths
         (default 49152; 0 = always the per-stage kernels)."""

@@ -336,6 +336,32 @@ def test_gt_tail_kernel_is_bit_identical(oracle_lib):
     assert out[0][2]["path_vertices"] > 10000
 
 
+def test_tile_order_is_scheduling_only():
+    """NRB_OPT_TILE_ORDER: the ground-truth primary pass takes its tiles most-expensive-first from the second frame of
+    a camera on.  Pixels, hit buffers and accumulation are those of the row-major order, frame after frame, also
+    across a camera change and with several samples per pixel."""
+    scene = nrb.scenes.make_scene("ico", 5)
+    eye, basis = nrb.scenes.default_camera()
+    outs = []
+    for on in (False, True):
+        r = nrb.RendererNeural(scene)
+        r.resize(200, 120)
+        r.set_camera_basis(basis)
+        r.set_samples_per_pixel(2)
+        r.set_bounce_count(2)
+        r.set_tile_order(on)
+        r.set_capture(True)
+        frames = []
+        for k in range(5):
+            cam = eye if k < 3 else eye * np.float32(1.1)  # the camera moves before the fourth frame
+            r.render(cam)
+            frames.append((r.read_pixels().copy(), r.read_buffer("hit_positions").copy(), r.read_buffer("accum").copy()))
+        outs.append(frames)
+        r.close()
+    for a, b in zip(*outs):
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+
+
 def test_normal_cone_culling_changes_nothing(oracle_lib):
     """The shells' node pairs carry normal cones (csrc/nrb_scene.cuh): facing-mode traversals skip subtrees in which
     every triangle would fail the facing test.  The run-time-mode loop of the segment stages (parity hook modes 5-7)
