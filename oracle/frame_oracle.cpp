@@ -1173,6 +1173,13 @@ int orc_create(const nrb_nn_config* cfg, int /*device*/, orc_renderer** out) {
     auto* r = new orc_renderer();
     r->net.configure(cfg);
     r->pool.threads = 1;
+    {
+        // the reference zero-fills its parameter block at construction and renders with it until a checkpoint is
+        // loaded (cuda_renderer_neural.cu:1691-1697; neuralReady needs only the network and an outer shell, :2258)
+        std::vector<uint16_t> zeros(r->net.fileBytes() / 2, 0);
+        r->net.load(zeros.data(), true);
+        r->weightsLoaded = true;
+    }
     *out = r;
     return 0;
 }

@@ -163,6 +163,14 @@ def test_zero_weights_render_like_the_reference(oracle_lib):
     r.set_use_neural_query(True)
     r.render(eye)
     assert r.counters()["neural_queries"] > 0
+    o = nrb.RendererNeural(scene, lib=oracle_lib)  # the oracle mirrors the same rule
+    o.resize(96, 54)
+    o.set_camera_basis(basis)
+    o.set_use_neural_query(True)
+    o.render(eye)
+    assert o.counters()["neural_queries"] == r.counters()["neural_queries"]
+    assert np.array_equal(o.read_pixels(), r.read_pixels())
+    o.close()
     y = r.neural_query(np.random.RandomState(1).uniform(0, 1, (300, r.input_dims())).astype(np.float32))
     assert np.all(y.view(np.uint16) << 1 == 0)  # +-0
     r.close()
