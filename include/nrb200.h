@@ -223,6 +223,11 @@ typedef enum nrb_option {
     NRB_OPT_TILE_ORDER = 16,          /* (new) 1 (default): the ground-truth primary pass hands its 8x4 tiles out most-expensive-first,
                                          ordered by the clocks an earlier frame of the same camera measured per tile; 0: row-major.
                                          Scheduling only: every pixel is computed by the same arithmetic either way. */
+    NRB_OPT_FRAME_SLICES = 17,        /* (new) 0 (default) = automatic: 4 in ground-truth mode, 1 in neural mode (measured).
+                                         S > 1: the rows this renderer owns are dealt to S internal slices (16-row bands round-robin,
+                                         the multi-GPU tile rule) whose stage chains run concurrently on S streams, so the latency-
+                                         bound tails of one slice run under the throughput stages of another.  Same pixels.  Not with
+                                         NRB_OPT_PROFILE / CAPTURE / DENOISE or NRB_OPT_TAIL_GRAPH != 2 (the frame then runs unsliced). */
     NRB_OPT_LITERAL_BOUNCE_TRACES = 14 /* (new, parity hook) 1: the bounce entry runs every trace of
                                          checkBounceEarlyTermination / traceOuterShellEntryFromRays
                                          (src/cuda_renderer_neural.cu:503-553, 773-852) literally.  0 (default): traces

@@ -46,19 +46,27 @@ int fail(int code, const std::string& msg) {
 struct DevBuf {
     void* p = nullptr;
     size_t bytes = 0;
+    bool borrowed = false;  // an alias of another renderer's allocation (frame slices): never freed here
     DevBuf() = default;
     DevBuf(const DevBuf&) = delete;
     DevBuf& operator=(const DevBuf&) = delete;
-    DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes) { o.p = nullptr; o.bytes = 0; }
+    DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes), borrowed(o.borrowed) { o.p = nullptr; o.bytes = 0; o.borrowed = false; }
     DevBuf& operator=(DevBuf&& o) noexcept {
-        if (this != &o) { release(); p = o.p; bytes = o.bytes; o.p = nullptr; o.bytes = 0; }
+        if (this != &o) { release(); p = o.p; bytes = o.bytes; borrowed = o.borrowed; o.p = nullptr; o.bytes = 0; o.borrowed = false; }
         return *this;
     }
     ~DevBuf() { release(); }
     void release() {
-        if (p) cudaFree(p);
+        if (p && !borrowed) cudaFree(p);
         p = nullptr;
         bytes = 0;
+        borrowed = false;
+    }
+    void alias(void* ptr, size_t n) {
+        release();
+        p = ptr;
+        bytes = n;
+        borrowed = ptr != nullptr;
     }
     cudaError_t alloc(size_t n) {
         release();
@@ -99,6 +107,18 @@ struct MeshSlot {
 
 struct nrb_renderer {
     int device = 0;
+    // Frame slices (NRB_OPT_FRAME_SLICES = S > 1): the rows this renderer owns are dealt to S slice renderers - children
+    // with their own wavefront state, queues and stream, borrowing this renderer's scene, weights and frame buffer -
+    // through the very tile mechanism of the multi-GPU partition (virtual rank = rank + k * world of world * S).  Their
+    // stage chains run concurrently, so the latency-bound tails of one slice (the long rays that end a traversal
+    // launch, the later bounces) run under the throughput stages of another.  Pixels are those of the unsliced frame.
+    int slices = 0;        // NRB_OPT_FRAME_SLICES: 0 = automatic (4 in ground-truth mode, 1 in neural mode), else the count
+    int activeSlices = 1;  // what the current frame uses
+    std::vector<nrb_renderer*> kids;
+    nrb_renderer* parent = nullptr;
+    cudaEvent_t evFork = nullptr, evDone = nullptr;
+    uchar4* pixelsOverride = nullptr;
+    bool lastSliced = false;
     cudaStream_t stream = nullptr;
     cudaEvent_t evStart = nullptr, evStop = nullptr, evJoin = nullptr, evJoinIn = nullptr;
     // nrb_read_pixels_async: frame -> staging copy on `stream`, staging -> host on `copyStream`
@@ -562,6 +582,10 @@ int nrb_create(const nrb_nn_config* cfg, int device, nrb_renderer** out) {
 void nrb_destroy(nrb_renderer* r) {
     if (!r) return;
     cudaSetDevice(r->device);
+    for (nrb_renderer* k : r->kids) nrb_destroy(k);
+    r->kids.clear();
+    if (r->evFork) cudaEventDestroy(r->evFork);
+    if (r->evDone) cudaEventDestroy(r->evDone);
     if (r->stream) cudaStreamSynchronize(r->stream);
     if (r->evStart) cudaEventDestroy(r->evStart);
     if (r->evStop) cudaEventDestroy(r->evStop);
@@ -742,6 +766,7 @@ int nrb_set_option(nrb_renderer* r, int option, int value) {
         case NRB_OPT_DENOISE: r->denoise = value != 0; break;
         case NRB_OPT_LITERAL_BOUNCE_TRACES: r->literalBounceTraces = value != 0; break;
         case NRB_OPT_TILE_ORDER: r->tileOrderOn = value != 0; r->tileOrderState = 0; break;
+        case NRB_OPT_FRAME_SLICES: r->slices = value < 0 ? 0 : (value > 8 ? 8 : value); break;
         case NRB_OPT_PATH_TAIL:
             r->pathTailBelow = value < 0 ? 0 : value;
             if (r->pathFeedback) r->pathFeedback[0] = r->pathFeedback[1] = -1;
@@ -770,6 +795,7 @@ int nrb_get_option(const nrb_renderer* r, int option) {
         case NRB_OPT_LITERAL_BOUNCE_TRACES: return r->literalBounceTraces ? 1 : 0;
         case NRB_OPT_PATH_TAIL: return r->pathTailBelow;
         case NRB_OPT_TILE_ORDER: return r->tileOrderOn ? 1 : 0;
+        case NRB_OPT_FRAME_SLICES: return r->slices;
         default: return 0;
     }
 }
@@ -855,7 +881,7 @@ int ensure_state(nrb_renderer* r, size_t nElems, size_t localPixels, size_t fram
         r->accumPixels = localPixels;
         r->accumSampleCount = 0;
     }
-    if (framePixels != r->pixelCount) {
+    if (!r->parent && framePixels != r->pixelCount) {
         NRB_CUDA(r->pixels.alloc(framePixels * sizeof(uchar4)));
         NRB_CUDA(cudaMemsetAsync(r->pixels.p, 0, r->pixels.bytes, r->stream));
         r->pixelCount = framePixels;
@@ -873,7 +899,8 @@ int ensure_state(nrb_renderer* r, size_t nElems, size_t localPixels, size_t fram
         }
     }
     r->st.accum = r->accum.as<float>();
-    r->st.pixels = r->gather.role == 2 ? static_cast<uchar4*>(r->gather.remotePixels) : r->pixels.as<uchar4>();
+    r->st.pixels = r->parent ? r->pixelsOverride
+                             : (r->gather.role == 2 ? static_cast<uchar4*>(r->gather.remotePixels) : r->pixels.as<uchar4>());
     return NRB_OK;
 }
 
@@ -954,15 +981,44 @@ extern "C" {
 int nrb_reset_samples(nrb_renderer* r) {
     if (!r) return fail(NRB_ERR_INVALID, "null renderer");
     NRB_CUDA(cudaSetDevice(r->device));
+    for (nrb_renderer* k : r->kids) {
+        if (k->accum.p) NRB_CUDA(cudaMemsetAsync(k->accum.p, 0, k->accum.bytes, k->stream));
+        k->accumSampleCount = 0;
+    }
     if (r->accum.p) NRB_CUDA(cudaMemsetAsync(r->accum.p, 0, r->accum.bytes, r->stream));
     r->accumSampleCount = 0;
     return NRB_OK;
 }
 
+static int render_impl(nrb_renderer* r, const float cam_pos[3]);
+static int render_sliced(nrb_renderer* r, const float cam_pos[3]);
+
 int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     if (!r || !cam_pos) return fail(NRB_ERR_INVALID, "null argument");
     if (r->width <= 0 || r->height <= 0) return NRB_OK;  // the reference returns silently (:2086-2091)
     NRB_CUDA(cudaSetDevice(r->device));
+    // slices need the frame's stages to be plain launches on one stream each: not with the per-launch profiler, the
+    // debug capture buffers (whole-frame element order), the denoiser (whole-frame window) or the graph-driven tail
+    // Measured at 1080p: ground truth 1.25 -> 1.06 ms with 4 slices (6.03 -> 4.98 ms at 8 spp) - its
+    // traversal launches end on a few long silhouette rays, which the other slices' work covers; the neural path
+    // gets slower (1.39 -> 1.43 ms with 2): its stages already fill the machine and the query kernels of two slices
+    // cannot share an SM's shared memory.  Hence the automatic choice.
+    const bool neuralActive = r->useNeuralQuery && r->weightsLoaded && r->mesh[NRB_MESH_OUTER_SHELL].view.numTriangles > 0;
+    const int S = r->slices > 0 ? r->slices : (neuralActive ? 1 : 4);
+    const bool sliced = S > 1 && !r->profile && !r->capture && !r->denoise && !debug_sync_enabled() &&
+                        (r->tailMode == 2 || !neuralActive) && local_rows(r) >= 64 * S;
+    r->activeSlices = sliced ? S : 1;
+    if (sliced != r->lastSliced) {  // the accumulation lives in different buffers: start over
+        int rc = nrb_reset_samples(r);
+        if (rc != NRB_OK) return rc;
+        r->hasLastCamera = false;
+        for (nrb_renderer* k : r->kids) k->hasLastCamera = false;
+        r->lastSliced = sliced;
+    }
+    return sliced ? render_sliced(r, cam_pos) : render_impl(r, cam_pos);
+}
+
+static int render_impl(nrb_renderer* r, const float cam_pos[3]) {
     const int maxBounces = std::max(0, r->bounceCount);
     const int spp = r->samplesPerPixel <= 0 ? 1 : r->samplesPerPixel;
 
@@ -1056,11 +1112,15 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     }
     // symmetric join: whatever the caller enqueued on the legacy default stream since the last frame (an async copy or
     // a kernel reading devicePixels()) finishes before this frame may overwrite the buffers
-    NRB_CUDA(cudaEventRecord(r->evJoinIn, cudaStreamLegacy));
-    NRB_CUDA(cudaStreamWaitEvent(s, r->evJoinIn, 0));
+    if (!r->parent) {
+        NRB_CUDA(cudaEventRecord(r->evJoinIn, cudaStreamLegacy));
+        NRB_CUDA(cudaStreamWaitEvent(s, r->evJoinIn, 0));
+    }
     NRB_CUDA(cudaMemsetAsync(r->st.stats, 0, 16 * sizeof(unsigned long long), s));
     NRB_CUDA(cudaEventRecord(r->evStart, s));
-    if (r->gather.role == 1) {
+    if (r->parent) {
+        // a slice: the parent does the hand-shakes of the frame gather and the stream joins
+    } else if (r->gather.role == 1) {
         // everything the caller enqueued on this stream since the last frame has read it: peers may overwrite
         launch_gather_release(r->gather.sync.as<unsigned>(), r->gather.frames, s);
     } else if (r->gather.role == 2) {
@@ -1091,7 +1151,7 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
         }
     }
     if (r->denoise && !r->lambertView) launches += launch_denoise(f, s);
-    if (r->gather.role != 0) {
+    if (!r->parent && r->gather.role != 0) {
         ++r->gather.frames;
         if (r->gather.role == 2) launch_gather_signal(static_cast<unsigned*>(r->gather.remoteSync), s);
         else launch_gather_wait(r->gather.sync.as<unsigned>(), r->gather.frames * static_cast<unsigned>(r->gather.peers),
@@ -1107,7 +1167,119 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     r->lastNeural = neural;
     r->lastLaunches = launches;
     r->lastRayCount = static_cast<int>(nElems);
+    if (r->parent) return NRB_OK;
     // join to the legacy default stream: a following cudaMemcpy(devicePixels) sees the frame
+    NRB_CUDA(cudaEventRecord(r->evJoin, s));
+    NRB_CUDA(cudaStreamWaitEvent(cudaStreamLegacy, r->evJoin, 0));
+    return NRB_OK;
+}
+
+// One slice renderer: own stream, events and feedback block; everything else arrives through sync_slice.
+static nrb_renderer* make_slice(nrb_renderer* r) {
+    nrb_renderer* k = new nrb_renderer();
+    k->device = r->device;
+    k->parent = r;
+    if (cudaStreamCreateWithFlags(&k->stream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreate(&k->evStart) != cudaSuccess ||
+        cudaEventCreate(&k->evStop) != cudaSuccess || cudaEventCreateWithFlags(&k->evDone, cudaEventDisableTiming) != cudaSuccess) {
+        nrb_destroy(k);
+        return nullptr;
+    }
+    if (cudaHostAlloc(reinterpret_cast<void**>(&k->pathFeedback), 4 * sizeof(int), cudaHostAllocMapped) == cudaSuccess) {
+        k->pathFeedback[0] = k->pathFeedback[1] = -1;
+    } else {
+        k->pathFeedback = nullptr;
+        cudaGetLastError();
+    }
+    return k;
+}
+
+// Bring a slice up to date with its parent: scene views, weights (borrowed pointers), options, camera, tile.
+static int sync_slice(nrb_renderer* r, nrb_renderer* k, int index, uchar4* pixels) {
+    for (int m = 0; m < 4; ++m) {
+        k->mesh[m].view = r->mesh[m].view;
+        std::memcpy(k->mesh[m].boundsMin, r->mesh[m].boundsMin, 12);
+        std::memcpy(k->mesh[m].boundsMax, r->mesh[m].boundsMax, 12);
+        k->mesh[m].depth = r->mesh[m].depth;
+        k->mesh[m].closed = r->mesh[m].closed;
+    }
+    k->envPixels.alias(r->envPixels.p, r->envPixels.bytes);
+    k->envW = r->envW; k->envH = r->envH; k->envStrength = r->envStrength;
+    k->globalMaterial = r->globalMaterial;
+    k->cfg = r->cfg;
+    {
+        NetDev n = r->net;  // the slice keeps its own query scratch
+        n.xt = k->net.xt; n.xtRows = k->net.xtRows; n.encCursor = k->net.encCursor;
+        k->net = n;
+    }
+    k->gridParams = r->gridParams; k->mlpParams = r->mlpParams; k->weightsLoaded = r->weightsLoaded;
+    k->tailMode = r->tailMode; k->literalBounceTraces = r->literalBounceTraces; k->pathTailBelow = r->pathTailBelow;
+    k->tileOrderOn = r->tileOrderOn;
+    std::memcpy(k->fwd, r->fwd, 12); std::memcpy(k->right, r->right, 12); std::memcpy(k->up, r->up, 12);
+    k->fovY = r->fovY;
+    k->lambertView = r->lambertView; k->useNeuralQuery = r->useNeuralQuery; k->samplesPerPixel = r->samplesPerPixel;
+    k->bounceCount = r->bounceCount; k->classicMeshIndex = r->classicMeshIndex; k->envmapRotation = r->envmapRotation;
+    k->useConstantNeuralColor = r->useConstantNeuralColor; k->useDirectEnvColor = r->useDirectEnvColor;
+    k->useAdditionalMesh = r->useAdditionalMesh;
+    std::memcpy(k->constantNeuralColor, r->constantNeuralColor, 12);
+    std::memcpy(k->directEnvColor, r->directEnvColor, 12);
+    k->pixelsOverride = pixels;
+    int rc = NRB_OK;
+    if (k->width != r->width || k->height != r->height) rc = nrb_resize(k, r->width, r->height);
+    if (rc == NRB_OK) rc = nrb_set_tile(k, r->bandRows, r->rank + index * r->world, r->world * r->activeSlices);  // bands b with b % world == rank, dealt to the slices
+    return rc;
+}
+
+static int render_sliced(nrb_renderer* r, const float cam_pos[3]) {
+    const int S = r->activeSlices;
+    while (static_cast<int>(r->kids.size()) > S) { nrb_destroy(r->kids.back()); r->kids.pop_back(); }
+    while (static_cast<int>(r->kids.size()) < S) {
+        nrb_renderer* k = make_slice(r);
+        if (!k) return fail(NRB_ERR_CUDA, "slice renderer creation failed");
+        r->kids.push_back(k);
+    }
+    if (!r->evFork) NRB_CUDA(cudaEventCreateWithFlags(&r->evFork, cudaEventDisableTiming));
+    const size_t framePixels = static_cast<size_t>(r->width) * r->height;
+    if (framePixels != r->pixelCount) {
+        NRB_CUDA(cudaStreamSynchronize(r->stream));
+        NRB_CUDA(r->pixels.alloc(framePixels * sizeof(uchar4)));
+        NRB_CUDA(cudaMemsetAsync(r->pixels.p, 0, r->pixels.bytes, r->stream));
+        r->pixelCount = framePixels;
+    }
+    uchar4* target = r->gather.role == 2 ? static_cast<uchar4*>(r->gather.remotePixels) : r->pixels.as<uchar4>();
+    cudaStream_t s = r->stream;
+    NRB_CUDA(cudaEventRecord(r->evJoinIn, cudaStreamLegacy));
+    NRB_CUDA(cudaStreamWaitEvent(s, r->evJoinIn, 0));
+    NRB_CUDA(cudaEventRecord(r->evStart, s));
+    if (r->gather.role == 1) launch_gather_release(r->gather.sync.as<unsigned>(), r->gather.frames, s);
+    else if (r->gather.role == 2)
+        launch_gather_wait(static_cast<unsigned*>(r->gather.remoteSync) + 1, r->gather.frames, r->gather.sync.as<unsigned>() + 4, s);
+    NRB_CUDA(cudaEventRecord(r->evFork, s));
+    int launches = 0, rays = 0;
+    for (int i = 0; i < S; ++i) {
+        nrb_renderer* k = r->kids[i];
+        int rc = sync_slice(r, k, i, target);
+        if (rc != NRB_OK) return rc;
+        NRB_CUDA(cudaStreamWaitEvent(k->stream, r->evFork, 0));
+        rc = render_impl(k, cam_pos);
+        if (rc != NRB_OK) return rc;
+        NRB_CUDA(cudaEventRecord(k->evDone, k->stream));
+        NRB_CUDA(cudaStreamWaitEvent(s, k->evDone, 0));
+        launches += k->lastLaunches;
+        rays += k->lastRayCount;
+    }
+    if (r->gather.role != 0) {
+        ++r->gather.frames;
+        if (r->gather.role == 2) launch_gather_signal(static_cast<unsigned*>(r->gather.remoteSync), s);
+        else launch_gather_wait(r->gather.sync.as<unsigned>(), r->gather.frames * static_cast<unsigned>(r->gather.peers),
+                                r->gather.sync.as<unsigned>() + 4, s);
+        launches += 2;
+    }
+    NRB_CUDA(cudaEventRecord(r->evStop, s));
+    NRB_CUDA(cudaGetLastError());
+    r->accumSampleCount = r->kids[0]->accumSampleCount;
+    r->lastNeural = r->kids[0]->lastNeural;
+    r->lastLaunches = launches;
+    r->lastRayCount = rays;
     NRB_CUDA(cudaEventRecord(r->evJoin, s));
     NRB_CUDA(cudaStreamWaitEvent(cudaStreamLegacy, r->evJoin, 0));
     return NRB_OK;
@@ -1219,6 +1391,15 @@ int nrb_gather_detach(nrb_renderer* r) {
 }
 
 static int fetch_stats(nrb_renderer* r) {
+    if (r->lastSliced && !r->kids.empty()) {
+        for (uint64_t& v : r->lastStats) v = 0;
+        for (nrb_renderer* k : r->kids) {
+            int rc = fetch_stats(k);
+            if (rc != NRB_OK) return rc;
+            for (int i = 0; i < 8; ++i) r->lastStats[i] += k->lastStats[i];
+        }
+        return NRB_OK;
+    }
     if (!r->st.stats) return NRB_OK;
     NRB_CUDA(cudaSetDevice(r->device));
     NRB_CUDA(cudaStreamSynchronize(r->stream));

@@ -306,6 +306,10 @@ class RendererNeural:
         """Parity hook: run every trace of the reference's bounce entry, also those whose outcome is decided."""
         self._opt(K.OPT_LITERAL_BOUNCE_TRACES, int(v))
 
+    def set_frame_slices(self, n: int):
+        """Run the frame as n concurrent row-band slices on n streams inside this renderer (same pixels)."""
+        self._opt(K.OPT_FRAME_SLICES, int(n))
+
     def set_tile_order(self, on: bool):
         """Ground-truth primary pass: tiles most-expensive-first from an earlier frame's per-tile clocks (default on)."""
         self._opt(K.OPT_TILE_ORDER, int(on))

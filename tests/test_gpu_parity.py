@@ -336,6 +336,48 @@ def test_gt_tail_kernel_is_bit_identical(oracle_lib):
     assert out[0][2]["path_vertices"] > 10000
 
 
+@pytest.mark.parametrize("neural", [False, True], ids=["gt", "neural"])
+def test_frame_slices_give_the_unsliced_frame(neural):
+    """NRB_OPT_FRAME_SLICES: the frame as 2 or 3 concurrent row-band slices on as many streams - every pixel is computed
+    by the same kernels on the same inputs (global pixel indices and RNG streams), so frames, accumulation and counters
+    equal the unsliced renderer's exactly, frame after frame, and also combined with the multi-GPU tile partition."""
+    scene = nrb.scenes.make_scene("ico", 4, additional=True)
+    eye, basis = nrb.scenes.default_camera()
+
+    def run(slices, tile=None):
+        r = nrb.RendererNeural(scene)
+        r.resize(256, 208)
+        r.set_camera_basis(basis)
+        r.set_samples_per_pixel(2)
+        r.set_bounce_count(3)
+        r.set_path_tail(0)  # the same kernels in every slice whatever its path count
+        if neural:
+            r.load_weights(_weights())
+            r.set_use_neural_query(True)
+        if tile:
+            r.set_tile(16, *tile)
+        r.set_frame_slices(slices)
+        frames = []
+        for _ in range(3):
+            r.render(eye)
+            frames.append(r.read_pixels().copy())
+        c = r.counters()
+        r.close()
+        return frames, c
+
+    base, cb = run(1)
+    for s in (2, 3):
+        got, cg = run(s)
+        for a, b in zip(base, got):
+            assert np.array_equal(a, b), s
+        for key in ("ray_segments", "neural_queries", "path_vertices"):
+            assert cb[key] == cg[key], (key, cb, cg)
+    # slices inside a rank of a 2-GPU partition: still that rank's rows of the full frame
+    part, _ = run(2, tile=(1, 2))
+    rows = [y for y in range(208) if (y // 16) % 2 == 1]
+    assert np.array_equal(part[2][rows], base[2][rows])
+
+
 def test_tile_order_is_scheduling_only():
     """NRB_OPT_TILE_ORDER: the ground-truth primary pass takes its tiles most-expensive-first from the second frame of
     a camera on.  Pixels, hit buffers and accumulation are those of the row-major order, frame after frame, also
