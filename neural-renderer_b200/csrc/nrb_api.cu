@@ -1478,6 +1478,7 @@ extern "C" {
 
 int nrb_read_buffer(nrb_renderer* r, const char* name, void* dst, size_t bytes) {
     if (!r || !name || !dst) return fail(NRB_ERR_INVALID, "null argument");
+    if (r->lastSliced) return fail(NRB_ERR_STATE, "the last frame ran as concurrent slices: set NRB_OPT_CAPTURE = 1 before the frame to read its per-element buffers");
     if (!r->stateElems) return fail(NRB_ERR_STATE, "no frame has been rendered");
     NRB_CUDA(cudaSetDevice(r->device));
     NRB_CUDA(cudaStreamSynchronize(r->stream));

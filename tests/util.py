@@ -21,6 +21,8 @@ def make_pair(scene, oracle_lib, width, height, spp=1, bounces=0, neural=False, 
         if weights is not None:
             r.load_weights(weights)
         r.set_use_neural_query(neural)
+        if lib is None:
+            r.set_capture(True)  # the parity tests read per-element buffers (nrb_read_buffer): whole-frame element order, unsliced
         out.append(r)
     return out[0], out[1], eye
 
