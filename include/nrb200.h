@@ -332,6 +332,20 @@ int nrb_trace_rays_host(nrb_renderer* r, int slot, int mode, const float* origin
  * [input_dims x n]), outputs fp16 [n][16].  n need not be a multiple of 256. */
 int nrb_neural_query(nrb_renderer* r, const float* d_inputs, size_t n, void* d_outputs_fp16);
 int nrb_neural_query_host(nrb_renderer* r, const float* inputs, size_t n, void* outputs_fp16);
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  The same query as
+ * nrb_neural_query (split encode + tcgen05 MLP kernels), with the encoded-tile scratch in a file-scope
+ * static __device__ array of the library (8 MiB + 256 B, held by every GPU that loads the library until exit)
+ * instead of the renderer's cudaMalloc'ed buffer: the call allocates nothing (no cudaMalloc / cudaFree, no allocating
+ * library routine) and only enqueues a 64-byte memset and two kernels on the renderer's stream.
+ * Limits: n <= NRB_STATIC_QUERY_MAX queries per call, a network shape the split query supports (width 64 or 128,
+ * 2 or 4 features per level, encoded width <= 256) with weights loaded; anything else returns NRB_ERR_INVALID with a
+ * message in nrb_last_error().  All calls on a device share the one array (it keeps the last call's tiles; the
+ * cursors it must find at zero are cleared by the call): calls that overlap on the GPU - two streams, two renderers,
+ * or this call beside a running nrb_render of ANOTHER renderer is fine, but two static queries at once are not -
+ * race on it.  Inputs and outputs are the caller's device arrays, as for nrb_neural_query. */
+#define NRB_STATIC_QUERY_MAX 16384
+int nrb_neural_query_static(nrb_renderer* r, const float* d_inputs, size_t n, void* d_outputs_fp16);
 int nrb_input_dims(const nrb_renderer* r);
 int nrb_output_dims(const nrb_renderer* r);
 

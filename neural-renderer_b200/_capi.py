@@ -140,7 +140,7 @@ class Lib:
             "accum_sample_count": ([vp], C.c_uint32), "get_timings": ([vp, P(C.c_double), P(i), P(C.c_uint64)], i),
             "get_counters": ([vp, P(C.c_uint64)], i), "get_trace_stats": ([vp, P(C.c_uint64)], i), "read_buffer": ([vp, C.c_char_p, vp, sz], i),
             "trace_rays": ([vp, i, i, vp, vp, sz, vp], i), "trace_rays_host": ([vp, i, i, vp, vp, sz, vp], i),
-            "neural_query": ([vp, vp, sz, vp], i), "neural_query_host": ([vp, vp, sz, vp], i),
+            "neural_query": ([vp, vp, sz, vp], i), "neural_query_host": ([vp, vp, sz, vp], i), "neural_query_static": ([vp, vp, sz, vp], i),
             "input_dims": ([vp], i), "output_dims": ([vp], i), "sync": ([vp], i), "stream": ([vp], vp),
             "gather_export": ([vp, i, vp, sz], i), "gather_attach": ([vp, vp, sz], i), "gather_detach": ([vp], i),
             "build_bvh": ([vp, i, vp, i, vp, P(i), vp], i),

@@ -1571,6 +1571,19 @@ int nrb_neural_query(nrb_renderer* r, const float* d_inputs, size_t n, void* d_o
     return NRB_OK;
 }
 
+int nrb_neural_query_static(nrb_renderer* r, const float* d_inputs, size_t n, void* d_outputs_fp16) {
+    if (!r || !d_inputs || !d_outputs_fp16) return fail(NRB_ERR_INVALID, "null argument");
+    if (!r->weightsLoaded) return fail(NRB_ERR_STATE, "no weights loaded");
+    if (n > split_static_max_rows())
+        return fail(NRB_ERR_INVALID, "nrb_neural_query_static: n exceeds NRB_STATIC_QUERY_MAX (16384 queries per call)");
+    NRB_CUDA(cudaSetDevice(r->device));
+    const char* why = nullptr;
+    const int rc = launch_split_query_static(r->net, d_inputs, n, static_cast<__half*>(d_outputs_fp16), r->stream, &why);
+    if (rc < 0) return fail(rc == -2 ? NRB_ERR_CUDA : NRB_ERR_INVALID, why ? why : "static-scratch query refused");
+    NRB_CUDA(cudaGetLastError());
+    return NRB_OK;
+}
+
 int nrb_neural_query_host(nrb_renderer* r, const float* inputs, size_t n, void* outputs_fp16) {
     if (!r || !inputs || !outputs_fp16) return fail(NRB_ERR_INVALID, "null argument");
     if (n == 0) return NRB_OK;

@@ -54,6 +54,11 @@ size_t split_packed_bytes(const NetDev& net);
 size_t split_xt_bytes(const NetDev& net, size_t rows);           // rows rounded up to 128 inside
 int split_prepack(const NetDev& net, void* packedW, cudaStream_t s);
 int launch_split_query(const NetDev& net, const float* in, size_t n, const int* dCount, __half* out, cudaStream_t s);
+// The same two kernels with the encoded tiles and cursors in a file-scope __device__ array of nrb_query_split.cu
+// (nrb_neural_query_static): no allocation in the call, at most split_static_max_rows() rows.  < 0 = refused
+// (-1 shape or size, -2 CUDA), *why says it.
+int launch_split_query_static(const NetDev& net, const float* in, size_t n, __half* out, cudaStream_t s, const char** why);
+size_t split_static_max_rows();
 // Bytes of dynamic shared memory the query kernel needs for this network (0 = unsupported shape).
 size_t neural_query_smem(const NetDev& net, int* warpsOut);
 

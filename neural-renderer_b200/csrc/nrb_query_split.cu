@@ -678,4 +678,65 @@ int launch_split_query(const NetDev& net, const float* in, size_t n, const int* 
     return launches;
 }
 
+// ---- the split query on static scratch (nrb_neural_query_static: no allocation inside the call) ----------
+// The encoded tiles and the level cursors live in ONE file-scope device array instead of the renderer's cudaMalloc'ed
+// buffers: 16 384 rows of at most 512 bytes (EK <= 256 encoded fp16 values), then the cursors.  Every GPU that loads
+// the library holds these 8 MiB + 256 B until exit.  All calls on a device share the array: calls that overlap on the
+// GPU (two streams, two renderers) race on it.
+constexpr size_t kStaticRows = 16384;
+constexpr size_t kStaticRowBytes = 512;
+constexpr size_t kStaticXtBytes = kStaticRows * kStaticRowBytes;
+static __device__ __align__(256) unsigned char g_staticScratch[kStaticXtBytes + 256];
+
+size_t split_static_max_rows() { return kStaticRows; }
+
+// g_staticScratch is a host-side stand-in here, not a device address: ask the runtime once per device, with that
+// device current (the caller's cudaSetDevice), and keep the answer.
+static cudaError_t static_scratch_address(unsigned char** out) {
+    static unsigned char* cached[64] = {nullptr};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (!cached[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_staticScratch);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        cached[dev] = static_cast<unsigned char*>(p);
+    }
+    *out = cached[dev];
+    return cudaSuccess;
+}
+
+int launch_split_query_static(const NetDev& net, const float* in, size_t n, __half* out, cudaStream_t s, const char** why) {
+    *why = nullptr;
+    if (n == 0) return 0;
+    if (!net.packedW || !split_query_supported(net)) {
+        *why = "the static-scratch query needs a network shape the split query supports (width 64/128, 2 or 4 features)";
+        return -1;
+    }
+    if (n > kStaticRows || split_xt_bytes(net, n) > kStaticXtBytes) {
+        *why = "too many queries for the static scratch (at most 16384 per call, encoded width <= 256)";
+        return -1;
+    }
+    unsigned char* base = nullptr;
+    const cudaError_t e = static_scratch_address(&base);
+    if (e != cudaSuccess) {
+        *why = cudaGetErrorString(e);
+        return -2;
+    }
+    NetDev tmp = net;
+    tmp.debug = 0;
+    tmp.xt = base;
+    tmp.xtRows = static_cast<uint32_t>((n + kTileM - 1) / kTileM * kTileM);
+    tmp.encCursor = reinterpret_cast<int*>(base + kStaticXtBytes);
+    // the cursors must be zero at launch; k_query_mlp leaves them so, but a call that failed half-way would not have
+    if (cudaMemsetAsync(tmp.encCursor, 0, kMaxLevels * sizeof(int), s) != cudaSuccess) {
+        *why = "cudaMemsetAsync on the static scratch failed";
+        return -2;
+    }
+    return launch_split_query(tmp, in, n, nullptr, out, s);
+}
+
 }  // namespace nrb
