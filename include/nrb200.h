@@ -228,6 +228,13 @@ typedef enum nrb_option {
                                          the multi-GPU tile rule) whose stage chains run concurrently on S streams, so the latency-
                                          bound tails of one slice run under the throughput stages of another.  Same pixels.  Not with
                                          NRB_OPT_PROFILE / CAPTURE / DENOISE or NRB_OPT_TAIL_GRAPH != 2 (the frame then runs unsliced). */
+    NRB_OPT_PIPELINE = 18,            /* (new) 1 (default): consecutive neural frames are pipelined - a frame's stages up to the end of
+                                         bounce 1 run on a second stream and alternate between two wavefront-state buffers, its end
+                                         (the later bounces in k_path_tail, finalize) stays on nrb_stream(), so frame k+1 starts under
+                                         the latency-bound end of frame k.  Frames still COMPLETE in order on nrb_stream(); pixels and
+                                         accumulation are those of the unpipelined frames, bit for bit.  0: one stream, one buffer.
+                                         Not with NRB_OPT_PROFILE / CAPTURE, NRB_OPT_TAIL_GRAPH != 2, the lambert view or ground-truth
+                                         mode (those frames run unpipelined). */
     NRB_OPT_LITERAL_BOUNCE_TRACES = 14 /* (new, parity hook) 1: the bounce entry runs every trace of
                                          checkBounceEarlyTermination / traceOuterShellEntryFromRays
                                          (src/cuda_renderer_neural.cu:503-553, 773-852) literally.  0 (default): traces

@@ -93,7 +93,8 @@ SLOT_ORIGINAL, SLOT_INNER, SLOT_OUTER, SLOT_ADDITIONAL = 0, 1, 2, 3
 TRACE_ANY, TRACE_FORWARD_ONLY, TRACE_BACKWARD_ONLY = 0, 1, 2
 (OPT_USE_NEURAL_QUERY, OPT_SAMPLES_PER_PIXEL, OPT_BOUNCE_COUNT, OPT_LAMBERT_VIEW, OPT_CLASSIC_MESH_INDEX,
  OPT_USE_ADDITIONAL_MESH, OPT_USE_CONSTANT_NEURAL_COLOR, OPT_USE_DIRECT_ENV_COLOR, OPT_CAPTURE,
- OPT_USE_HARDWARE_RT, OPT_PROFILE, OPT_QUERY_KERNEL, OPT_TAIL_GRAPH, OPT_DENOISE, OPT_LITERAL_BOUNCE_TRACES, OPT_PATH_TAIL, OPT_TILE_ORDER, OPT_FRAME_SLICES) = range(18)
+ OPT_USE_HARDWARE_RT, OPT_PROFILE, OPT_QUERY_KERNEL, OPT_TAIL_GRAPH, OPT_DENOISE, OPT_LITERAL_BOUNCE_TRACES, OPT_PATH_TAIL, OPT_TILE_ORDER, OPT_FRAME_SLICES,
+ OPT_PIPELINE) = range(19)
 
 PRODUCT_LIB = os.path.join(HERE, "libnrb200.so")
 

@@ -121,6 +121,19 @@ struct nrb_renderer {
     bool lastSliced = false;
     cudaStream_t stream = nullptr;
     cudaEvent_t evStart = nullptr, evStop = nullptr, evJoin = nullptr, evJoinIn = nullptr;
+    // Frame pipelining (NRB_OPT_PIPELINE, neural mode): the frame's stages up to the end of bounce 1 run on `early`, its
+    // end (k_path_tail, finalize) on `stream` behind them, and consecutive frames alternate between two wavefront-state
+    // buffers - so frame k+1 starts under the latency-bound end of frame k.  `stream` stays the stream every frame
+    // COMPLETES on, in order (read-backs, gather, nrb_sync and callers' events on nrb_stream() keep their meaning); work
+    // other entry points enqueue on it between frames is waited for by the next frame's early part (`touched`).
+    int pipeline = 1;      // 2 (experiment): two early streams - a frame's early part may run beside the WHOLE previous frame
+    cudaStream_t early = nullptr, early2 = nullptr;
+    cudaEvent_t evSplit = nullptr, evTouch = nullptr, evFrameDone[2] = {nullptr, nullptr};
+    bool frameDoneValid[2] = {false, false};
+    bool touched = true;   // something other than a pipelined frame was enqueued on `stream` since the last frame
+    int parity = 0;        // which state buffer the last frame used
+    State stBuf[2];
+    bool stBufValid[2] = {false, false};
     // nrb_read_pixels_async: frame -> staging copy on `stream`, staging -> host on `copyStream`
     cudaStream_t copyStream = nullptr;
     cudaEvent_t evStaged = nullptr, evCopied = nullptr;
@@ -146,6 +159,7 @@ struct nrb_renderer {
     nrb_nn_config cfg{};
     NetDev net{};
     DevBuf grid, mlp, packedW, xt, encCur;
+    DevBuf xt2, encCur2;  // the second query scratch of deep-pipelined frames (NRB_OPT_PIPELINE = 2)
     SegTail segTail;
     int tailMode = 2;  // NRB_OPT_TAIL_GRAPH: 0 fixed loop, 1 conditional WHILE graph, 2 fused tail kernel
     int pathTailBelow = 49152;  // NRB_OPT_PATH_TAIL: bounces >= 2 run as one kernel while they start with at most this many paths
@@ -541,7 +555,13 @@ int nrb_create(const nrb_nn_config* cfg, int device, nrb_renderer** out) {
     r->device = device;
     int rc = configure_network(r, cfg);
     if (rc != NRB_OK) { delete r; return rc; }
-    if (cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking) != cudaSuccess ||
+    if (cudaStreamCreateWithFlags(&r->early, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&r->early2, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&r->evSplit, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&r->evTouch, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&r->evFrameDone[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&r->evFrameDone[1], cudaEventDisableTiming) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreate(&r->evStart) != cudaSuccess || cudaEventCreate(&r->evStop) != cudaSuccess ||
         cudaEventCreateWithFlags(&r->evJoin, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&r->evJoinIn, cudaEventDisableTiming) != cudaSuccess) {
@@ -586,7 +606,15 @@ void nrb_destroy(nrb_renderer* r) {
     r->kids.clear();
     if (r->evFork) cudaEventDestroy(r->evFork);
     if (r->evDone) cudaEventDestroy(r->evDone);
+    if (r->early) cudaStreamSynchronize(r->early);
+    if (r->early2) cudaStreamSynchronize(r->early2);
     if (r->stream) cudaStreamSynchronize(r->stream);
+    if (r->early) cudaStreamDestroy(r->early);
+    if (r->early2) cudaStreamDestroy(r->early2);
+    if (r->evSplit) cudaEventDestroy(r->evSplit);
+    if (r->evTouch) cudaEventDestroy(r->evTouch);
+    for (cudaEvent_t e : r->evFrameDone)
+        if (e) cudaEventDestroy(e);
     if (r->evStart) cudaEventDestroy(r->evStart);
     if (r->evStop) cudaEventDestroy(r->evStop);
     if (r->evJoin) cudaEventDestroy(r->evJoin);
@@ -605,6 +633,7 @@ void nrb_destroy(nrb_renderer* r) {
 
 int nrb_update_mesh(nrb_renderer* r, int slot, const nrb_mesh_desc* d) {
     if (!r || slot < 0 || slot >= NRB_MESH_SLOT_COUNT) return fail(NRB_ERR_INVALID, "bad renderer/slot");
+    r->touched = true;  // the next pipelined frame waits for what this call enqueues
     NRB_CUDA(cudaSetDevice(r->device));
     NRB_CUDA(cudaStreamSynchronize(r->stream));
     MeshSlot& m = r->mesh[slot];
@@ -661,6 +690,7 @@ int nrb_update_mesh(nrb_renderer* r, int slot, const nrb_mesh_desc* d) {
 
 int nrb_update_env(nrb_renderer* r, const float* rgb, int width, int height, float strength) {
     if (!r) return fail(NRB_ERR_INVALID, "null renderer");
+    r->touched = true;  // the next pipelined frame waits for what this call enqueues
     NRB_CUDA(cudaSetDevice(r->device));
     NRB_CUDA(cudaStreamSynchronize(r->stream));
     r->envPixels.release();
@@ -685,6 +715,7 @@ size_t nrb_weights_file_bytes(const nrb_renderer* r) { return (r->gridParams + r
 
 int nrb_load_weights(nrb_renderer* r, const void* fp16, size_t bytes, int swap_order) {
     if (!r || !fp16) return fail(NRB_ERR_INVALID, "null argument");
+    r->touched = true;  // the next pipelined frame waits for what this call enqueues
     const size_t expect = nrb_weights_file_bytes(r);
     if (bytes != expect)
         return fail(NRB_ERR_SIZE, "Weights file size mismatch: expected " + std::to_string(expect) + " bytes, got " +
@@ -724,6 +755,7 @@ int nrb_load_weights_file(nrb_renderer* r, const char* path, int swap_order) {
 
 int nrb_resize(nrb_renderer* r, int width, int height) {
     if (!r) return fail(NRB_ERR_INVALID, "null renderer");
+    r->touched = true;  // the next pipelined frame waits for what this call enqueues
     if (width == r->width && height == r->height) return NRB_OK;
     NRB_CUDA(cudaSetDevice(r->device));
     NRB_CUDA(cudaStreamSynchronize(r->stream));
@@ -767,6 +799,7 @@ int nrb_set_option(nrb_renderer* r, int option, int value) {
         case NRB_OPT_LITERAL_BOUNCE_TRACES: r->literalBounceTraces = value != 0; break;
         case NRB_OPT_TILE_ORDER: r->tileOrderOn = value != 0; r->tileOrderState = 0; break;
         case NRB_OPT_FRAME_SLICES: r->slices = value < 0 ? 0 : (value > 8 ? 8 : value); break;
+        case NRB_OPT_PIPELINE: r->pipeline = value < 0 ? 0 : (value > 2 ? 2 : value); break;
         case NRB_OPT_PATH_TAIL:
             r->pathTailBelow = value < 0 ? 0 : value;
             if (r->pathFeedback) r->pathFeedback[0] = r->pathFeedback[1] = -1;
@@ -796,6 +829,7 @@ int nrb_get_option(const nrb_renderer* r, int option) {
         case NRB_OPT_PATH_TAIL: return r->pathTailBelow;
         case NRB_OPT_TILE_ORDER: return r->tileOrderOn ? 1 : 0;
         case NRB_OPT_FRAME_SLICES: return r->slices;
+        case NRB_OPT_PIPELINE: return r->pipeline;
         default: return 0;
     }
 }
@@ -806,6 +840,7 @@ int nrb_set_direct_env_color(nrb_renderer* r, const float rgb[3]) { std::memcpy(
 
 int nrb_set_tile(nrb_renderer* r, int band_rows, int rank, int world) {
     if (!r || band_rows <= 0 || world <= 0 || rank < 0 || rank >= world) return fail(NRB_ERR_INVALID, "bad tile spec");
+    r->touched = true;  // the next pipelined frame waits for what this call enqueues
     if (band_rows != r->bandRows || rank != r->rank || world != r->world) {
         r->bandRows = band_rows; r->rank = rank; r->world = world;
         r->pool.clear();
@@ -846,10 +881,19 @@ namespace {
 
 // ensureNetworkBuffers / ensureAccumBuffer (src/cuda_renderer_neural.cu:2826-2975): one pool of
 // 16-byte-record SoA arrays sized for the elements this renderer owns.
-int ensure_state(nrb_renderer* r, size_t nElems, size_t localPixels, size_t framePixels) {
+int ensure_state(nrb_renderer* r, size_t nElems, size_t localPixels, size_t framePixels, int buffers) {
     if (nElems != r->stateElems) {
+        if (r->early) NRB_CUDA(cudaStreamSynchronize(r->early));
+        if (r->stream) NRB_CUDA(cudaStreamSynchronize(r->stream));
         r->pool.clear();
         r->st = State{};
+        r->stBuf[0] = r->stBuf[1] = State{};
+        r->stBufValid[0] = r->stBufValid[1] = false;
+        r->frameDoneValid[0] = r->frameDoneValid[1] = false;
+        r->stateElems = nElems;
+    }
+    for (int b = 0; b < buffers; ++b) {
+        if (r->stBufValid[b]) continue;
         const size_t n = (nElems + 255) / 256 * 256;
         auto take = [&](size_t bytes, void** out) -> cudaError_t {
             r->pool.emplace_back();
@@ -857,7 +901,7 @@ int ensure_state(nrb_renderer* r, size_t nElems, size_t localPixels, size_t fram
             *out = r->pool.back().p;
             return e;
         };
-        State& s = r->st;
+        State& s = r->stBuf[b];
         for (int k = 0; k < 3; ++k) {
             NRB_CUDA(take(n * 16, reinterpret_cast<void**>(&s.rec[k].P)));
             NRB_CUDA(take(n * 16, reinterpret_cast<void**>(&s.rec[k].N)));
@@ -873,7 +917,7 @@ int ensure_state(nrb_renderer* r, size_t nElems, size_t localPixels, size_t fram
         NRB_CUDA(take(16 * sizeof(unsigned long long), reinterpret_cast<void**>(&s.stats)));
         NRB_CUDA(take(n * r->net.inputDims * sizeof(float), reinterpret_cast<void**>(&s.netIn)));
         NRB_CUDA(take(n * 16 * sizeof(__half), reinterpret_cast<void**>(&s.netOut)));
-        r->stateElems = nElems;
+        r->stBufValid[b] = true;
     }
     if (localPixels != r->accumPixels) {
         NRB_CUDA(r->accum.alloc(localPixels * 3 * sizeof(float)));
@@ -898,9 +942,13 @@ int ensure_state(nrb_renderer* r, size_t nElems, size_t localPixels, size_t fram
             r->tileOrderState = 0;
         }
     }
-    r->st.accum = r->accum.as<float>();
-    r->st.pixels = r->parent ? r->pixelsOverride
-                             : (r->gather.role == 2 ? static_cast<uchar4*>(r->gather.remotePixels) : r->pixels.as<uchar4>());
+    for (int b = 0; b < 2; ++b) {
+        r->stBuf[b].accum = r->accum.as<float>();
+        r->stBuf[b].pixels = r->parent ? r->pixelsOverride
+                                       : (r->gather.role == 2 ? static_cast<uchar4*>(r->gather.remotePixels) : r->pixels.as<uchar4>());
+    }
+    if (!r->stBufValid[r->parity]) r->parity = 0;
+    r->st = r->stBuf[r->parity];
     return NRB_OK;
 }
 
@@ -923,6 +971,13 @@ int ensure_xt(nrb_renderer* r, size_t rows) {
     if (!r->encCur.p) {
         NRB_CUDA(r->encCur.alloc(kMaxLevels * sizeof(int)));
         NRB_CUDA(cudaMemsetAsync(r->encCur.p, 0, r->encCur.bytes, r->stream));
+    }
+    if (r->pipeline >= 2 && (r->xt2.bytes < need || !r->encCur2.p)) {
+        NRB_CUDA(cudaStreamSynchronize(r->stream));
+        NRB_CUDA(r->xt2.alloc(r->xt.bytes));
+        NRB_CUDA(r->encCur2.alloc(kMaxLevels * sizeof(int)));
+        NRB_CUDA(cudaMemsetAsync(r->encCur2.p, 0, r->encCur2.bytes, r->stream));
+        r->touched = true;
     }
     r->net.encCursor = r->encCur.as<int>();
     r->net.xt = r->xt.p;
@@ -1015,6 +1070,7 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
         for (nrb_renderer* k : r->kids) k->hasLastCamera = false;
         r->lastSliced = sliced;
     }
+    if (sliced) r->touched = true;  // the slices' streams join `stream`: a pipelined frame after them waits for it
     return sliced ? render_sliced(r, cam_pos) : render_impl(r, cam_pos);
 }
 
@@ -1033,7 +1089,13 @@ static int render_impl(nrb_renderer* r, const float cam_pos[3]) {
     const size_t localPixels = static_cast<size_t>(r->width) * r->localHeight;
     const size_t nElems = localPixels * spp;
     if (nElems >= (1ull << 31)) return fail(NRB_ERR_INVALID, "width*height*spp exceeds 2^31 elements; render in smaller spp batches");
-    int rc = ensure_state(r, nElems, localPixels, framePixels);
+    const MeshSlot& outer = r->mesh[NRB_MESH_OUTER_SHELL];
+    const bool neural = r->useNeuralQuery && r->weightsLoaded && outer.view.numTriangles > 0;  // (:2258-2260)
+    // pipelined frames: see nrb_renderer::pipeline.  Plain launches on two streams only - not with the per-launch
+    // profiler, the capture buffers, the graph-driven tail or as a slice.
+    const bool pipelined = r->pipeline && neural && !r->parent && !r->lambertView && !r->profile && !r->capture &&
+                           r->tailMode == 2 && !debug_sync_enabled() && r->early != nullptr;
+    int rc = ensure_state(r, nElems, localPixels, framePixels, pipelined ? 2 : 1);
     if (rc != NRB_OK) return rc;
     if (r->useNeuralQuery && r->weightsLoaded) {
         rc = ensure_xt(r, nElems);
@@ -1063,7 +1125,6 @@ static int render_impl(nrb_renderer* r, const float cam_pos[3]) {
     Frame f{};
     FrameParams& fp = f.fp;
     fp.camPos = to_v3(cam_pos); fp.camForward = to_v3(r->fwd); fp.camRight = to_v3(r->right); fp.camUp = to_v3(r->up);
-    const MeshSlot& outer = r->mesh[NRB_MESH_OUTER_SHELL];
     fp.outerMin = to_v3(outer.boundsMin);
     for (int k = 0; k < 3; ++k) {  // (:2171-2178)
         const float ext = outer.boundsMax[k] - outer.boundsMin[k];
@@ -1093,6 +1154,10 @@ static int render_impl(nrb_renderer* r, const float cam_pos[3]) {
     if (!r->useAdditionalMesh) f.mesh[NRB_MESH_ADDITIONAL] = MeshDev{};
     f.env = EnvDev{r->envPixels.as<float>(), r->envW, r->envH, r->envmapRotation, r->envStrength};
     f.gmat = r->globalMaterial;
+    if (pipelined) {
+        r->parity ^= 1;
+        r->st = r->stBuf[r->parity];
+    }
     f.st = r->st;
     f.st.tileOrder = nullptr;
     f.st.tileCost = nullptr;
@@ -1101,7 +1166,23 @@ static int render_impl(nrb_renderer* r, const float cam_pos[3]) {
     f.literalBounceTraces = r->literalBounceTraces ? 1 : 0;
     f.literalSegExits = (r->literalBounceTraces || !outer.closed) ? 1 : 0;
 
-    cudaStream_t s = r->stream;
+    // sOut: the stream the frame completes on.  s: where it starts (the same stream unless pipelined).
+    cudaStream_t sOut = r->stream;
+    cudaStream_t s = pipelined ? ((r->pipeline >= 2 && r->parity) ? r->early2 : r->early) : r->stream;
+    NetDev net = r->net;
+    if (pipelined && r->pipeline >= 2 && r->parity && r->xt2.p && r->xt2.bytes == r->xt.bytes) {
+        net.xt = r->xt2.p;
+        net.encCursor = r->encCur2.as<int>();
+    }
+    if (pipelined) {
+        if (r->touched) {  // scene / weight uploads, batch queries or an unpipelined frame since the last frame: wait for them
+            NRB_CUDA(cudaEventRecord(r->evTouch, sOut));
+            NRB_CUDA(cudaStreamWaitEvent(s, r->evTouch, 0));
+        }
+        // this state buffer is free once the frame before the last has completed
+        if (r->frameDoneValid[r->parity]) NRB_CUDA(cudaStreamWaitEvent(s, r->evFrameDone[r->parity], 0));
+    }
+    r->touched = !pipelined;
     if (r->profile) {
         rc = drain_profiler(r);
         if (rc != NRB_OK) return rc;
@@ -1114,7 +1195,7 @@ static int render_impl(nrb_renderer* r, const float cam_pos[3]) {
     // a kernel reading devicePixels()) finishes before this frame may overwrite the buffers
     if (!r->parent) {
         NRB_CUDA(cudaEventRecord(r->evJoinIn, cudaStreamLegacy));
-        NRB_CUDA(cudaStreamWaitEvent(s, r->evJoinIn, 0));
+        NRB_CUDA(cudaStreamWaitEvent(sOut, r->evJoinIn, 0));  // only the end of the frame (finalize) writes them
     }
     NRB_CUDA(cudaMemsetAsync(r->st.stats, 0, 16 * sizeof(unsigned long long), s));
     NRB_CUDA(cudaEventRecord(r->evStart, s));
@@ -1122,19 +1203,18 @@ static int render_impl(nrb_renderer* r, const float cam_pos[3]) {
         // a slice: the parent does the hand-shakes of the frame gather and the stream joins
     } else if (r->gather.role == 1) {
         // everything the caller enqueued on this stream since the last frame has read it: peers may overwrite
-        launch_gather_release(r->gather.sync.as<unsigned>(), r->gather.frames, s);
+        launch_gather_release(r->gather.sync.as<unsigned>(), r->gather.frames, sOut);
     } else if (r->gather.role == 2) {
-        launch_gather_wait(static_cast<unsigned*>(r->gather.remoteSync) + 1, r->gather.frames, r->gather.sync.as<unsigned>() + 4, s);
+        launch_gather_wait(static_cast<unsigned*>(r->gather.remoteSync) + 1, r->gather.frames, r->gather.sync.as<unsigned>() + 4, sOut);
     }
     if (r->profile) {
         r->prof.marks = 0;
         NRB_CUDA(cudaEventRecord(r->prof.ev[0], s));
         set_stage_profiler(&r->prof);
     }
-    const bool neural = r->useNeuralQuery && r->weightsLoaded && outer.view.numTriangles > 0;  // (:2258-2260)
     int launches;
-    if (neural) launches = launch_neural_frame(f, r->net, r->lambertView, s, (r->tailMode == 1 && !debug_sync_enabled()) ? &r->segTail : nullptr, r->tailMode == 2,
-                                               r->pathFeedback, r->tailMode == 2 ? r->pathTailBelow : 0);
+    if (neural) launches = launch_neural_frame(f, net, r->lambertView, s, (r->tailMode == 1 && !debug_sync_enabled()) ? &r->segTail : nullptr, r->tailMode == 2,
+                                               r->pathFeedback, r->tailMode == 2 ? r->pathTailBelow : 0, sOut, r->evSplit);
     else {
         // primary tiles most-expensive-first, from the clocks an earlier frame of this camera measured (see k_gt_primary)
         const bool order = r->tileOrderOn && r->tileCount > 0;
@@ -1150,17 +1230,21 @@ static int render_impl(nrb_renderer* r, const float cam_pos[3]) {
             launches += 2;
         }
     }
-    if (r->denoise && !r->lambertView) launches += launch_denoise(f, s);
+    if (r->denoise && !r->lambertView) launches += launch_denoise(f, sOut);
     if (!r->parent && r->gather.role != 0) {
         ++r->gather.frames;
-        if (r->gather.role == 2) launch_gather_signal(static_cast<unsigned*>(r->gather.remoteSync), s);
+        if (r->gather.role == 2) launch_gather_signal(static_cast<unsigned*>(r->gather.remoteSync), sOut);
         else launch_gather_wait(r->gather.sync.as<unsigned>(), r->gather.frames * static_cast<unsigned>(r->gather.peers),
-                                r->gather.sync.as<unsigned>() + 4, s);
+                                r->gather.sync.as<unsigned>() + 4, sOut);
         launches += 2;
     }
     set_stage_profiler(nullptr);
     r->profPending = r->profile != 0;
-    NRB_CUDA(cudaEventRecord(r->evStop, s));
+    NRB_CUDA(cudaEventRecord(r->evStop, sOut));
+    if (pipelined) {
+        NRB_CUDA(cudaEventRecord(r->evFrameDone[r->parity], sOut));
+        r->frameDoneValid[r->parity] = true;
+    }
     NRB_CUDA(cudaGetLastError());
     if (r->lambertView) r->accumSampleCount = 0;
     else r->accumSampleCount += static_cast<uint32_t>(spp);
@@ -1169,7 +1253,7 @@ static int render_impl(nrb_renderer* r, const float cam_pos[3]) {
     r->lastRayCount = static_cast<int>(nElems);
     if (r->parent) return NRB_OK;
     // join to the legacy default stream: a following cudaMemcpy(devicePixels) sees the frame
-    NRB_CUDA(cudaEventRecord(r->evJoin, s));
+    NRB_CUDA(cudaEventRecord(r->evJoin, sOut));
     NRB_CUDA(cudaStreamWaitEvent(cudaStreamLegacy, r->evJoin, 0));
     return NRB_OK;
 }
@@ -1334,6 +1418,7 @@ int nrb_read_pixels_async(nrb_renderer* r, void* rgba, size_t bytes) {
 // the whole frame: the gather is fused into the last kernel of the frame, no collective call follows.
 int nrb_gather_export(nrb_renderer* r, int peers, void* handle, size_t handle_bytes) {
     if (!r || !handle || peers < 0) return fail(NRB_ERR_INVALID, "bad argument");
+    r->touched = true;  // the next pipelined frame waits for what this call enqueues
     if (handle_bytes < NRB_GATHER_HANDLE_BYTES) return fail(NRB_ERR_SIZE, "gather handle buffer too small");
     if (r->width <= 0 || r->height <= 0) return fail(NRB_ERR_INVALID, "nrb_resize first");
     NRB_CUDA(cudaSetDevice(r->device));
@@ -1360,6 +1445,7 @@ int nrb_gather_export(nrb_renderer* r, int peers, void* handle, size_t handle_by
 
 int nrb_gather_attach(nrb_renderer* r, const void* handle, size_t handle_bytes) {
     if (!r || !handle) return fail(NRB_ERR_INVALID, "bad argument");
+    r->touched = true;  // the next pipelined frame waits for what this call enqueues
     if (handle_bytes < NRB_GATHER_HANDLE_BYTES) return fail(NRB_ERR_SIZE, "gather handle buffer too small");
     NRB_CUDA(cudaSetDevice(r->device));
     NRB_CUDA(cudaStreamSynchronize(r->stream));
@@ -1384,6 +1470,7 @@ int nrb_gather_attach(nrb_renderer* r, const void* handle, size_t handle_bytes) 
 
 int nrb_gather_detach(nrb_renderer* r) {
     if (!r) return fail(NRB_ERR_INVALID, "null renderer");
+    r->touched = true;  // the next pipelined frame waits for what this call enqueues
     NRB_CUDA(cudaSetDevice(r->device));
     NRB_CUDA(cudaStreamSynchronize(r->stream));
     gather_reset(r);
@@ -1527,6 +1614,7 @@ int nrb_read_buffer(nrb_renderer* r, const char* name, void* dst, size_t bytes) 
 int nrb_trace_rays(nrb_renderer* r, int slot, int mode, const float* d_origins, const float* d_directions, size_t n,
                    nrb_hit* d_out) {
     if (!r || slot < 0 || slot >= NRB_MESH_SLOT_COUNT || mode < 0 || mode > 7) return fail(NRB_ERR_INVALID, "bad argument");
+    r->touched = true;  // the next pipelined frame waits for what this call enqueues
     if (n >= (1ull << 31)) return fail(NRB_ERR_INVALID, "too many rays for one call");
     NRB_CUDA(cudaSetDevice(r->device));
     if (!r->scratchC.p) {
@@ -1558,6 +1646,7 @@ int nrb_trace_rays_host(nrb_renderer* r, int slot, int mode, const float* origin
 
 int nrb_neural_query(nrb_renderer* r, const float* d_inputs, size_t n, void* d_outputs_fp16) {
     if (!r || !d_inputs || !d_outputs_fp16) return fail(NRB_ERR_INVALID, "null argument");
+    r->touched = true;  // the next pipelined frame waits for what this call enqueues
     if (!r->weightsLoaded) return fail(NRB_ERR_STATE, "no weights loaded");
     if (n >= (1ull << 31)) return fail(NRB_ERR_INVALID, "too many queries for one call");
     NRB_CUDA(cudaSetDevice(r->device));
@@ -1573,6 +1662,7 @@ int nrb_neural_query(nrb_renderer* r, const float* d_inputs, size_t n, void* d_o
 
 int nrb_neural_query_static(nrb_renderer* r, const float* d_inputs, size_t n, void* d_outputs_fp16) {
     if (!r || !d_inputs || !d_outputs_fp16) return fail(NRB_ERR_INVALID, "null argument");
+    r->touched = true;  // the next pipelined frame waits for what this call enqueues
     if (!r->weightsLoaded) return fail(NRB_ERR_STATE, "no weights loaded");
     if (n > split_static_max_rows())
         return fail(NRB_ERR_INVALID, "nrb_neural_query_static: n exceeds NRB_STATIC_QUERY_MAX (16384 queries per call)");

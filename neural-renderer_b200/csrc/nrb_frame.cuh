@@ -67,8 +67,10 @@ struct SegTail {
     void release();
     ~SegTail() { release(); }
 };
+// sOut / evSplit: frame pipelining - with sOut != s the last part of the frame (k_path_tail, finalize) is enqueued on sOut
+// behind an event recorded on s; nullptr = everything on s.
 int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStream_t s, SegTail* tail, bool fusedTail,
-                        int* hostFeedback, int pathTailBelow);
+                        int* hostFeedback, int pathTailBelow, cudaStream_t sOut = nullptr, cudaEvent_t evSplit = nullptr);
 size_t tile_sort_temp_bytes(int n);
 int launch_tile_sort(const unsigned int* cost, unsigned int* costSorted, int* ids, int* order, int n, void* temp, size_t tempBytes,
                      cudaStream_t s);

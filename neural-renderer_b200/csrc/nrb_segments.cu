@@ -946,12 +946,21 @@ void init_frame_kernels() {
 }
 
 // Bounces firstBounce..maxBounces in one launch (see k_path_tail).
-static bool launch_path_tail(const Frame& f, const NetDev& net, int firstBounce, int* hostFeedback, cudaStream_t s) {
+static bool path_tail_plan(const NetDev& net, int* ekOut, size_t* smemOut) {
     int warps = 0, ek = 0;
     if (seg_tail_smem(net, &warps, &ek) == 0) return false;  // shapes the mma.sync tile supports
     const int ldA = (ek > net.width ? ek : net.width) + 8;
     const size_t smem = static_cast<size_t>(kPathTailWarps) * (qwarp::kRows * ldA * 2 + qwarp::kRows * 16 * 4 + qwarp::kRows * 16 * 2);
     if (smem > 64 * 1024) return false;
+    *ekOut = ek;
+    *smemOut = smem;
+    return true;
+}
+
+static bool launch_path_tail(const Frame& f, const NetDev& net, int firstBounce, int* hostFeedback, cudaStream_t s) {
+    int ek = 0;
+    size_t smem = 0;
+    if (!path_tail_plan(net, &ek, &smem)) return false;
     const int grid = sm_count() * 2;
     if (net.width == 128) k_path_tail<128><<<grid, kPathTailWarps * 32, smem, s>>>(f, net, firstBounce, ek, hostFeedback);
     else k_path_tail<64><<<grid, kPathTailWarps * 32, smem, s>>>(f, net, firstBounce, ek, hostFeedback);
@@ -989,9 +998,24 @@ static int run_segments(const Frame& f, const NetDev& net, int recIdx, cudaStrea
 }
 
 int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStream_t s, SegTail* tail, bool fusedTail,
-                        int* hostFeedback, int pathTailBelow) {
+                        int* hostFeedback, int pathTailBelow, cudaStream_t sOut, cudaEvent_t evSplit) {
     const FrameParams& fp = f.fp;
     int launches = 0;
+    // Frame pipelining (sOut != s): the end of the frame - the later bounces as k_path_tail, finalize - goes to sOut
+    // behind everything on s, so the caller's NEXT frame (other state buffers, enqueued on s) starts under it.
+    bool split = false;
+    auto out_stream = [&]() -> cudaStream_t {
+        if (sOut == nullptr || sOut == s) return s;
+        if (!split) {
+            cudaEventRecord(evSplit, s);
+            cudaStreamWaitEvent(sOut, evSplit, 0);
+            split = true;
+        }
+        return sOut;
+    };
+    int tailEk = 0;
+    size_t tailSmem = 0;
+    const bool pathTailOk = path_tail_plan(net, &tailEk, &tailSmem);
     if (fusedTail) tail = nullptr;  // the fused tail kernel needs no graph
     if (tail && !prepare_tail(*tail, f, net, s)) tail = nullptr;
     if (tail) cudaMemcpyAsync(tail->dFrame, &f, sizeof(Frame), cudaMemcpyHostToDevice, s);
@@ -1012,7 +1036,7 @@ int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStr
         // for any count, the per-stage kernels below are merely faster for large ones.
         if (b >= 2 && pathTailBelow > 0 && hostFeedback) {
             const int last = *reinterpret_cast<volatile int*>(hostFeedback);
-            if ((last < 0 || last <= pathTailBelow) && launch_path_tail(f, net, b, hostFeedback, s)) {
+            if ((last < 0 || last <= pathTailBelow) && pathTailOk && launch_path_tail(f, net, b, hostFeedback, out_stream())) {
                 ++launches;
                 break;
             }
@@ -1036,7 +1060,7 @@ int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStr
         NRB_LAUNCHED("k_bounce_finish", s);
         ++launches;
     }
-    return launches + launch_finalize(f, s);
+    return launches + launch_finalize(f, out_stream());
 }
 
 }  // namespace nrb

@@ -310,6 +310,11 @@ class RendererNeural:
         """Run the frame as n concurrent row-band slices on n streams inside this renderer (same pixels)."""
         self._opt(K.OPT_FRAME_SLICES, int(n))
 
+    def set_pipeline(self, on):
+        """Neural frames: frame k+1 starts (second stream, second state buffer) under the latency-bound end of frame k
+        (default on; same pixels, frames complete in order)."""
+        self._opt(K.OPT_PIPELINE, int(on))
+
     def set_tile_order(self, on: bool):
         """Ground-truth primary pass: tiles most-expensive-first from an earlier frame's per-tile clocks (default on)."""
         self._opt(K.OPT_TILE_ORDER, int(on))

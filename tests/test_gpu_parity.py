@@ -460,6 +460,64 @@ def test_async_read_back_is_the_frame():
         a.read_pixels_async(host[0].data_ptr(), n - 4)
 
 
+@pytest.mark.parametrize("path_tail", [0, 1 << 30], ids=["per_stage", "path_tail"])
+def test_pipelined_frames_equal_unpipelined(path_tail):
+    """NRB_OPT_PIPELINE: frame k+1 starts on a second stream and a second state buffer under the end of frame k.  Every
+    frame - enqueued back to back with streamed read-backs, across a camera move, a weight reload, a batch query on the
+    renderer's scratch and a frame of the ground-truth mode in between - equals the unpipelined renderer's bit for bit,
+    and so do the counters.  (path_tail fixes which kernels run bounces >= 2, so both runs launch the same ones.)"""
+    import torch
+    scene = nrb.scenes.make_scene("ico", 4, additional=True)
+    eye, basis = nrb.scenes.default_camera()
+    eye2 = (np.asarray(eye, np.float32) * np.float32(1.07)).astype(np.float32)
+    w1, w2 = _weights(), nrb.scenes.make_weights(seed=7)
+    W, H = 288, 200
+    n = W * H * 4
+    x = np.random.RandomState(3).uniform(0, 1, (3000, 12)).astype(np.float32)
+
+    def run(pipeline):
+        r = nrb.RendererNeural(scene)
+        r.resize(W, H)
+        r.set_camera_basis(basis)
+        r.set_samples_per_pixel(2)
+        r.set_bounce_count(3)
+        r.set_path_tail(path_tail)
+        r.set_pipeline(pipeline)
+        r.load_weights(w1)
+        r.set_use_neural_query(True)
+        host = [torch.empty(n, dtype=torch.uint8).pin_memory() for _ in range(12)]
+        k = 0
+        q = None
+        for phase in range(4):
+            for _ in range(3):
+                r.render(eye if phase < 2 else eye2)
+                r.read_pixels_async(host[k].data_ptr(), n)
+                k += 1
+            if phase == 0:
+                q = r.neural_query(x)          # the split query's scratch between two pipelined frames
+            elif phase == 1:
+                r.load_weights(w2)             # new parameters: accumulation continues, the frames change
+            elif phase == 2:
+                r.set_use_neural_query(False)  # one ground-truth frame (unpipelined), then back
+                r.render(eye2)
+                r.set_use_neural_query(True)
+        r.sync()
+        c = r.counters()
+        out = [h.numpy().copy() for h in host]
+        r.close()
+        return out, c, q
+
+    base, cb, qb = run(0)
+    for mode in (1, 2):
+        got, cg, qg = run(mode)
+        for k, (a, b) in enumerate(zip(base, got)):
+            assert np.array_equal(a, b), (mode, k)
+        assert np.array_equal(qb, qg)
+        for key in ("ray_segments", "neural_queries", "path_vertices"):
+            assert cb[key] == cg[key], (mode, key, cb, cg)
+    assert not np.array_equal(base[0], base[2]) and not np.array_equal(base[5], base[6])
+
+
 def test_denoiser_matches_oracle(oracle_lib):
     """NRB_OPT_DENOISE: bilateralDenoiseKernel of the reference (src/denoiser.cuh:47-113) behind finalize, GPU vs
     the oracle's restatement on the same noisy 2-spp frame (8-bit output; device expf/powf may move a value
