@@ -72,7 +72,7 @@ def parse():
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
                     help="multi-GPU frame gather: peer-memory stores fused into finalize (default) or an NCCL reduce")
     ap.add_argument("--no-tail-graph", action="store_true", help="fixed nine-iteration segment tail (profiling aid)")
-    ap.add_argument("--pipeline", type=int, default=1, choices=[0, 1, 2],
+    ap.add_argument("--pipeline", type=int, default=1, choices=[0, 1],
                     help="neural mode: frame k+1 starts under the end of frame k (NRB_OPT_PIPELINE, the library default)")
     return ap.parse_args()
 

@@ -126,8 +126,8 @@ struct nrb_renderer {
     // buffers - so frame k+1 starts under the latency-bound end of frame k.  `stream` stays the stream every frame
     // COMPLETES on, in order (read-backs, gather, nrb_sync and callers' events on nrb_stream() keep their meaning); work
     // other entry points enqueue on it between frames is waited for by the next frame's early part (`touched`).
-    int pipeline = 1;      // 2 (experiment): two early streams - a frame's early part may run beside the WHOLE previous frame
-    cudaStream_t early = nullptr, early2 = nullptr;
+    int pipeline = 1;
+    cudaStream_t early = nullptr;
     cudaEvent_t evSplit = nullptr, evTouch = nullptr, evFrameDone[2] = {nullptr, nullptr};
     bool frameDoneValid[2] = {false, false};
     bool touched = true;   // something other than a pipelined frame was enqueued on `stream` since the last frame
@@ -159,7 +159,6 @@ struct nrb_renderer {
     nrb_nn_config cfg{};
     NetDev net{};
     DevBuf grid, mlp, packedW, xt, encCur;
-    DevBuf xt2, encCur2;  // the second query scratch of deep-pipelined frames (NRB_OPT_PIPELINE = 2)
     SegTail segTail;
     int tailMode = 2;  // NRB_OPT_TAIL_GRAPH: 0 fixed loop, 1 conditional WHILE graph, 2 fused tail kernel
     int pathTailBelow = 49152;  // NRB_OPT_PATH_TAIL: bounces >= 2 run as one kernel while they start with at most this many paths
@@ -556,7 +555,6 @@ int nrb_create(const nrb_nn_config* cfg, int device, nrb_renderer** out) {
     int rc = configure_network(r, cfg);
     if (rc != NRB_OK) { delete r; return rc; }
     if (cudaStreamCreateWithFlags(&r->early, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaStreamCreateWithFlags(&r->early2, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&r->evSplit, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&r->evTouch, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&r->evFrameDone[0], cudaEventDisableTiming) != cudaSuccess ||
@@ -607,10 +605,8 @@ void nrb_destroy(nrb_renderer* r) {
     if (r->evFork) cudaEventDestroy(r->evFork);
     if (r->evDone) cudaEventDestroy(r->evDone);
     if (r->early) cudaStreamSynchronize(r->early);
-    if (r->early2) cudaStreamSynchronize(r->early2);
     if (r->stream) cudaStreamSynchronize(r->stream);
     if (r->early) cudaStreamDestroy(r->early);
-    if (r->early2) cudaStreamDestroy(r->early2);
     if (r->evSplit) cudaEventDestroy(r->evSplit);
     if (r->evTouch) cudaEventDestroy(r->evTouch);
     for (cudaEvent_t e : r->evFrameDone)
@@ -799,7 +795,7 @@ int nrb_set_option(nrb_renderer* r, int option, int value) {
         case NRB_OPT_LITERAL_BOUNCE_TRACES: r->literalBounceTraces = value != 0; break;
         case NRB_OPT_TILE_ORDER: r->tileOrderOn = value != 0; r->tileOrderState = 0; break;
         case NRB_OPT_FRAME_SLICES: r->slices = value < 0 ? 0 : (value > 8 ? 8 : value); break;
-        case NRB_OPT_PIPELINE: r->pipeline = value < 0 ? 0 : (value > 2 ? 2 : value); break;
+        case NRB_OPT_PIPELINE: r->pipeline = value != 0; break;
         case NRB_OPT_PATH_TAIL:
             r->pathTailBelow = value < 0 ? 0 : value;
             if (r->pathFeedback) r->pathFeedback[0] = r->pathFeedback[1] = -1;
@@ -971,13 +967,6 @@ int ensure_xt(nrb_renderer* r, size_t rows) {
     if (!r->encCur.p) {
         NRB_CUDA(r->encCur.alloc(kMaxLevels * sizeof(int)));
         NRB_CUDA(cudaMemsetAsync(r->encCur.p, 0, r->encCur.bytes, r->stream));
-    }
-    if (r->pipeline >= 2 && (r->xt2.bytes < need || !r->encCur2.p)) {
-        NRB_CUDA(cudaStreamSynchronize(r->stream));
-        NRB_CUDA(r->xt2.alloc(r->xt.bytes));
-        NRB_CUDA(r->encCur2.alloc(kMaxLevels * sizeof(int)));
-        NRB_CUDA(cudaMemsetAsync(r->encCur2.p, 0, r->encCur2.bytes, r->stream));
-        r->touched = true;
     }
     r->net.encCursor = r->encCur.as<int>();
     r->net.xt = r->xt.p;
@@ -1168,12 +1157,7 @@ static int render_impl(nrb_renderer* r, const float cam_pos[3]) {
 
     // sOut: the stream the frame completes on.  s: where it starts (the same stream unless pipelined).
     cudaStream_t sOut = r->stream;
-    cudaStream_t s = pipelined ? ((r->pipeline >= 2 && r->parity) ? r->early2 : r->early) : r->stream;
-    NetDev net = r->net;
-    if (pipelined && r->pipeline >= 2 && r->parity && r->xt2.p && r->xt2.bytes == r->xt.bytes) {
-        net.xt = r->xt2.p;
-        net.encCursor = r->encCur2.as<int>();
-    }
+    cudaStream_t s = pipelined ? r->early : r->stream;
     if (pipelined) {
         if (r->touched) {  // scene / weight uploads, batch queries or an unpipelined frame since the last frame: wait for them
             NRB_CUDA(cudaEventRecord(r->evTouch, sOut));
@@ -1213,7 +1197,7 @@ static int render_impl(nrb_renderer* r, const float cam_pos[3]) {
         set_stage_profiler(&r->prof);
     }
     int launches;
-    if (neural) launches = launch_neural_frame(f, net, r->lambertView, s, (r->tailMode == 1 && !debug_sync_enabled()) ? &r->segTail : nullptr, r->tailMode == 2,
+    if (neural) launches = launch_neural_frame(f, r->net, r->lambertView, s, (r->tailMode == 1 && !debug_sync_enabled()) ? &r->segTail : nullptr, r->tailMode == 2,
                                                r->pathFeedback, r->tailMode == 2 ? r->pathTailBelow : 0, sOut, r->evSplit);
     else {
         // primary tiles most-expensive-first, from the clocks an earlier frame of this camera measured (see k_gt_primary)

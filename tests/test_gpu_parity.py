@@ -508,7 +508,7 @@ def test_pipelined_frames_equal_unpipelined(path_tail):
         return out, c, q
 
     base, cb, qb = run(0)
-    for mode in (1, 2):
+    for mode in (1,):
         got, cg, qg = run(mode)
         for k, (a, b) in enumerate(zip(base, got)):
             assert np.array_equal(a, b), (mode, k)
