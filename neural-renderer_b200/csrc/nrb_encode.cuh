@@ -78,6 +78,12 @@ __device__ __forceinline__ void encode_item(const NetDev& net, int level, const 
     for (int k = 0; k < F / 2; ++k) *reinterpret_cast<__half2*>(dst + 2 * k) = acc[k];
 }
 
+template <int F>
+__device__ __forceinline__ void encode_item(const NetDev& net, int level, float x0, float x1, float x2, __half* dst) {
+    const float x[3] = {x0, x1, x2};
+    encode_item<F>(net, level, x, dst);
+}
+
 // Lane-pair variant of encode_item.  The L1/TEX unit pays ~2 cycles per distinct 128-byte line a
 // warp-wide load touches; with one item per lane a gather instruction touches 32 lines.  Here the
 // two lanes of a pair (2i, 2i+1) split the x-corners of the pair's two items: in every load

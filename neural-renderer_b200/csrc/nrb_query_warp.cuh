@@ -85,13 +85,21 @@ __device__ __forceinline__ void query_tile(const NetDev& net, int ek, const __ha
     const int PL = net.nPoints * net.nLevels, F = net.nFeatures;
     const int shBase = PL * F, shN = net.shDegree * net.shDegree;
     // ---- encode: (point, level) major so a half-warp shares one level's table --------------
+    // a lane keeps its row for the whole loop (32 is a multiple of 16): its point's coordinates are read when the point
+    // changes, not per level - the 16 rows of the [16][16] input tile sit on two banks, an 8-way conflict per read
+    int curP = -1;
+    float x0 = 0.0f, x1 = 0.0f, x2 = 0.0f;
     for (int it = lane; it < kRows * PL; it += 32) {
         const int pl = it >> 4, r = it & 15;
         const int p = pl / net.nLevels, level = pl - p * net.nLevels;
-        const float* x = inp + r * 16 + 3 * p;
+        if (p != curP) {
+            const float* x = inp + r * 16 + 3 * p;
+            x0 = x[0]; x1 = x[1]; x2 = x[2];
+            curP = p;
+        }
         __half* dst = act + r * ldA + pl * F;
-        if (F == 4) encode_item<4>(net, level, x, dst);
-        else encode_item<2>(net, level, x, dst);
+        if (F == 4) encode_item<4>(net, level, x0, x1, x2, dst);
+        else encode_item<2>(net, level, x0, x1, x2, dst);
     }
     if (lane < kRows) {
         __half* dst = act + lane * ldA + shBase;
