@@ -72,6 +72,7 @@ def parse():
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
                     help="multi-GPU frame gather: peer-memory stores fused into finalize (default) or an NCCL reduce")
     ap.add_argument("--no-tail-graph", action="store_true", help="fixed nine-iteration segment tail (profiling aid)")
+    ap.add_argument("--slices", type=int, default=0, help="NRB_OPT_FRAME_SLICES (0 = the library's automatic choice)")
     ap.add_argument("--pipeline", type=int, default=1, choices=[0, 1],
                     help="neural mode: frame k+1 starts under the end of frame k (NRB_OPT_PIPELINE, the library default)")
     return ap.parse_args()
@@ -115,6 +116,8 @@ def setup(nrb, a, scene, lib=None):
     r.set_camera_basis(basis)
     r.set_samples_per_pixel(a.spp)
     r.set_bounce_count(a.bounces)
+    if lib is None and getattr(a, "slices", 0):
+        r.set_frame_slices(a.slices)
     if a.mode == "neural":
         r.load_weights(nrb.scenes.make_weights())
         r.set_use_neural_query(True)

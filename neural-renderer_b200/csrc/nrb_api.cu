@@ -1560,6 +1560,11 @@ int nrb_read_buffer(nrb_renderer* r, const char* name, void* dst, size_t bytes) 
         NRB_CUDA(cudaMemcpy(dst, r->accum.p, bytes, cudaMemcpyDeviceToHost));
         return NRB_OK;
     }
+    if (n == "tile_cost") {  // (development aid) clocks per 8x4 primary tile of the last ground-truth frame that measured them
+        if (!r->tileCost.p || bytes > r->tileCost.bytes) return fail(NRB_ERR_SIZE, "buffer size mismatch for tile_cost");
+        NRB_CUDA(cudaMemcpy(dst, r->tileCost.p, bytes, cudaMemcpyDeviceToHost));
+        return NRB_OK;
+    }
     // element buffers are repacked on the host from the 16-byte records into the reference's
     // triplet/scalar arrays (src/cuda_renderer_neural.h:160-214); debug path, not timed
     const SurfRec& rec = r->st.rec[0];

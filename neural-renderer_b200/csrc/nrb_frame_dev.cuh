@@ -113,6 +113,24 @@ __device__ __forceinline__ bool hit_record(const Frame& f, int slot, V3 o, V3 d,
     return true;
 }
 
+// hit_record for a converged warp (every lane calls, `valid` lanes hold a ray): the traversal is trace_sync, the same walk
+// reconverged every few steps.  Same hit, same record.
+template <int MODE>
+__device__ __forceinline__ bool hit_record_sync(const Frame& f, int slot, bool valid, V3 o, V3 d, V3& pos, V3& nrm, V3& alb,
+                                                V3& mp) {
+    const MeshDev& m = f.mesh[slot];
+    const Hit h = trace_sync(target_of(m), MODE, valid, o, d);
+    if (!valid || h.t >= 1e30f) {
+        mp = global_mparams(f.gmat);
+        return false;
+    }
+    const Surface s = surface_at(m, h);
+    pos = s.position;
+    nrm = s.normal;
+    resolve_surface_material(m, s, f.gmat, alb, mp);
+    return true;
+}
+
 // One bounce vertex: sampleBounceDirectionsKernel for a live path.  Returns false when the
 // reference deactivates the path (pdf <= 0, NaN/Inf weight).
 __device__ __forceinline__ bool sample_vertex(const Frame& f, const ElemId& id, V3 hitPos, V3 normal, V3 albedo,

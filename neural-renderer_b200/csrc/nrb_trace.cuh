@@ -281,6 +281,106 @@ __device__ __forceinline__ Hit trace_dyn_inline(const TraceTarget& m, int mode, 
     return best;
 }
 
+// ---- the same walk for a converged warp, reconverged every few steps ------------------------------------------------
+// trace_dyn_inline leaves reconvergence to the compiler's placement: lanes of a warp drift apart over a long walk (one in
+// its node loop, one testing a leaf, one popping) and each instruction issues for a handful of them.  trace_sync runs the
+// identical per-lane walk in rounds of kSyncRound steps (a node pair or a leaf each) with a warp-wide vote between the
+// rounds - a convergence barrier, nothing else: no state is exchanged, every lane visits what it would have visited.
+// Measured on the ground-truth primary pass of the 1080p bench frame (k_gt_primary, ms): unbounded rounds 0.56 (= the
+// loop above), 256 steps 0.56, 96: 0.46, 48: 0.43, 16: 0.39, 8: 0.39, 4: 0.377, 2: 0.379, 1: 0.381.
+// (Finishing the last long rays of a tile by all 32 lanes - each lane one slice of the ray's parameter range, exact by
+// construction and parity-green - was also measured on top of the rounds: slower at every threshold, removed.)
+// Every lane of the warp must call (valid = the lane holds a ray).
+#ifndef NRB_SYNC_ROUND
+#define NRB_SYNC_ROUND 4
+#endif
+constexpr int kSyncRound = NRB_SYNC_ROUND;
+
+__device__ __forceinline__ Hit trace_sync(const TraceTarget& m, int mode, bool valid, V3 o, V3 d, float tMax = 1e30f) {
+    const unsigned full = 0xffffffffu;
+    Hit best{tMax, 0.0f, 0.0f, 0u};
+    int ref = kTraceDone;
+    const V3 inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    if (valid && m.numTriangles > 0) {
+        float tn;
+        if (slab(o, inv, m.bmin.x, m.bmin.y, m.bmin.z, m.bmax.x, m.bmax.y, m.bmax.z, best.t, tn)) ref = m.rootRef;
+    }
+    const RayPack rp = ray_pack(o, inv);
+    int2 stack[kTraceStack];
+    int sp = 0;
+    const NodePair* __restrict__ nodes = m.nodes;
+    const TriBlock* __restrict__ tris = m.tris;
+    // facing modes skip subtrees whose normal cone says every triangle fails the facing test (nrb_scene.cuh)
+    const int coneBit = mode == TRACE_FORWARD ? 1 : (mode == TRACE_BACKWARD ? 2 : 0);
+    const float dlen = coneBit ? sqrtf(dot(d, d)) : 0.0f;
+    auto pop = [&]() {
+        int next = kTraceDone;
+        while (sp > 0) {
+            const int2 e = stack[--sp];
+            if (!(__int_as_float(e.y) > best.t)) { next = e.x; break; }
+        }
+        return next;
+    };
+    for (;;) {
+        int steps = 0;
+        while (ref != kTraceDone && steps < kSyncRound) {
+            while (ref >= 0 && steps < kSyncRound) {
+                ++steps;
+                const float4 a = __ldg(&nodes[ref].a), b = __ldg(&nodes[ref].b), c = __ldg(&nodes[ref].c);
+                const int4 k = __ldg(&nodes[ref].d);
+                float ln, rn;
+                bool hl, hr;
+                slab_pair(rp, a, b, c, hl, ln, hr, rn);
+                hl = hl && !(ln > best.t);
+                hr = hr && !(rn > best.t);
+                if (coneBit) {
+                    hl = hl && !(cone_culls(static_cast<uint32_t>(k.z), d.x, d.y, d.z, dlen) & coneBit);
+                    hr = hr && !(cone_culls(static_cast<uint32_t>(k.w), d.x, d.y, d.z, dlen) & coneBit);
+                }
+                if (hl && hr) {
+                    const bool rightFirst = rn < ln;
+                    if (sp < kTraceStack) stack[sp++] = make_int2(rightFirst ? k.x : k.y, __float_as_int(rightFirst ? ln : rn));
+                    ref = rightFirst ? k.y : k.x;
+                } else if (hl) {
+                    ref = k.x;
+                } else if (hr) {
+                    ref = k.y;
+                } else {
+                    ref = pop();
+                }
+            }
+            if (ref != kTraceDone && ref < 0) {
+                ++steps;
+                const int packed = ~ref;
+                const int first = packed >> kLeafCountBits;
+                const int end = first + (packed & ((1 << kLeafCountBits) - 1)) + 1;
+                for (int i = first; i < end; ++i) {
+                    const float4 p = __ldg(&tris[i].p), q = __ldg(&tris[i].q), r = __ldg(&tris[i].r);
+                    const float facing = dot(v3(p.w, q.w, r.w), d);
+                    bool ok = !((mode == TRACE_FORWARD && facing >= 0.0f) || (mode == TRACE_BACKWARD && facing <= 0.0f));
+                    const V3 e1 = v3(q.x, q.y, q.z), e2 = v3(r.x, r.y, r.z);
+                    const V3 pv = cross(d, e2);
+                    const float det = dot(e1, pv);
+                    ok = ok && !(fabsf(det) < 1e-8f);
+                    const float invDet = 1.0f / det;
+                    const V3 tv = o - v3(p.x, p.y, p.z);
+                    const float u = dot(tv, pv) * invDet;
+                    ok = ok && !(u < 0.0f || u > 1.0f);
+                    const V3 qv = cross(tv, e1);
+                    const float v = dot(d, qv) * invDet;
+                    ok = ok && !(v < 0.0f || u + v > 1.0f);
+                    const float t = dot(e2, qv) * invDet;
+                    ok = ok && !(t <= 1e-8f) && t > 1e-6f && t < best.t;
+                    if (ok) best = Hit{t, u, v, static_cast<uint32_t>(i)};
+                }
+                ref = pop();
+            }
+        }
+        if (!__any_sync(full, ref != kTraceDone)) break;
+    }
+    return best;
+}
+
 // The out-of-line copy.  A function that is really called keeps the global-memory descriptor in a vector
 // register and moves it to a uniform one before every load (6 R2UR per node step): stages with one or two
 // traces on their critical path (segment exits, re-entry) inline the loop instead, once per kernel.
