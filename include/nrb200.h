@@ -137,7 +137,10 @@ typedef enum nrb_trace_mode {
                                      which prunes by the union of the live modes */
     NRB_TRACE_DYN_ANY = 5,         /* (new, parity hooks) modes 0..2 through the run-time-mode traversal loop of the */
     NRB_TRACE_DYN_FORWARD = 6,     /* segment stages (k_seg_exits, k_seg_apply), which skips subtrees whose normal    */
-    NRB_TRACE_DYN_BACKWARD = 7     /* cone rules the facing mode out: same {t,u,v,prim} as modes 0..2                  */
+    NRB_TRACE_DYN_BACKWARD = 7,    /* cone rules the facing mode out: same {t,u,v,prim} as modes 0..2                  */
+    NRB_TRACE_PLAIN_ANY = 8,       /* (new, parity hooks) modes 0..2 through the first engine (one loop per facing mode, */
+    NRB_TRACE_PLAIN_FORWARD = 9,   /* reconvergence left to the compiler); modes 0..2 themselves run the frame kernels'  */
+    NRB_TRACE_PLAIN_BACKWARD = 10  /* walk, reconverged by a warp vote every few steps (trace_sync): same {t,u,v,prim}   */
 } nrb_trace_mode;
 
 /* = PreliminaryHitInfo, reference src/hit_info.h:7-13.  t == 1e30f means no hit. */

@@ -1602,7 +1602,7 @@ int nrb_read_buffer(nrb_renderer* r, const char* name, void* dst, size_t bytes) 
 
 int nrb_trace_rays(nrb_renderer* r, int slot, int mode, const float* d_origins, const float* d_directions, size_t n,
                    nrb_hit* d_out) {
-    if (!r || slot < 0 || slot >= NRB_MESH_SLOT_COUNT || mode < 0 || mode > 7) return fail(NRB_ERR_INVALID, "bad argument");
+    if (!r || slot < 0 || slot >= NRB_MESH_SLOT_COUNT || mode < 0 || mode > 10) return fail(NRB_ERR_INVALID, "bad argument");
     r->touched = true;  // the next pipelined frame waits for what this call enqueues
     if (n >= (1ull << 31)) return fail(NRB_ERR_INVALID, "too many rays for one call");
     NRB_CUDA(cudaSetDevice(r->device));

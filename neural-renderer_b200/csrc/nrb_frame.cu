@@ -289,7 +289,13 @@ __global__ void __launch_bounds__(128) k_trace_rays(const __grid_constant__ Mesh
                                                     const float* d, size_t n, Hit* out, unsigned long long* stats) {
     const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     TraceStats st{0u, 0u};
-    if (i < n) {
+    if (mode < 3) {  // the closest-hit walk of the frame kernels, entered by the whole warp (trace_sync)
+        const bool valid = i < n;
+        const V3 ro = valid ? ld3(o, i) : v3s(0.0f), rd = valid ? ld3(d, i) : v3(0.0f, 0.0f, 1.0f);
+        Hit h = trace_sync<true>(target_of(m), mode, valid, ro, rd, 1e30f, &st);
+        if (h.t >= 1e30f) h = Hit{1e30f, 0.0f, 0.0f, 0u};
+        if (valid) out[i] = h;
+    } else if (i < n) {
         Hit h;
         if (mode == 3) {  // parity hook for the fused three-mode pass: t = ANY, u = FORWARD, v = BACKWARD distances
             trace_multi(target_of(m), 7, ld3(o, i), ld3(d, i), h.t, h.u, h.v);
@@ -304,11 +310,11 @@ __global__ void __launch_bounds__(128) k_trace_rays(const __grid_constant__ Mesh
                 else tr.step_pop();
             }
             h = Hit{tr.best0, tr.best1, tr.best2, 0u};
-        } else if (mode >= 5) {  // parity hook: the run-time-mode loop of the segment stages (cone culling included)
+        } else if (mode >= 5 && mode < 8) {  // parity hook: the run-time-mode loop of the segment stages (cone culling included)
             h = trace_dyn_inline(target_of(m), mode - 5, ld3(o, i), ld3(d, i));
             if (h.t >= 1e30f) h = Hit{1e30f, 0.0f, 0.0f, 0u};
-        } else {
-            h = trace_mode<true>(m, mode, ld3(o, i), ld3(d, i), &st);
+        } else {  // modes 8..10: the first engine (one loop per facing mode), kept as a cross-check of trace_sync
+            h = trace_mode<true>(m, mode - 8, ld3(o, i), ld3(d, i), &st);
             if (h.t >= 1e30f) h = Hit{1e30f, 0.0f, 0.0f, 0u};
         }
         out[i] = h;

@@ -296,7 +296,9 @@ __device__ __forceinline__ Hit trace_dyn_inline(const TraceTarget& m, int mode, 
 #endif
 constexpr int kSyncRound = NRB_SYNC_ROUND;
 
-__device__ __forceinline__ Hit trace_sync(const TraceTarget& m, int mode, bool valid, V3 o, V3 d, float tMax = 1e30f) {
+template <bool STATS = false>
+__device__ __forceinline__ Hit trace_sync(const TraceTarget& m, int mode, bool valid, V3 o, V3 d, float tMax = 1e30f,
+                                          TraceStats* st = nullptr) {
     const unsigned full = 0xffffffffu;
     Hit best{tMax, 0.0f, 0.0f, 0u};
     int ref = kTraceDone;
@@ -328,6 +330,7 @@ __device__ __forceinline__ Hit trace_sync(const TraceTarget& m, int mode, bool v
                 ++steps;
                 const float4 a = __ldg(&nodes[ref].a), b = __ldg(&nodes[ref].b), c = __ldg(&nodes[ref].c);
                 const int4 k = __ldg(&nodes[ref].d);
+                if (STATS) st->pairs++;
                 float ln, rn;
                 bool hl, hr;
                 slab_pair(rp, a, b, c, hl, ln, hr, rn);
@@ -356,6 +359,7 @@ __device__ __forceinline__ Hit trace_sync(const TraceTarget& m, int mode, bool v
                 const int end = first + (packed & ((1 << kLeafCountBits) - 1)) + 1;
                 for (int i = first; i < end; ++i) {
                     const float4 p = __ldg(&tris[i].p), q = __ldg(&tris[i].q), r = __ldg(&tris[i].r);
+                    if (STATS) st->tris++;
                     const float facing = dot(v3(p.w, q.w, r.w), d);
                     bool ok = !((mode == TRACE_FORWARD && facing >= 0.0f) || (mode == TRACE_BACKWARD && facing <= 0.0f));
                     const V3 e1 = v3(q.x, q.y, q.z), e2 = v3(r.x, r.y, r.z);
