@@ -635,7 +635,9 @@ int nrb_update_mesh(nrb_renderer* r, int slot, const nrb_mesh_desc* d) {
     MeshSlot& m = r->mesh[slot];
     m.clear();
     if (!d || d->num_triangles <= 0) return NRB_OK;
-    int rc = relayout_mesh(r, m, d, slot == NRB_MESH_INNER_SHELL || slot == NRB_MESH_OUTER_SHELL);
+    // normal cones on every mesh: the shells' facing-mode traces, and the ground-truth primary pass (FORWARD_ONLY on the
+    // classic mesh: k_gt_primary 0.364 -> 0.324 ms at 1080p - silhouette rays skip the back-facing leaves they graze)
+    int rc = relayout_mesh(r, m, d, true);
     if (rc != NRB_OK) { m.clear(); return rc; }
     MeshDev& v = m.view;
     cudaStream_t s = r->stream;
