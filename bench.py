@@ -118,13 +118,14 @@ def setup(nrb, a, scene, lib=None):
     r.set_bounce_count(a.bounces)
     if lib is None and getattr(a, "slices", 0):
         r.set_frame_slices(a.slices)
+    if lib is None:
+        r.set_pipeline(int(getattr(a, "pipeline", 1)))
     if a.mode == "neural":
         r.load_weights(nrb.scenes.make_weights())
         r.set_use_neural_query(True)
         if getattr(a, "no_tail_graph", False) and lib is None:
             r.set_tail_graph(False)
-        if lib is None:
-            r.set_pipeline(int(getattr(a, "pipeline", 1)))
+
     return r, eye, basis
 
 

@@ -226,18 +226,20 @@ typedef enum nrb_option {
     NRB_OPT_TILE_ORDER = 16,          /* (new) 1 (default): the ground-truth primary pass hands its 8x4 tiles out most-expensive-first,
                                          ordered by the clocks an earlier frame of the same camera measured per tile; 0: row-major.
                                          Scheduling only: every pixel is computed by the same arithmetic either way. */
-    NRB_OPT_FRAME_SLICES = 17,        /* (new) 0 (default) = automatic: 4 in ground-truth mode, 1 in neural mode (measured).
+    NRB_OPT_FRAME_SLICES = 17,        /* (new) 0 (default) = automatic: 1 while frames are pipelined (NRB_OPT_PIPELINE), else 4 in ground-truth mode
+                                         and 1 in neural mode (measured).
                                          S > 1: the rows this renderer owns are dealt to S internal slices (16-row bands round-robin,
                                          the multi-GPU tile rule) whose stage chains run concurrently on S streams, so the latency-
                                          bound tails of one slice run under the throughput stages of another.  Same pixels.  Not with
                                          NRB_OPT_PROFILE / CAPTURE / DENOISE or NRB_OPT_TAIL_GRAPH != 2 (the frame then runs unsliced). */
-    NRB_OPT_PIPELINE = 18,            /* (new) 1 (default): consecutive neural frames are pipelined - a frame's stages up to the end of
+    NRB_OPT_PIPELINE = 18,            /* (new) 1 (default): consecutive frames are pipelined - in neural mode a frame's stages up to the end of
                                          bounce 1 run on a second stream and alternate between two wavefront-state buffers, its end
                                          (the later bounces in k_path_tail, finalize) stays on nrb_stream(), so frame k+1 starts under
                                          the latency-bound end of frame k.  Frames still COMPLETE in order on nrb_stream(); pixels and
                                          accumulation are those of the unpipelined frames, bit for bit.  0: one stream, one buffer.
-                                         Not with NRB_OPT_PROFILE / CAPTURE, NRB_OPT_TAIL_GRAPH != 2, the lambert view or ground-truth
-                                         mode (those frames run unpipelined). */
+                                         Ground-truth mode likewise: k_gt_primary / k_gt_bounce of frame k+1 under k_gt_tail and
+                                         finalize of frame k.  Not with NRB_OPT_PROFILE / CAPTURE / DENOISE, NRB_OPT_TAIL_GRAPH != 2 in
+                                         neural mode, the lambert view, or frame slices (those frames run unpipelined). */
     NRB_OPT_LITERAL_BOUNCE_TRACES = 14 /* (new, parity hook) 1: the bounce entry runs every trace of
                                          checkBounceEarlyTermination / traceOuterShellEntryFromRays
                                          (src/cuda_renderer_neural.cu:503-553, 773-852) literally.  0 (default): traces

@@ -1050,7 +1050,9 @@ int nrb_render(nrb_renderer* r, const float cam_pos[3]) {
     // gets slower (1.39 -> 1.43 ms with 2): its stages already fill the machine and the query kernels of two slices
     // cannot share an SM's shared memory.  Hence the automatic choice.
     const bool neuralActive = r->useNeuralQuery && r->weightsLoaded && r->mesh[NRB_MESH_OUTER_SHELL].view.numTriangles > 0;
-    const int S = r->slices > 0 ? r->slices : (neuralActive ? 1 : 4);
+    // ground truth: pipelined unsliced frames measured best (0.759 ms against 0.820 with 4 slices and 0.848 with neither)
+    const bool canPipeline = r->pipeline && !r->lambertView && !r->profile && !r->capture && !r->denoise && !debug_sync_enabled();
+    const int S = r->slices > 0 ? r->slices : ((neuralActive || canPipeline) ? 1 : 4);
     const bool sliced = S > 1 && !r->profile && !r->capture && !r->denoise && !debug_sync_enabled() &&
                         (r->tailMode == 2 || !neuralActive) && local_rows(r) >= 64 * S;
     r->activeSlices = sliced ? S : 1;
@@ -1084,8 +1086,8 @@ static int render_impl(nrb_renderer* r, const float cam_pos[3]) {
     const bool neural = r->useNeuralQuery && r->weightsLoaded && outer.view.numTriangles > 0;  // (:2258-2260)
     // pipelined frames: see nrb_renderer::pipeline.  Plain launches on two streams only - not with the per-launch
     // profiler, the capture buffers, the graph-driven tail or as a slice.
-    const bool pipelined = r->pipeline && neural && !r->parent && !r->lambertView && !r->profile && !r->capture &&
-                           r->tailMode == 2 && !debug_sync_enabled() && r->early != nullptr;
+    const bool pipelined = r->pipeline && !r->parent && !r->lambertView && !r->profile && !r->capture && !r->denoise &&
+                           (r->tailMode == 2 || !neural) && !debug_sync_enabled() && r->early != nullptr;
     int rc = ensure_state(r, nElems, localPixels, framePixels, pipelined ? 2 : 1);
     if (rc != NRB_OK) return rc;
     if (r->useNeuralQuery && r->weightsLoaded) {
@@ -1208,7 +1210,7 @@ static int render_impl(nrb_renderer* r, const float cam_pos[3]) {
             f.st.tileCost = r->tileOrderState == 2 ? nullptr : r->tileCost.as<unsigned int>();
             f.st.tileOrder = r->tileOrderState >= 2 ? r->tileOrder.as<int>() : nullptr;
         }
-        launches = launch_gt_frame(f, r->lambertView, s, r->pathFeedback, r->pathTailBelow);
+        launches = launch_gt_frame(f, r->lambertView, s, r->pathFeedback, r->pathTailBelow, sOut, r->evSplit);
         if (order && r->tileOrderState != 2) {
             if (launch_tile_sort(r->tileCost.as<unsigned int>(), r->tileCostSorted.as<unsigned int>(), r->tileIds.as<int>(),
                                  r->tileOrder.as<int>(), r->tileCount, r->tileSortTemp.p, r->tileSortTemp.bytes, s) == 0)

@@ -445,9 +445,21 @@ int launch_lambert(const Frame& f, cudaStream_t s) {
     return 1;
 }
 
-int launch_gt_frame(const Frame& f, bool lambert, cudaStream_t s, int* hostFeedback, int pathTailBelow) {
+int launch_gt_frame(const Frame& f, bool lambert, cudaStream_t s, int* hostFeedback, int pathTailBelow, cudaStream_t sOut,
+                    cudaEvent_t evSplit) {
     const FrameParams& fp = f.fp;
     int launches = 0;
+    // frame pipelining (sOut != s): the end of the frame (k_gt_tail, finalize) goes to sOut behind everything on s
+    bool split = false;
+    auto out_stream = [&]() -> cudaStream_t {
+        if (sOut == nullptr || sOut == s) return s;
+        if (!split) {
+            cudaEventRecord(evSplit, s);
+            cudaStreamWaitEvent(sOut, evSplit, 0);
+            split = true;
+        }
+        return sOut;
+    };
     cudaMemsetAsync(f.st.counts, 0, 16 * sizeof(int), s);
     {
         const int tiles = ((fp.width + 7) / 8) * ((fp.localHeight + 3) / 4) * fp.spp;
@@ -463,8 +475,9 @@ int launch_gt_frame(const Frame& f, bool lambert, cudaStream_t s, int* hostFeedb
         if (b >= 2 && pathTailBelow > 0 && hostFeedback) {  // few paths left: the rest of the frame is one launch (see k_path_tail)
             const int last = reinterpret_cast<volatile int*>(hostFeedback)[1];
             if (last < 0 || last <= pathTailBelow) {
-                k_gt_tail<<<sm_count() * 8, kQueueThreads, 0, s>>>(f, b, qin, hostFeedback);
-                NRB_LAUNCHED("k_gt_tail", s);
+                cudaStream_t so = out_stream();
+                k_gt_tail<<<sm_count() * 8, kQueueThreads, 0, so>>>(f, b, qin, hostFeedback);
+                NRB_LAUNCHED("k_gt_tail", so);
                 ++launches;
                 break;
             }
@@ -475,7 +488,7 @@ int launch_gt_frame(const Frame& f, bool lambert, cudaStream_t s, int* hostFeedb
         ++launches;
         qin = qout;
     }
-    return launches + launch_finalize(f, s);
+    return launches + launch_finalize(f, out_stream());
 }
 
 }  // namespace nrb

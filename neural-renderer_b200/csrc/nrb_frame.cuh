@@ -51,7 +51,8 @@ void init_query_split_kernels();
 struct NetDev;
 void launch_trace_rays(const MeshDev& m, int mode, const float* o, const float* d, size_t n, Hit* out,
                        unsigned long long* stats, cudaStream_t s);
-int launch_gt_frame(const Frame& f, bool lambert, cudaStream_t s, int* hostFeedback, int pathTailBelow);  // returns kernels launched
+int launch_gt_frame(const Frame& f, bool lambert, cudaStream_t s, int* hostFeedback, int pathTailBelow,
+                    cudaStream_t sOut = nullptr, cudaEvent_t evSplit = nullptr);  // returns kernels launched; sOut: see launch_neural_frame
 // Host-side state of the device-driven segment-loop tail (nrb_segments.cu): one instantiated
 // conditional-WHILE graph per hit-record target, the device copy of the frame block its kernels
 // read, and the key the graphs were built for.  Owned by the renderer; null = fixed ten iterations.

@@ -520,6 +520,42 @@ def test_pipelined_frames_equal_unpipelined(path_tail):
     assert not np.array_equal(base[0], base[2]) and not np.array_equal(base[5], base[6])
 
 
+def test_pipelined_ground_truth_frames_equal_unpipelined():
+    """The same for ground-truth frames (unsliced: k_gt_tail and finalize of frame k under k_gt_primary of frame k+1)."""
+    import torch
+    scene = nrb.scenes.make_scene("ico", 5, additional=True)
+    eye, basis = nrb.scenes.default_camera()
+    eye2 = (np.asarray(eye, np.float32) * np.float32(0.93)).astype(np.float32)
+    W, H = 320, 208
+    n = W * H * 4
+
+    def run(pipeline):
+        r = nrb.RendererNeural(scene)
+        r.resize(W, H)
+        r.set_camera_basis(basis)
+        r.set_samples_per_pixel(2)
+        r.set_bounce_count(3)
+        r.set_frame_slices(1)
+        r.set_pipeline(pipeline)
+        host = [torch.empty(n, dtype=torch.uint8).pin_memory() for _ in range(8)]
+        for k in range(8):
+            r.render(eye if k < 4 else eye2)
+            r.read_pixels_async(host[k].data_ptr(), n)
+        r.sync()
+        c = r.counters()
+        out = [h.numpy().copy() for h in host]
+        r.close()
+        return out, c
+
+    base, cb = run(False)
+    got, cg = run(True)
+    for k, (a, b) in enumerate(zip(base, got)):
+        assert np.array_equal(a, b), k
+    for key in ("ray_segments", "path_vertices"):
+        assert cb[key] == cg[key], (key, cb, cg)
+    assert not np.array_equal(base[0], base[3]) and not np.array_equal(base[3], base[4])
+
+
 def test_denoiser_matches_oracle(oracle_lib):
     """NRB_OPT_DENOISE: bilateralDenoiseKernel of the reference (src/denoiser.cuh:47-113) behind finalize, GPU vs
     the oracle's restatement on the same noisy 2-spp frame (8-bit output; device expf/powf may move a value
