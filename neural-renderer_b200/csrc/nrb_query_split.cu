@@ -428,6 +428,15 @@ __global__ void __launch_bounds__(kMlpThreads, 1)
     const int nMine = (tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
 
     const int EK = plan.ek, H = net.nHidden, LAYERS = H + 1;
+#ifndef NRB_MLP_TS
+#define NRB_MLP_TS 1
+#endif
+    // Hidden activations as the A operand in tensor memory (width 128): the epilogue writes the fp16 rows back with
+    // tcgen05.st instead of st.shared + a generic-to-async proxy fence.  Columns: [0, 2W) the two accumulators,
+    // [2W, 3W) the two activation tiles (W / 2 columns each, two K elements per column).
+    constexpr bool kTS = NRB_MLP_TS && WIDTH == 128;
+    constexpr uint32_t kTmemCols = kTS ? 512u : 2u * WIDTH;
+    constexpr uint32_t kActBase = 2u * WIDTH, kActCols = WIDTH / 2u;
     unsigned char* wsm = smem + plan.offW;
     unsigned char* X = smem + plan.offX;
     unsigned char* Hb = smem + plan.offH;
@@ -449,7 +458,7 @@ __global__ void __launch_bounds__(kMlpThreads, 1)
         tc::mbar_init(barEpi + 1, kEpiWarps);
         tc::mbar_init_fence();
     }
-    if (warp == 0) tc::tmem_alloc(tmemSlot, 2 * WIDTH);
+    if (warp == 0) tc::tmem_alloc(tmemSlot, kTmemCols);
     tc::fence_before();
     __syncthreads();
     tc::fence_after();
@@ -514,7 +523,13 @@ __global__ void __launch_bounds__(kMlpThreads, 1)
                 trace(tr && lane == 0, out, n, 0, step, 1);
                 const uint64_t a0 = c == 0 ? dHA : dHB;
                 const uint64_t b0 = dWh + static_cast<uint64_t>(static_cast<uint32_t>(layer - 1) * (WIDTH * WIDTH * 2u / 16u));
-                if (layer == H) {
+                if (kTS) {
+                    const uint32_t aT = tmem + kActBase + static_cast<uint32_t>(c) * kActCols;
+                    const uint32_t idesc = layer == H ? idescL : idescW;
+#pragma unroll
+                    for (int k = 0; k < WIDTH / 16; ++k)
+                        tc::mma_f16_ts_elect(elected, acc, aT + 8u * k, b0 + static_cast<uint64_t>(16u * k), idesc, k > 0);
+                } else if (layer == H) {
 #pragma unroll
                     for (int k = 0; k < WIDTH / 16; ++k)
                         tc::mma_f16_elect(elected, acc, a0 + static_cast<uint64_t>(256u * k), b0 + static_cast<uint64_t>(16u * k), idescL, k > 0);
@@ -566,6 +581,16 @@ __global__ void __launch_bounds__(kMlpThreads, 1)
                 for (int b = 0; b < kCols / 32; ++b) tc::ld32(acc + half * kCols + b * 32, v[b]);
                 tc::wait_ld();
                 trace(trE, out, n, 1 + c, ev, 2);
+                if constexpr (kTS) {
+                    uint32_t pk[32];
+#pragma unroll
+                    for (int b = 0; b < kCols / 32; ++b)
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) pk[b * 16 + j] = pack_leaky(v[b][2 * j], v[b][2 * j + 1]);
+                    tc::st32(tmem + (static_cast<uint32_t>(quarter * 32) << 16) + kActBase + static_cast<uint32_t>(c) * kActCols +
+                                 static_cast<uint32_t>(half) * 32u, pk);
+                    tc::wait_st();
+                } else {
 #pragma unroll
                 for (int b = 0; b < kCols / 32; ++b)
 #pragma unroll
@@ -578,6 +603,7 @@ __global__ void __launch_bounds__(kMlpThreads, 1)
                         *reinterpret_cast<uint4*>(Hc + ((((half * kCols) >> 3) + b * 4 + j) * kTileM + row) * 16) = o;
                     }
                 tc::proxy_fence();
+                }
                 tc::fence_before();
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(barEpi + c);
@@ -604,7 +630,7 @@ __global__ void __launch_bounds__(kMlpThreads, 1)
     }
     tc::fence_before();
     __syncthreads();
-    if (warp == 0) tc::tmem_dealloc(tmem, 2 * WIDTH);
+    if (warp == 0) tc::tmem_dealloc(tmem, kTmemCols);
 }
 
 }  // namespace

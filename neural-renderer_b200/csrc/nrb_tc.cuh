@@ -82,6 +82,29 @@ __device__ __forceinline__ void mma_f16_elect(uint32_t elected, uint32_t dTmem, 
         "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(dTmem), "l"(aDesc), "l"(bDesc), "r"(iDesc), "r"(accumulate), "r"(elected) : "memory");
 }
+// The same with the A operand in tensor memory (lane = row, two fp16 K elements per 32-bit column: a K = 16 step
+// is 8 columns), B from a shared-memory descriptor.
+__device__ __forceinline__ void mma_f16_ts_elect(uint32_t elected, uint32_t dTmem, uint32_t aTmem, uint64_t bDesc, uint32_t iDesc,
+                                                 uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "setp.ne.b32 q, %5, 0;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(dTmem), "r"(aTmem), "l"(bDesc), "r"(iDesc), "r"(accumulate), "r"(elected) : "memory");
+}
+__device__ __forceinline__ void st32(uint32_t taddr, const uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
+        "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+        ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+          "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
+          "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
+          "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+        : "memory");
+}
+__device__ __forceinline__ void wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void commit_elect(uint32_t elected, uint64_t* bar) {
     asm volatile(
         "{\n\t.reg .pred q;\n\t"
