@@ -437,21 +437,32 @@ __global__ void __launch_bounds__(kMlpThreads, 1)
     constexpr bool kTS = NRB_MLP_TS && WIDTH == 128;
     constexpr uint32_t kTmemCols = kTS ? 512u : 2u * WIDTH;
     constexpr uint32_t kActBase = 2u * WIDTH, kActCols = WIDTH / 2u;
+    // ... which frees the two hidden tiles' shared memory: the encoded tiles then arrive through a ring of two slots
+    // (one otherwise), so a tile's load no longer waits for the layer-0 MMAs of the tile before it
+#ifndef NRB_MLP_XSLOTS
+#define NRB_MLP_XSLOTS 2
+#endif
+    constexpr int kXSlots = kTS ? NRB_MLP_XSLOTS : 1;
+    const int nX = plan.xBytes <= plan.hBytes ? kXSlots : 1;  // the spare slots are the hidden tiles' (unused) space
     unsigned char* wsm = smem + plan.offW;
     unsigned char* X = smem + plan.offX;
     unsigned char* Hb = smem + plan.offH;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + plan.offBar);
     uint64_t* barW = bars + 0;
-    uint64_t* barXFull = bars + 1;
-    uint64_t* barXEmpty = bars + 2;
+    // slot 0: bars 1 (full), 2 (empty); slots 1, 2: bars 8 / 9, 10 / 11
+    auto barXFull = [&](int slot) { return slot == 0 ? bars + 1 : bars + 6 + 2 * slot; };
+    auto barXEmpty = [&](int slot) { return slot == 0 ? bars + 2 : bars + 7 + 2 * slot; };
+    auto xSlot = [&](int slot) { return slot == 0 ? X : Hb + static_cast<size_t>(slot - 1) * plan.hBytes; };
     uint64_t* barMma = bars + 3;   // [2]
     uint64_t* barEpi = bars + 5;   // [2]
     uint32_t* tmemSlot = reinterpret_cast<uint32_t*>(bars + 7);
 
     if (tid == 0) {
         tc::mbar_init(barW, 1);
-        tc::mbar_init(barXFull, 1);
-        tc::mbar_init(barXEmpty, 1);
+        for (int sl = 0; sl < nX; ++sl) {
+            tc::mbar_init(barXFull(sl), 1);
+            tc::mbar_init(barXEmpty(sl), 1);
+        }
         tc::mbar_init(barMma + 0, 1);
         tc::mbar_init(barMma + 1, 1);
         tc::mbar_init(barEpi + 0, kEpiWarps);
@@ -474,9 +485,10 @@ __global__ void __launch_bounds__(kMlpThreads, 1)
             }
             for (int k = 0; k < nMine; ++k) {
                 const int tile = blockIdx.x + k * gridDim.x;
-                tc::mbar_wait(barXEmpty, (k & 1) ^ 1);
-                tc::mbar_expect_tx(barXFull, plan.xBytes);
-                tc::bulk_g2s(X, xt + static_cast<size_t>(tile) * plan.xBytes, plan.xBytes, barXFull);
+                const int sl = k % nX;
+                tc::mbar_wait(barXEmpty(sl), ((k / nX) & 1) ^ 1);
+                tc::mbar_expect_tx(barXFull(sl), plan.xBytes);
+                tc::bulk_g2s(xSlot(sl), xt + static_cast<size_t>(tile) * plan.xBytes, plan.xBytes, barXFull(sl));
             }
         }
     } else if (warp == 1) {
@@ -491,7 +503,9 @@ __global__ void __launch_bounds__(kMlpThreads, 1)
         const int delay = LAYERS >> 1;
         const uint32_t wBase = tc::s32(wsm);
         const uint32_t idescW = tc::instr_desc(kTileM, WIDTH), idescL = tc::instr_desc(kTileM, 16);
-        const uint64_t dX = tc::smem_desc(tc::s32(X), 2048u, 128u);
+        uint64_t dXs[kXSlots];
+#pragma unroll
+        for (int sl = 0; sl < kXSlots; ++sl) dXs[sl] = tc::smem_desc(tc::s32(xSlot(sl)), 2048u, 128u);
         const uint64_t dW0 = tc::smem_desc(wBase, 128u, static_cast<uint32_t>(EK) * 16u);
         const uint64_t dWh = tc::smem_desc(wBase + plan.w0Bytes, 128u, static_cast<uint32_t>(WIDTH) * 16u);
         const uint64_t dHA = tc::smem_desc(tc::s32(Hb), 2048u, 128u);
@@ -508,13 +522,18 @@ __global__ void __launch_bounds__(kMlpThreads, 1)
                     tc::mbar_wait(barEpi + c, epiPhase);
                     epiPhase ^= 1u;
                 }
-                tc::mbar_wait(barXFull, xUse & 1u);
+                const int sl = static_cast<int>(xUse % static_cast<uint32_t>(nX));
+                tc::mbar_wait(barXFull(sl), (xUse / static_cast<uint32_t>(nX)) & 1u);
                 ++xUse;
                 tc::fence_after();
                 trace(tr && lane == 0, out, n, 0, step, 1);
+                uint64_t dX = dXs[0];
+#pragma unroll
+                for (int q = 1; q < kXSlots; ++q)
+                    if (sl == q) dX = dXs[q];
                 for (int k = 0; k < ksteps0; ++k)
                     tc::mma_f16_elect(elected, acc, dX + static_cast<uint64_t>(256u * k), dW0 + static_cast<uint64_t>(16u * k), idescW, k > 0);
-                tc::commit_elect(elected, barXEmpty);
+                tc::commit_elect(elected, barXEmpty(sl));
                 tc::commit_elect(elected, barMma + c);
             } else {
                 tc::mbar_wait(barEpi + c, epiPhase);
