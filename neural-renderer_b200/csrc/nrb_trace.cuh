@@ -287,12 +287,14 @@ __device__ __forceinline__ Hit trace_dyn_inline(const TraceTarget& m, int mode, 
 // identical per-lane walk in rounds of kSyncRound steps (a node pair or a leaf each) with a warp-wide vote between the
 // rounds - a convergence barrier, nothing else: no state is exchanged, every lane visits what it would have visited.
 // Measured on the ground-truth primary pass of the 1080p bench frame (k_gt_primary, ms): unbounded rounds 0.56 (= the
-// loop above), 256 steps 0.56, 96: 0.46, 48: 0.43, 16: 0.39, 8: 0.39, 4: 0.377, 2: 0.379, 1: 0.381.
+// loop above), 256 steps 0.56, 96: 0.46, 48: 0.43, 16: 0.39, 8: 0.39, 4: 0.377, 2: 0.379, 1: 0.381; with normal cones on
+// the mesh (v24) 16: 0.349, 8: 0.345, 4: 0.326, 3: 0.311, 2: 0.318, 1: 0.305 - and k_gt_bounce 0.426 / 0.411 / 0.402 /
+// 0.393 / 0.397 / 0.410: rounds of 2 give the shortest frame at 1 and at 8 samples per pixel.
 // (Finishing the last long rays of a tile by all 32 lanes - each lane one slice of the ray's parameter range, exact by
 // construction and parity-green - was also measured on top of the rounds: slower at every threshold, removed.)
 // Every lane of the warp must call (valid = the lane holds a ray).
 #ifndef NRB_SYNC_ROUND
-#define NRB_SYNC_ROUND 4
+#define NRB_SYNC_ROUND 2
 #endif
 constexpr int kSyncRound = NRB_SYNC_ROUND;
 
