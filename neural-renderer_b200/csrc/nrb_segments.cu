@@ -424,9 +424,12 @@ __global__ void __launch_bounds__(kQueueThreads, kBounceCtasPerSm) k_bounce_begi
                 // all - its candidates are a subset of that trace's, so it finds nothing either; and the inner-shell
                 // trace only matters where it is nearer than the outer-shell hit.  NRB_OPT_LITERAL_BOUNCE_TRACES
                 // runs them all, as the reference does.
-                const bool wouldReenter = !(tr.best1 < 1e30f) && tr.best2 < 1e30f;  // valid in stage 1; stage 2 uses tFwd / tBwd
                 if (stage == 1) {
-                    tAny = tr.best0; tFwd = tr.best1; tBwd = tr.best2;
+                    tAny = tr.best0; tFwd = tr.best1;
+                    // outside the literal setting the BACKWARD class is not traced: its distance is only asked "is there
+                    // one" when there is no front face, and then the nearest face of any kind is a back face
+                    tBwd = literal ? tr.best2 : (tFwd < 1e30f ? 1e30f : tAny);
+                    const bool wouldReenter = !(tFwd < 1e30f) && tBwd < 1e30f;
                     nTrace += (carried > 0.0f ? 1u : 0u) + 1u + (tFwd >= 1e30f ? 1u : 0u);
                     const int after = tFwd < 1e30f ? 5 : (tBwd < 1e30f ? (literal ? 3 : 5) : 5);
                     next = carried > 0.0f ? 2 : after;
@@ -498,7 +501,7 @@ __global__ void __launch_bounds__(kQueueThreads, kBounceCtasPerSm) k_bounce_begi
                     if (O.w > 0.0f) {
                         baseOffset = 0.0f;
                         entryOrigin = org;
-                        tr.begin(tOuter, (carried > 0.0f ? 1 : 0) | 2 | 4, org, wi);
+                        tr.begin(tOuter, literal ? ((carried > 0.0f ? 1 : 0) | 2 | 4) : (1 | 2), org, wi);
                         stage = 1;
                     }
                 }
