@@ -240,6 +240,12 @@ typedef enum nrb_option {
                                          Ground-truth mode likewise: k_gt_primary / k_gt_bounce of frame k+1 under k_gt_tail and
                                          finalize of frame k.  Not with NRB_OPT_PROFILE / CAPTURE / DENOISE, NRB_OPT_TAIL_GRAPH != 2 in
                                          neural mode, the lambert view, or frame slices (those frames run unpipelined). */
+    NRB_OPT_BOUNCE_ENTRY = 19,        /* (new) which kernel runs checkBounceEarlyTermination + traceOuterShellEntryFromRays
+                                         (src/cuda_renderer_neural.cu:503-553, 773-852).  0 (default): separate pruned walks - nearest
+                                         face of the outer shell, its nearest front face searched only beyond a nearest face that
+                                         is a back face, the inner shell as far as the outer hit.  1: one fused three-class walk
+                                         under a warp-voting scheduler (the kernel of rounds 1-2, kept as a cross-check).  Same
+                                         frames and counters. */
     NRB_OPT_LITERAL_BOUNCE_TRACES = 14 /* (new, parity hook) 1: the bounce entry runs every trace of
                                          checkBounceEarlyTermination / traceOuterShellEntryFromRays
                                          (src/cuda_renderer_neural.cu:503-553, 773-852) literally.  0 (default): traces

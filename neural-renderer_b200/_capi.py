@@ -94,7 +94,7 @@ TRACE_ANY, TRACE_FORWARD_ONLY, TRACE_BACKWARD_ONLY = 0, 1, 2
 (OPT_USE_NEURAL_QUERY, OPT_SAMPLES_PER_PIXEL, OPT_BOUNCE_COUNT, OPT_LAMBERT_VIEW, OPT_CLASSIC_MESH_INDEX,
  OPT_USE_ADDITIONAL_MESH, OPT_USE_CONSTANT_NEURAL_COLOR, OPT_USE_DIRECT_ENV_COLOR, OPT_CAPTURE,
  OPT_USE_HARDWARE_RT, OPT_PROFILE, OPT_QUERY_KERNEL, OPT_TAIL_GRAPH, OPT_DENOISE, OPT_LITERAL_BOUNCE_TRACES, OPT_PATH_TAIL, OPT_TILE_ORDER, OPT_FRAME_SLICES,
- OPT_PIPELINE) = range(19)
+ OPT_PIPELINE, OPT_BOUNCE_ENTRY) = range(20)
 
 PRODUCT_LIB = os.path.join(HERE, "libnrb200.so")
 

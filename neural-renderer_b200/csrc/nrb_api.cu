@@ -165,6 +165,7 @@ struct nrb_renderer {
     int* pathFeedback = nullptr;  // mapped host memory: [0] paths that entered bounce 2 in the last finished frame
     bool denoise = false;
     bool literalBounceTraces = false;
+    int bounceEntry = 0;  // NRB_OPT_BOUNCE_ENTRY
     size_t gridParams = 0, mlpParams = 0;
     bool weightsLoaded = false;
 
@@ -795,6 +796,7 @@ int nrb_set_option(nrb_renderer* r, int option, int value) {
         case NRB_OPT_TAIL_GRAPH: r->tailMode = value < 0 ? 0 : (value > 2 ? 2 : value); break;
         case NRB_OPT_DENOISE: r->denoise = value != 0; break;
         case NRB_OPT_LITERAL_BOUNCE_TRACES: r->literalBounceTraces = value != 0; break;
+        case NRB_OPT_BOUNCE_ENTRY: r->bounceEntry = value != 0; break;
         case NRB_OPT_TILE_ORDER: r->tileOrderOn = value != 0; r->tileOrderState = 0; break;
         case NRB_OPT_FRAME_SLICES: r->slices = value < 0 ? 0 : (value > 8 ? 8 : value); break;
         case NRB_OPT_PIPELINE: r->pipeline = value != 0; break;
@@ -824,6 +826,7 @@ int nrb_get_option(const nrb_renderer* r, int option) {
         case NRB_OPT_TAIL_GRAPH: return r->tailMode;
         case NRB_OPT_DENOISE: return r->denoise ? 1 : 0;
         case NRB_OPT_LITERAL_BOUNCE_TRACES: return r->literalBounceTraces ? 1 : 0;
+        case NRB_OPT_BOUNCE_ENTRY: return r->bounceEntry;
         case NRB_OPT_PATH_TAIL: return r->pathTailBelow;
         case NRB_OPT_TILE_ORDER: return r->tileOrderOn ? 1 : 0;
         case NRB_OPT_FRAME_SLICES: return r->slices;
@@ -1157,6 +1160,7 @@ static int render_impl(nrb_renderer* r, const float cam_pos[3]) {
     f.classicSlot = classicSlot;
     f.additionalEnabled = r->useAdditionalMesh ? 1 : 0;
     f.literalBounceTraces = r->literalBounceTraces ? 1 : 0;
+    f.bounceEntryVote = r->bounceEntry;
     f.literalSegExits = (r->literalBounceTraces || !outer.closed) ? 1 : 0;
 
     // sOut: the stream the frame completes on.  s: where it starts (the same stream unless pipelined).
@@ -1284,7 +1288,7 @@ static int sync_slice(nrb_renderer* r, nrb_renderer* k, int index, uchar4* pixel
         k->net = n;
     }
     k->gridParams = r->gridParams; k->mlpParams = r->mlpParams; k->weightsLoaded = r->weightsLoaded;
-    k->tailMode = r->tailMode; k->literalBounceTraces = r->literalBounceTraces; k->pathTailBelow = r->pathTailBelow;
+    k->tailMode = r->tailMode; k->literalBounceTraces = r->literalBounceTraces; k->bounceEntry = r->bounceEntry; k->pathTailBelow = r->pathTailBelow;
     k->tileOrderOn = r->tileOrderOn;
     std::memcpy(k->fwd, r->fwd, 12); std::memcpy(k->right, r->right, 12); std::memcpy(k->up, r->up, 12);
     k->fovY = r->fovY;

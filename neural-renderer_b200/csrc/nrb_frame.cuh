@@ -16,6 +16,7 @@ struct Frame {
     int classicSlot;
     int additionalEnabled;
     int literalBounceTraces;  // NRB_OPT_LITERAL_BOUNCE_TRACES
+    int bounceEntryVote;      // NRB_OPT_BOUNCE_ENTRY = 1: the fused three-class walk under the voting scheduler
     int literalSegExits;      // the option above, or an outer shell that is not a closed surface: k_seg_exits traces the
                               // outer shell to the end, so the reference's exitT = 1e-8 fallback for rays that find no
                               // back face (:899-905) is reproduced exactly

@@ -392,7 +392,7 @@ __global__ void __launch_bounds__(kQueueThreads, 8) k_bounce_sample(const __grid
 // Ten resident CTAs per SM (48 registers) measured best: 8 / 10 / 12 / 16 -> 0.808 / 0.791 / 0.800 / 0.921 ms (v7);
 // 10 / 12 -> 0.543 / 0.572 ms with the decided traces skipped (v16).
 constexpr int kBounceCtasPerSm = 10;
-__global__ void __launch_bounds__(kQueueThreads, kBounceCtasPerSm) k_bounce_begin(const __grid_constant__ Frame f, int bounce, int qin,
+__global__ void __launch_bounds__(kQueueThreads, kBounceCtasPerSm) k_bounce_begin_vote(const __grid_constant__ Frame f, int bounce, int qin,
                                                                 int qray) {
     const int n = f.st.counts[qin];
     int* cursor = f.st.counts + 8;
@@ -555,6 +555,108 @@ __global__ void __launch_bounds__(kQueueThreads, kBounceCtasPerSm) k_bounce_begi
                 }
             }
         }
+    }
+    stat_flush(f.st.stats + 0, nTrace);
+}
+
+// The bounce entry since v26 (NRB_OPT_BOUNCE_ENTRY = 0): separate, PRUNED traces instead of the fused three-class walk of
+// k_bounce_begin_vote, whose FORWARD class finds nothing on 96 % of the rays and so never prunes.  A warp takes 32
+// vertices from the cursor.  (1) The outer shell's nearest face of any kind - a closest-hit walk that stops at the exit
+// a few percent of the object away.  (2) The nearest FRONT face: if the nearest face is a front face, that is it; if
+// it is a back face, no front face lies nearer (it would have been the nearest face), so the FORWARD walk skips every
+// subtree the ray leaves before that distance (trace_sync's tMin) - which is the whole neighbourhood of the origin -
+// and sees only what lies beyond the exit.  (3) The inner shell as far as the outer hit.  Each is a trace_sync walk
+// (reconverged every few steps).  Same decisions and counters as the voting kernel (tests compare the two):
+// 0.452 -> 0.342 ms at 1080p.  Cost split measured by leaving traces out: (1) 0.205, (3) 0.09, (2) 0.13 unbounded,
+// ~0.045 with the lower bound.
+constexpr int kBounceEntryCtasPerSm = 8;  // 6 / 8 / 10: 0.456 / 0.424 / 0.424 ms (before the lower bound)
+__global__ void __launch_bounds__(kQueueThreads, kBounceEntryCtasPerSm) k_bounce_begin(const __grid_constant__ Frame f, int bounce,
+                                                                                      int qin, int qray) {
+    const int n = f.st.counts[qin];
+    int* cursor = f.st.counts + 8;
+    const TraceTarget tOuter = target_of(f.mesh[NRB_SLOT_OUTER]), tInner = target_of(f.mesh[NRB_SLOT_INNER]);
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const bool literal = f.literalBounceTraces != 0;
+    unsigned int nTrace = 0;
+    for (;;) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(cursor, 32);
+        base = __shfl_sync(full, base, 0);
+        if (base >= n) break;
+        const int i = base + lane;
+        int e = 0;
+        V3 org = v3s(0.0f), wi = v3(0.0f, 0.0f, 1.0f);
+        float carried = 0.0f;
+        bool has = false;
+        if (i < n) {
+            e = f.st.queue[qin][i];
+            const float4 O = f.st.rayO[e], D = f.st.rayD[e];
+            org = f4v(O);
+            wi = f4v(D);
+            carried = D.w;
+            has = O.w > 0.0f;
+        }
+        V3 entryOrigin = org;
+        float baseOffset = 0.0f;
+        // nearest face of any kind; if it is a front face it is also the nearest front face, and if it is a back face
+        // no front face lies nearer: the FORWARD search then skips everything the ray leaves before that distance
+        const Hit hAny = trace_sync(tOuter, TRACE_ANY, has, org, wi);
+        const float tAny = hAny.t;
+        bool anyIsFront = false;
+        if (has && tAny < 1e30f) {
+            const TriBlock& tb = tOuter.tris[hAny.prim];
+            anyIsFront = dot(v3(__ldg(&tb.p.w), __ldg(&tb.q.w), __ldg(&tb.r.w)), wi) < 0.0f;
+        }
+        const bool needFwd = has && tAny < 1e30f && !anyIsFront;
+        float tFwd = trace_sync<false, true>(tOuter, TRACE_FORWARD, needFwd, org, wi, 1e30f, nullptr, tAny).t;
+        if (!needFwd) tFwd = anyIsFront ? tAny : 1e30f;
+        float tBwd = tFwd < 1e30f ? 1e30f : tAny;
+        if (literal) tBwd = trace_sync(tOuter, TRACE_BACKWARD, has, org, wi).t;
+        const int after = tFwd < 1e30f ? 5 : (tBwd < 1e30f ? (literal ? 3 : 5) : 5);
+        int next = 5;
+        bool alive = has;
+        float entryT = tFwd;
+        if (has) {
+            const bool wouldReenter = !(tFwd < 1e30f) && tBwd < 1e30f;
+            nTrace += (carried > 0.0f ? 1u : 0u) + 1u + (tFwd >= 1e30f ? 1u : 0u);
+            next = carried > 0.0f ? 2 : after;
+            if (!literal) {
+                if (next == 2 && !(tAny < 1e30f)) { next = after; ++nTrace; }
+                if (next == 5 && wouldReenter) ++nTrace;
+            }
+        }
+        const bool need2 = has && next == 2;
+        if (need2) ++nTrace;
+        const float ht = trace_sync(tInner, TRACE_ANY, need2, org, wi, literal ? 1e30f : tAny).t;
+        if (need2) {
+            const bool ends = ht < 1e30f && tAny < 1e30f && ht < tAny;
+            if (!literal && !(tFwd < 1e30f) && tBwd < 1e30f && !ends) ++nTrace;
+            if (ends) { next = 5; alive = false; }
+            else { next = after; entryT = tFwd; }
+        }
+        if (__any_sync(full, has && next == 3)) {  // literal setting only: the re-entry trace from beyond the exit
+            const bool need3 = has && next == 3;
+            if (need3) {
+                baseOffset = tBwd + kSegEps;
+                entryOrigin = org + wi * baseOffset;
+                ++nTrace;
+            }
+            const float t3 = trace_sync(tOuter, TRACE_FORWARD, need3, entryOrigin, wi).t;
+            if (need3) entryT = t3;
+        }
+        bool enters = false;
+        if (alive) {
+            rec_clear(f.st.rec[1], e);
+            if (entryT < 1e30f) {
+                const V3 p = entryOrigin + wi * entryT;
+                f.st.segE[e] = make_float4(p.x, p.y, p.z, baseOffset + entryT);
+                f.st.segD[e] = make_float4(wi.x, wi.y, wi.z, 0.0f);
+                enters = true;
+            }
+        }
+        queue_push(f.st.queue[qray], f.st.counts + qray, alive, e);
+        queue_push(f.st.queue[2], f.st.counts + 2, enters, e);
     }
     stat_flush(f.st.stats + 0, nTrace);
 }
@@ -1052,7 +1154,12 @@ int launch_neural_frame(const Frame& f, const NetDev& net, bool lambert, cudaStr
             const int need = (fp.nElems + kQueueThreads - 1) / kQueueThreads;
             const int cap = sm_count() * kBounceCtasPerSm;
             const int g = need < cap ? (need < 1 ? 1 : need) : cap;
-            k_bounce_begin<<<g, kQueueThreads, 0, s>>>(f, b, 0, 1);
+            if (f.bounceEntryVote) {
+                k_bounce_begin_vote<<<g, kQueueThreads, 0, s>>>(f, b, 0, 1);
+            } else {
+                const int cap2 = sm_count() * kBounceEntryCtasPerSm;
+                k_bounce_begin<<<need < cap2 ? (need < 1 ? 1 : need) : cap2, kQueueThreads, 0, s>>>(f, b, 0, 1);
+            }
         }
         NRB_LAUNCHED("k_bounce_begin", s);
         launches += 2;

@@ -69,6 +69,28 @@ __device__ __forceinline__ bool slab_finish(float t1x, float t1y, float t1z, flo
     tNear = tmin;
     return !(tmax < 0.0f || tmin > tmax);
 }
+__device__ __forceinline__ bool slab_finish_far(float t1x, float t1y, float t1z, float t2x, float t2y, float t2z, float& tNear,
+                                                float& tFar) {
+    float tmin = fminf(t1x, t2x), tmax = fmaxf(t1x, t2x);
+    tmin = fmaxf(tmin, fminf(t1y, t2y)); tmax = fminf(tmax, fmaxf(t1y, t2y));
+    tmin = fmaxf(tmin, fminf(t1z, t2z)); tmax = fminf(tmax, fmaxf(t1z, t2z));
+    tNear = tmin;
+    tFar = tmax;
+    return !(tmax < 0.0f || tmin > tmax);
+}
+// slab_pair that also hands out the exit distances (the same arithmetic; trace_sync's lower bound needs them)
+__device__ __forceinline__ void slab_pair_far(const RayPack& rp, float4 a, float4 b, float4 c, bool& okL, float& nearL, float& farL,
+                                              bool& okR, float& nearR, float& farR) {
+    float l1x, l1y, l2x, l2y, l1z, l2z, r1x, r1y, r2x, r2y, r1z, r2z;
+    unpack2(submul2(pack2(a.x, a.y), rp.oxy, rp.ixy), l1x, l1y);
+    unpack2(submul2(pack2(a.z, a.w), rp.oxy, rp.ixy), l2x, l2y);
+    unpack2(submul2(pack2(b.x, b.y), rp.oxy, rp.ixy), r1x, r1y);
+    unpack2(submul2(pack2(b.z, b.w), rp.oxy, rp.ixy), r2x, r2y);
+    unpack2(submul2(pack2(c.x, c.y), rp.ozz, rp.izz), l1z, l2z);
+    unpack2(submul2(pack2(c.z, c.w), rp.ozz, rp.izz), r1z, r2z);
+    okL = slab_finish_far(l1x, l1y, l1z, l2x, l2y, l2z, nearL, farL);
+    okR = slab_finish_far(r1x, r1y, r1z, r2x, r2y, r2z, nearR, farR);
+}
 __device__ __forceinline__ void slab_pair(const RayPack& rp, float4 a, float4 b, float4 c, bool& okL, float& nearL,
                                           bool& okR, float& nearR) {
     float l1x, l1y, l2x, l2y, l1z, l2z, r1x, r1y, r2x, r2y, r1z, r2z;
@@ -298,9 +320,12 @@ __device__ __forceinline__ Hit trace_dyn_inline(const TraceTarget& m, int mode, 
 #endif
 constexpr int kSyncRound = NRB_SYNC_ROUND;
 
-template <bool STATS = false>
+// TMIN: the caller knows that nothing it looks for lies nearer than tMin (the bounce entry's FORWARD search behind a
+// nearest face that is a back face): subtrees the ray LEAVES before tMin (with a margin far above fp32 rounding) are
+// skipped; hits are accepted as always, so the result is that of the unbounded walk.
+template <bool STATS = false, bool TMIN = false>
 __device__ __forceinline__ Hit trace_sync(const TraceTarget& m, int mode, bool valid, V3 o, V3 d, float tMax = 1e30f,
-                                          TraceStats* st = nullptr) {
+                                          TraceStats* st = nullptr, float tMin = -1e30f) {
     const unsigned full = 0xffffffffu;
     Hit best{tMax, 0.0f, 0.0f, 0u};
     int ref = kTraceDone;
@@ -310,6 +335,7 @@ __device__ __forceinline__ Hit trace_sync(const TraceTarget& m, int mode, bool v
         if (slab(o, inv, m.bmin.x, m.bmin.y, m.bmin.z, m.bmax.x, m.bmax.y, m.bmax.z, best.t, tn)) ref = m.rootRef;
     }
     const RayPack rp = ray_pack(o, inv);
+    const float tMinCull = tMin - 1e-3f * (1.0f + fabsf(tMin));
     int2 stack[kTraceStack];
     int sp = 0;
     const NodePair* __restrict__ nodes = m.nodes;
@@ -335,7 +361,14 @@ __device__ __forceinline__ Hit trace_sync(const TraceTarget& m, int mode, bool v
                 if (STATS) st->pairs++;
                 float ln, rn;
                 bool hl, hr;
-                slab_pair(rp, a, b, c, hl, ln, hr, rn);
+                if (TMIN) {
+                    float lf, rf;
+                    slab_pair_far(rp, a, b, c, hl, ln, lf, hr, rn, rf);
+                    hl = hl && !(lf < tMinCull);
+                    hr = hr && !(rf < tMinCull);
+                } else {
+                    slab_pair(rp, a, b, c, hl, ln, hr, rn);
+                }
                 hl = hl && !(ln > best.t);
                 hr = hr && !(rn > best.t);
                 if (coneBit) {

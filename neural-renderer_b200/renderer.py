@@ -315,6 +315,10 @@ class RendererNeural:
         (default on; same pixels, frames complete in order)."""
         self._opt(K.OPT_PIPELINE, int(on))
 
+    def set_bounce_entry(self, which: int):
+        """0 (default): separate pruned walks; 1: the fused three-class walk under the voting scheduler (same frames)."""
+        self._opt(K.OPT_BOUNCE_ENTRY, int(which))
+
     def set_tile_order(self, on: bool):
         """Ground-truth primary pass: tiles most-expensive-first from an earlier frame's per-tile clocks (default on)."""
         self._opt(K.OPT_TILE_ORDER, int(on))

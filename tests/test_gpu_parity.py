@@ -209,17 +209,23 @@ def test_decided_bounce_traces_are_skipped_without_changing_the_frame(oracle_lib
     prod, _, eye = make_pair(scene, oracle_lib, 192, 128, spp=2, bounces=3, neural=True, weights=_weights())
     prod.set_tail_graph(0)  # fixed loop: bit-reproducible network arithmetic
     out = []
-    for literal in (True, False, True):
+    # (literal, entry kernel): NRB_OPT_BOUNCE_ENTRY 0 = separate pruned walks (the default), 1 = the fused walk under
+    # the voting scheduler; two independent implementations of the same stage
+    runs = ((True, 0), (False, 0), (True, 0), (True, 1), (False, 1))
+    for literal, entry in runs:
         prod.set_literal_bounce_traces(literal)
+        prod.set_bounce_entry(entry)
         prod.reset_samples()
         prod.render(eye)
         out.append((prod.read_pixels().copy(), prod.read_buffer("path_radiance").copy(), prod.counters()))
     prod.set_literal_bounce_traces(False)
+    prod.set_bounce_entry(0)
     assert np.array_equal(out[0][0], out[2][0])  # the literal run is reproducible
-    assert np.array_equal(out[0][0], out[1][0])
-    assert np.array_equal(out[0][1], out[1][1])
-    for key in ("neural_queries", "path_vertices", "ray_segments"):
-        assert out[0][2][key] == out[1][2][key], (key, out[0][2][key], out[1][2][key])
+    for k in (1, 3, 4):
+        assert np.array_equal(out[0][0], out[k][0]), runs[k]
+        assert np.array_equal(out[0][1], out[k][1]), runs[k]
+        for key in ("neural_queries", "path_vertices", "ray_segments"):
+            assert out[0][2][key] == out[k][2][key], (runs[k], key, out[0][2][key], out[k][2][key])
     assert out[0][2]["path_vertices"] > 1000
 
 
