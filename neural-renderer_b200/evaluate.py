@@ -6,8 +6,9 @@ neural render through RendererNeural, total_samples accumulated in batches of 8 
   python tools/evaluate.py CONFIG.json [OUT_DIR] [--width W --height H]
 
 Asset formats: the reference loads meshes through assimp/tinygltf and environments through stb/tinyexr
-(out of scope).  Here: Wavefront OBJ and ASCII / binary-little-endian PLY meshes, Radiance
-.hdr environments (RLE decoder below), raw fp16 .bin checkpoints, plus `synthetic:` pseudo-paths so the
+(out of scope).  Here: Wavefront OBJ, ASCII / binary-little-endian PLY and glTF 2.0 (.glb / .gltf, a
+restatement of the reference's LoadGltfWithMaterials: node transforms, per-primitive materials, embedded images) meshes,
+Radiance .hdr environments (RLE decoder below), raw fp16 .bin checkpoints, plus `synthetic:` pseudo-paths so the
 driver runs without any asset on disk:
     "path": "synthetic:ico:5"         displaced icosphere, 5 subdivisions       (original mesh)
     "path": "synthetic:shell:3:1.12"  icosphere(3) scaled by 1.12               (shells)
@@ -197,6 +198,207 @@ def load_hdr(path):
     return out[..., :3].astype(np.float32) * scale[..., None]
 
 
+# ---- glTF 2.0 (.glb / .gltf): LoadGltfWithMaterials, reference src/mesh_loader.cpp:160-624 ------------------------
+_GLTF_COMPONENT = {5120: np.int8, 5121: np.uint8, 5122: np.int16, 5123: np.uint16, 5125: np.uint32, 5126: np.float32}
+_GLTF_WIDTH = {"SCALAR": 1, "VEC2": 2, "VEC3": 3, "VEC4": 4, "MAT4": 16}
+
+
+def _gltf_read(path):
+    """-> (json dict, [buffer bytes]).  .glb: 12-byte header, then JSON and BIN chunks; .gltf: JSON with buffer URIs
+    (files beside it or base64 data URIs)."""
+    import base64
+    import struct
+    raw = open(path, "rb").read()
+    base = os.path.dirname(os.path.abspath(path))
+    bin_chunk = None
+    if raw[:4] == b"glTF":
+        _, _, total = struct.unpack_from("<4sII", raw, 0)
+        off, doc = 12, None
+        while off + 8 <= min(total, len(raw)):
+            n, kind = struct.unpack_from("<II", raw, off)
+            body = raw[off + 8: off + 8 + n]
+            if kind == 0x4E4F534A:
+                doc = json.loads(body.decode("utf-8"))
+            elif kind == 0x004E4942 and bin_chunk is None:
+                bin_chunk = body
+            off += 8 + n  # chunk lengths include their padding to 4 bytes
+        if doc is None:
+            raise ValueError(f"{path}: no JSON chunk")
+    else:
+        doc = json.loads(raw.decode("utf-8"))
+    buffers = []
+    for b in doc.get("buffers", []):
+        uri = b.get("uri")
+        if uri is None:
+            buffers.append(bin_chunk or b"")
+        elif uri.startswith("data:"):
+            buffers.append(base64.b64decode(uri.split(",", 1)[1]))
+        else:
+            buffers.append(open(os.path.join(base, uri), "rb").read())
+    return doc, buffers, base
+
+
+def _gltf_accessor(doc, buffers, index):
+    """-> [count, width] array of the accessor's component type (byteStride honoured; sparse accessors not read)."""
+    acc = doc["accessors"][index]
+    view = doc["bufferViews"][acc["bufferView"]]
+    dt = np.dtype(_GLTF_COMPONENT[acc["componentType"]]).newbyteorder("<")
+    width = _GLTF_WIDTH[acc["type"]]
+    start = view.get("byteOffset", 0) + acc.get("byteOffset", 0)
+    stride = view.get("byteStride", 0) or dt.itemsize * width
+    buf = np.frombuffer(buffers[view["buffer"]], np.uint8)
+    count = acc["count"]
+    rows = np.lib.stride_tricks.as_strided(buf[start:], shape=(count, dt.itemsize * width), strides=(stride, 1))
+    return np.ascontiguousarray(rows).view(dt).reshape(count, width)
+
+
+def load_gltf(path):
+    """-> dict(vertices, normals, texcoords, indices, materials, material_map, material_ids, textures): one mesh out of
+    every TRIANGLES primitive of every scene's node tree, positions and normals in world space (node matrices or TRS,
+    column-major, fp32 like the reference), one material-map entry per primitive, images as 8-bit RGBA (tinygltf's
+    default), materials from pbrMetallicRoughness: base colour factor / texture, metallic and roughness FACTORS (the
+    reference maps the packed texture and then switches it off again, :263-301), normal and emissive textures,
+    KHR_materials_transmission / _ior / _emissive_strength.  Non-indexed primitives contribute no triangles (:526)."""
+    import io
+    doc, buffers, base = _gltf_read(path)
+    f32 = np.float32
+    textures = []
+    for img in doc.get("images", []):
+        pixels = None
+        try:
+            from PIL import Image
+            if "bufferView" in img:
+                v = doc["bufferViews"][img["bufferView"]]
+                o = v.get("byteOffset", 0)
+                data = buffers[v["buffer"]][o: o + v["byteLength"]]
+                pixels = np.asarray(Image.open(io.BytesIO(data)).convert("RGBA"), np.uint8)
+            elif img.get("uri", "").startswith("data:"):
+                import base64
+                pixels = np.asarray(Image.open(io.BytesIO(base64.b64decode(img["uri"].split(",", 1)[1]))).convert("RGBA"), np.uint8)
+            elif img.get("uri"):
+                pixels = np.asarray(Image.open(os.path.join(base, img["uri"])).convert("RGBA"), np.uint8)
+        except Exception as e:  # noqa: BLE001 - an unreadable image stays an empty texture, as in the reference
+            print(f"[GLTF] image not loaded: {e}", file=sys.stderr)
+        textures.append([pixels if pixels is not None else np.zeros((0, 0, 4), np.uint8), False])
+
+    def source(tex_ref):
+        if not tex_ref or tex_ref.get("index", -1) < 0:
+            return -1
+        src = doc["textures"][tex_ref["index"]].get("source", -1)
+        return src if 0 <= src < len(textures) else -1
+
+    materials = []
+    for gm in doc.get("materials", []):
+        m = K.Material.default()
+        pbr = gm.get("pbrMetallicRoughness", {})
+        m.base_color.value[:] = [f32(x) for x in pbr.get("baseColorFactor", [1, 1, 1, 1])[:3]]
+        t = source(pbr.get("baseColorTexture"))
+        if t >= 0:
+            m.base_color.textured, m.base_color.texture_id = 1, t
+            textures[t][1] = True
+        m.metallic.value = f32(pbr.get("metallicFactor", 1.0))
+        m.roughness.value = f32(pbr.get("roughnessFactor", 1.0))
+        t = source(pbr.get("metallicRoughnessTexture"))
+        if t >= 0:
+            textures[t][1] = False
+        t = source(gm.get("normalTexture"))
+        if t >= 0:
+            m.normal.textured, m.normal.texture_id = 1, t
+            textures[t][1] = False
+        m.base_emission.value[:] = [f32(x) for x in gm.get("emissiveFactor", [0, 0, 0])[:3]]
+        t = source(gm.get("emissiveTexture"))
+        if t >= 0:
+            m.base_emission.textured, m.base_emission.texture_id = 1, t
+            textures[t][1] = True
+        ext = gm.get("extensions", {})
+        if "transmissionFactor" in ext.get("KHR_materials_transmission", {}):
+            m.specular_transmission = f32(ext["KHR_materials_transmission"]["transmissionFactor"])
+        if "ior" in ext.get("KHR_materials_ior", {}):
+            m.ior = f32(ext["KHR_materials_ior"]["ior"])
+        if "emissiveStrength" in ext.get("KHR_materials_emissive_strength", {}):
+            m.emission_scale = f32(ext["KHR_materials_emissive_strength"]["emissiveStrength"])
+        materials.append(m)
+    if not materials:
+        materials.append(K.Material.default())
+
+    def mat_mul(a, b):  # both column-major 4x4 as [16] fp32, fp32 accumulation in the reference's order
+        out = np.zeros(16, f32)
+        for col in range(4):
+            for row in range(4):
+                acc = f32(0.0)
+                for k in range(4):
+                    acc = f32(acc + f32(a[k * 4 + row] * b[col * 4 + k]))
+                out[col * 4 + row] = acc
+        return out
+
+    ident = np.array([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1], f32)
+    V, N, UV, IDX, mmap, mids = [], [], [], [], [], []
+    nv = [0]
+    ntri = [0]
+
+    def visit(ni, parent):
+        node = doc["nodes"][ni]
+        if node.get("matrix"):
+            local = np.asarray(node["matrix"], f32)
+        else:
+            T, R, S = ident.copy(), ident.copy(), ident.copy()
+            if node.get("translation"):
+                T[12:15] = np.asarray(node["translation"], f32)
+            if node.get("rotation"):
+                qx, qy, qz, qw = (f32(x) for x in node["rotation"])
+                one, two = f32(1), f32(2)
+                R[0] = one - two * (qy * qy + qz * qz); R[1] = two * (qx * qy + qz * qw); R[2] = two * (qx * qz - qy * qw)
+                R[4] = two * (qx * qy - qz * qw); R[5] = one - two * (qx * qx + qz * qz); R[6] = two * (qy * qz + qx * qw)
+                R[8] = two * (qx * qz + qy * qw); R[9] = two * (qy * qz - qx * qw); R[10] = one - two * (qx * qx + qy * qy)
+            if node.get("scale"):
+                S[0], S[5], S[10] = (f32(x) for x in node["scale"])
+            local = mat_mul(T, mat_mul(R, S))
+        world = mat_mul(parent, local)
+        if node.get("mesh", -1) >= 0:
+            for prim in doc["meshes"][node["mesh"]].get("primitives", []):
+                if prim.get("mode", 4) != 4 or "POSITION" not in prim.get("attributes", {}):
+                    continue
+                att = prim["attributes"]
+                pos = _gltf_accessor(doc, buffers, att["POSITION"]).astype(f32)[:, :3]
+                M = world.reshape(4, 4).T  # row-major view of the column-major matrix
+                # transformPoint: m0*x + m4*y + m8*z + m12, summed left to right in fp32
+                p = ((pos[:, 0:1] * M[:3, 0][None] + pos[:, 1:2] * M[:3, 1][None]) + pos[:, 2:3] * M[:3, 2][None]) + M[:3, 3][None]
+                base_vertex = nv[0]
+                V.append(p.astype(f32))
+                if "NORMAL" in att:
+                    nr = _gltf_accessor(doc, buffers, att["NORMAL"]).astype(f32)[:, :3]
+                    q = (nr[:, 0:1] * M[:3, 0][None] + nr[:, 1:2] * M[:3, 1][None]) + nr[:, 2:3] * M[:3, 2][None]
+                    ln = np.sqrt((q[:, 0] * q[:, 0] + q[:, 1] * q[:, 1]) + q[:, 2] * q[:, 2]).astype(f32)
+                    ok = ln > 0
+                    q = np.where(ok[:, None], q / np.where(ok, ln, 1)[:, None], np.array([0, 1, 0], f32)[None])
+                    N.append(q.astype(f32))
+                else:
+                    N.append(np.tile(np.array([0, 1, 0], f32), (len(pos), 1)))
+                if "TEXCOORD_0" in att:
+                    UV.append(_gltf_accessor(doc, buffers, att["TEXCOORD_0"]).astype(f32)[:, :2])
+                else:
+                    UV.append(np.zeros((len(pos), 2), f32))
+                nv[0] += len(pos)
+                mmap.append(ntri[0])
+                if prim.get("indices", -1) >= 0:
+                    ii = _gltf_accessor(doc, buffers, prim["indices"]).reshape(-1).astype(np.uint32)
+                    ii = ii[: len(ii) // 3 * 3].reshape(-1, 3) + np.uint32(base_vertex)
+                    IDX.append(ii)
+                    ntri[0] += len(ii)
+                mids.append(prim.get("material", 0) if prim.get("material", -1) >= 0 else 0)
+        for c in node.get("children", []):
+            visit(c, world)
+
+    for sc in doc.get("scenes", []):
+        for ni in sc.get("nodes", []):
+            visit(ni, ident)
+    if not IDX or ntri[0] == 0:
+        raise ValueError("No triangles found in GLTF file.")
+    return dict(vertices=np.concatenate(V), normals=np.concatenate(N), texcoords=np.concatenate(UV),
+                indices=np.concatenate(IDX), materials=materials, material_map=np.asarray(mmap, np.uint32),
+                material_ids=np.asarray(mids, np.int32), textures=[(px, srgb) for px, srgb in textures])
+
+
 def load_mesh(spec, what):
     """-> MeshData or None.  `spec` = {"path", "scale"}; vertices are multiplied by scale (LoadMeshLabeled)."""
     path, scale = spec["path"], np.float32(spec["scale"])
@@ -221,8 +423,16 @@ def load_mesh(spec, what):
         v, idx = load_obj(path)
     elif ext == ".ply":
         v, idx = load_ply(path)
+    elif ext in (".glb", ".gltf"):
+        g = load_gltf(path)
+        v = (g["vertices"] * scale).astype(np.float32)  # scaleMesh: positions only
+        # LoadMeshLabeled: nearest-neighbour texture filtering on the original and the additional mesh (evaluate.cu:153-176)
+        nearest = what in ("original mesh", "additional mesh")
+        return scenes.mesh_from(v, g["indices"], normals=g["normals"], texcoords=g["texcoords"], materials=g["materials"],
+                                material_map=g["material_map"], material_ids=g["material_ids"], textures=g["textures"],
+                                has_mesh_materials=True, texture_nearest=nearest)
     else:
-        raise ValueError(f"{what}: only .obj / .ply meshes are supported without assimp ({path})")
+        raise ValueError(f"{what}: .obj / .ply / .glb / .gltf meshes are read here; other formats need assimp ({path})")
     v = (v * scale).astype(np.float32)
     return scenes.mesh_from(v, idx, normals=scenes.vertex_normals(v, idx))
 
@@ -236,6 +446,14 @@ def build_scene(cfg):
     scene.global_material = K.Material.from_config(**{k: m[k] for k in (
         "base_color", "roughness", "metallic", "specular", "specular_tint", "anisotropy", "sheen", "sheen_tint", "clearcoat",
         "clearcoat_gloss")})
+    # applyMaterialParamsOnly (evaluate.cu:194-209): the config's scalar parameters replace those of every mesh material;
+    # base colour, normal and emission (and their textures) stay the file's
+    for mesh in (scene.original_mesh, scene.inner_shell, scene.outer_shell, scene.additional_mesh):
+        for mat in (mesh.materials if mesh is not None else []):
+            for k in ("roughness", "metallic", "specular", "specular_tint", "anisotropy", "sheen", "sheen_tint", "clearcoat",
+                      "clearcoat_gloss"):
+                p = getattr(mat, k)
+                p.value, p.textured, p.texture_id, p.channel = m[k], 0, 0, 0
     env = cfg["environment"]
     if env["hdri_path"].startswith("synthetic:"):
         scene.env_pixels = scenes.sky_env(1024, 512)

@@ -179,14 +179,40 @@ def build_bvh_gpu(vertices, indices, max_leaf: int = 4, device: int = -1):
     return nodes[: n.value].copy(), idx, prim, ms.value
 
 
+def remap_materials(material_map, material_ids, prim_ids):
+    """The material map after the BVH build has reordered the triangles (Mesh::buildBvh, reference
+    src/mesh_bvh.cpp:70-123): per-triangle material ids carried through prim_ids (new -> old triangle), then primitives
+    rebuilt as runs of consecutive triangles with the same material.  -> (material_map u32, material_ids i32)."""
+    material_map = np.asarray(material_map, np.int64)
+    material_ids = np.asarray(material_ids, np.int64)
+    n = len(prim_ids)
+    per_old = np.full(n, -1, np.int64)
+    for p, start in enumerate(material_map):
+        end = material_map[p + 1] if p + 1 < len(material_map) else n
+        per_old[start:end] = material_ids[p]
+    per_new = per_old[np.asarray(prim_ids, np.int64)]
+    if n == 0:
+        return np.zeros(1, np.uint32), np.array([-1], np.int32)
+    starts = np.concatenate([[0], np.nonzero(per_new[1:] != per_new[:-1])[0] + 1])
+    return starts.astype(np.uint32), per_new[starts].astype(np.int32)
+
+
 def mesh_from(vertices, indices, normals=None, texcoords=None, gpu_bvh: bool = False, builder=None, **kw):
-    """builder: (vertices, indices) -> (nodes, leaf-ordered indices, ...); default = the host SAH builder of libnrb200.
-    Callers that must not load libnrb200 (bench.py's reference arm) pass the reference's own Mesh::buildBvh."""
+    """builder: (vertices, indices) -> (nodes, leaf-ordered indices, prim ids, ...); default = the host SAH builder of
+    libnrb200.  Callers that must not load libnrb200 (bench.py's reference arm) pass the reference's own Mesh::buildBvh.
+    A material map with more than one primitive is carried through the reordering (remap_materials)."""
     from .renderer import MeshData
     if builder is not None:
-        nodes, idx = builder(vertices, indices)[:2]
+        built = builder(vertices, indices)
     else:
-        nodes, idx, _ = build_bvh_gpu(vertices, indices)[:3] if gpu_bvh else build_bvh(vertices, indices)
+        built = build_bvh_gpu(vertices, indices) if gpu_bvh else build_bvh(vertices, indices)
+    nodes, idx = built[0], built[1]
+    mm, mi = kw.get("material_map"), kw.get("material_ids")
+    if mm is not None and mi is not None and len(mm) > 1:
+        if len(built) < 3:
+            raise ValueError("a multi-primitive material map needs the builder's primitive ids")
+        kw = dict(kw)
+        kw["material_map"], kw["material_ids"] = remap_materials(mm, mi, built[2])
     return MeshData(vertices=vertices, indices=idx, nodes=nodes, normals=normals, texcoords=texcoords, **kw)
 
 

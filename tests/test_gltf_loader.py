@@ -1,0 +1,162 @@
+"""glTF loader of the evaluate driver (neural-renderer_b200/evaluate.py:load_gltf), a restatement of the reference's
+LoadGltfWithMaterials (src/mesh_loader.cpp:160-624), and the material-map remap of Mesh::buildBvh
+(src/mesh_bvh.cpp:70-123).  CPU only: a GLB is assembled here byte by byte."""
+import io
+import json
+import struct
+
+import numpy as np
+import pytest
+
+from tests.util import nrb
+
+
+def _glb(tmp_path, embed_png=True):
+    """Two nodes: a quad (2 triangles, u16 indices, normals + uvs, material 1 with a base colour texture) under a TRS
+    transform with a child holding a triangle (u32 indices, no normals / uvs, material 0, matrix transform)."""
+    quad_pos = np.array([[0, 0, 0], [1, 0, 0], [1, 1, 0], [0, 1, 0]], np.float32)
+    quad_nrm = np.tile(np.array([0, 0, 1], np.float32), (4, 1))
+    quad_uv = np.array([[0, 0], [1, 0], [1, 1], [0, 1]], np.float32)
+    quad_idx = np.array([0, 1, 2, 0, 2, 3], np.uint16)
+    tri_pos = np.array([[0, 0, 0], [0, 2, 0], [0, 0, 2]], np.float32)
+    tri_idx = np.array([0, 1, 2], np.uint32)
+    blobs, views = [], []
+
+    def add(b, target=None):
+        off = sum(len(x) for x in blobs)
+        pad = (4 - len(b) % 4) % 4
+        blobs.append(b + b"\0" * pad)
+        views.append({"buffer": 0, "byteOffset": off, "byteLength": len(b)})
+        return len(views) - 1
+
+    v_pos, v_nrm, v_uv, v_idx = add(quad_pos.tobytes()), add(quad_nrm.tobytes()), add(quad_uv.tobytes()), add(quad_idx.tobytes())
+    v_tpos, v_tidx = add(tri_pos.tobytes()), add(tri_idx.tobytes())
+    images = []
+    if embed_png:
+        from PIL import Image
+        px = np.zeros((2, 3, 3), np.uint8)
+        px[..., 0], px[0, 1, 1] = 200, 77
+        buf = io.BytesIO()
+        Image.fromarray(px, "RGB").save(buf, "PNG")
+        images.append({"bufferView": add(buf.getvalue()), "mimeType": "image/png"})
+    doc = {
+        "asset": {"version": "2.0"},
+        "scenes": [{"nodes": [0]}],
+        "nodes": [
+            {"mesh": 0, "translation": [1.0, 2.0, 3.0], "rotation": [0.0, 0.0, 0.70710678, 0.70710678], "scale": [2.0, 2.0, 2.0],
+             "children": [1]},
+            {"mesh": 1, "matrix": [1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0.5, 0, 0, 1]},
+        ],
+        "meshes": [
+            {"primitives": [{"attributes": {"POSITION": 0, "NORMAL": 1, "TEXCOORD_0": 2}, "indices": 3, "material": 1}]},
+            {"primitives": [{"attributes": {"POSITION": 4}, "indices": 5}]},
+        ],
+        "accessors": [
+            {"bufferView": v_pos, "componentType": 5126, "count": 4, "type": "VEC3"},
+            {"bufferView": v_nrm, "componentType": 5126, "count": 4, "type": "VEC3"},
+            {"bufferView": v_uv, "componentType": 5126, "count": 4, "type": "VEC2"},
+            {"bufferView": v_idx, "componentType": 5123, "count": 6, "type": "SCALAR"},
+            {"bufferView": v_tpos, "componentType": 5126, "count": 3, "type": "VEC3"},
+            {"bufferView": v_tidx, "componentType": 5125, "count": 3, "type": "SCALAR"},
+        ],
+        "materials": [
+            {"pbrMetallicRoughness": {"baseColorFactor": [0.1, 0.2, 0.3, 1.0], "metallicFactor": 0.25, "roughnessFactor": 0.75},
+             "emissiveFactor": [0.5, 0.0, 0.0],
+             "extensions": {"KHR_materials_ior": {"ior": 1.33}, "KHR_materials_transmission": {"transmissionFactor": 0.4},
+                            "KHR_materials_emissive_strength": {"emissiveStrength": 3.0}}},
+            {"pbrMetallicRoughness": dict({"metallicFactor": 0.0}, **({"baseColorTexture": {"index": 0}} if embed_png else {}))},
+        ],
+        "bufferViews": views,
+        "buffers": [{"byteLength": 0}],
+    }
+    if embed_png:
+        doc["images"] = images
+        doc["textures"] = [{"source": 0}]
+    binary = b"".join(blobs)
+    doc["buffers"][0]["byteLength"] = len(binary)
+    js = json.dumps(doc).encode()
+    js += b" " * ((4 - len(js) % 4) % 4)
+    glb = struct.pack("<4sII", b"glTF", 2, 12 + 8 + len(js) + 8 + len(binary)) + struct.pack("<II", len(js), 0x4E4F534A) + js + \
+        struct.pack("<II", len(binary), 0x004E4942) + binary
+    path = tmp_path / "scene.glb"
+    path.write_bytes(glb)
+    return str(path)
+
+
+def test_gltf_geometry_transforms_and_materials(tmp_path):
+    g = nrb.evaluate.load_gltf(_glb(tmp_path))
+    v, idx = g["vertices"], g["indices"]
+    assert v.shape == (7, 3) and idx.shape == (3, 3) and idx.dtype == np.uint32
+    # node 0: scale 2, rotate 90 degrees about z (x -> y, y -> -x), translate (1, 2, 3)
+    want_quad = np.array([[1, 2, 3], [1, 4, 3], [-1, 4, 3], [-1, 2, 3]], np.float32)
+    assert np.allclose(v[:4], want_quad, atol=1e-5)
+    # node 1 is a child: its matrix (translate x by 0.5) applies first, then the parent's transform
+    local = np.array([[0.5, 0, 0], [0.5, 2, 0], [0.5, 0, 2]], np.float32)
+    want_tri = np.stack([-2 * local[:, 1] + 1, 2 * local[:, 0] + 2, 2 * local[:, 2] + 3], 1)
+    assert np.allclose(v[4:], want_tri, atol=1e-5)
+    assert np.array_equal(idx, np.array([[0, 1, 2], [0, 2, 3], [4, 5, 6]], np.uint32))
+    # normals: rotated (not scaled), default (0, 1, 0) where the primitive has none; uvs default (0, 0)
+    assert np.allclose(g["normals"][:4], [[0, 0, 1]] * 4, atol=1e-6) and np.allclose(g["normals"][4:], [[0, 1, 0]] * 3)
+    assert np.allclose(g["texcoords"][:4], [[0, 0], [1, 0], [1, 1], [0, 1]]) and np.all(g["texcoords"][4:] == 0)
+    # one material-map entry per primitive, in node order; the second primitive has no material -> 0
+    assert g["material_map"].tolist() == [0, 2] and g["material_ids"].tolist() == [1, 0]
+    m0, m1 = g["materials"]
+    assert np.allclose(list(m0.base_color.value), [0.1, 0.2, 0.3]) and not m0.base_color.textured
+    assert m0.metallic.value == pytest.approx(0.25) and m0.roughness.value == pytest.approx(0.75)
+    assert m0.ior == pytest.approx(1.33) and m0.specular_transmission == pytest.approx(0.4)
+    assert m0.emission_scale == pytest.approx(3.0) and list(m0.base_emission.value) == [0.5, 0.0, 0.0]
+    assert m1.base_color.textured == 1 and m1.base_color.texture_id == 0 and m1.roughness.value == pytest.approx(1.0)
+    # images arrive as 8-bit RGBA (tinygltf's default); a base colour texture is tagged sRGB
+    (px, srgb), = g["textures"]
+    assert px.shape == (2, 3, 4) and srgb and px[0, 1].tolist() == [200, 77, 0, 255]
+
+
+def test_gltf_without_materials_or_images_gets_the_default_material(tmp_path):
+    path = _glb(tmp_path, embed_png=False)
+    doc_path = tmp_path / "nomats.glb"
+    raw = open(path, "rb").read()
+    n = struct.unpack_from("<I", raw, 12)[0]
+    doc = json.loads(raw[20:20 + n])
+    del doc["materials"]
+    for mesh in doc["meshes"]:
+        for p in mesh["primitives"]:
+            p.pop("material", None)
+    js = json.dumps(doc).encode()
+    js += b" " * ((4 - len(js) % 4) % 4)
+    rest = raw[20 + n:]
+    doc_path.write_bytes(struct.pack("<4sII", b"glTF", 2, 12 + 8 + len(js) + len(rest)) + struct.pack("<II", len(js), 0x4E4F534A) + js + rest)
+    g = nrb.evaluate.load_gltf(str(doc_path))
+    assert len(g["materials"]) == 1 and list(g["materials"][0].base_color.value) == pytest.approx([0.8, 0.8, 0.8])
+    assert g["material_ids"].tolist() == [0, 0] and g["textures"] == []
+
+
+def test_material_map_follows_the_bvh_reordering():
+    """Mesh::buildBvh reorders triangles; the material of every triangle must travel with it (src/mesh_bvh.cpp:70-123)."""
+    rng = np.random.RandomState(4)
+    prim_ids = rng.permutation(20).astype(np.uint32)            # new -> old triangle
+    mmap, mids = np.array([0, 5, 12], np.uint32), np.array([7, 3, 9], np.int32)
+    new_map, new_ids = nrb.scenes.remap_materials(mmap, mids, prim_ids)
+    old_mat = np.where(np.arange(20) < 5, 7, np.where(np.arange(20) < 12, 3, 9))
+    per_new = old_mat[prim_ids]
+    assert new_map[0] == 0 and np.all(np.diff(new_map.astype(int)) > 0)
+    for k, start in enumerate(new_map):
+        end = new_map[k + 1] if k + 1 < len(new_map) else 20
+        assert np.all(per_new[start:end] == new_ids[k])
+        if k + 1 < len(new_map):
+            assert new_ids[k] != new_ids[k + 1]                  # runs are maximal
+
+
+def test_gltf_mesh_goes_through_the_bvh_build_with_its_materials(tmp_path):
+    """load_mesh on a .glb: scale, BVH build by libnrb200's host builder, remapped material map, nearest filtering on
+    the original mesh (LoadMeshLabeled, evaluate.cu:153-176)."""
+    mesh = nrb.evaluate.load_mesh({"path": _glb(tmp_path), "scale": 0.5}, "original mesh")
+    assert mesh.num_triangles == 3 and mesh.has_mesh_materials and mesh.texture_nearest
+    assert np.allclose(np.sort(mesh.vertices[:, 2]), np.sort(np.array([3, 3, 3, 3, 3, 3, 7], np.float32) * 0.5), atol=1e-5)
+    # every triangle still carries the material of the primitive it came from: the quad's two triangles (vertices 0..3)
+    # have material 1, the child triangle (vertices 4..6) material 0
+    per_tri = np.zeros(3, int)
+    for k, start in enumerate(mesh.material_map):
+        end = mesh.material_map[k + 1] if k + 1 < len(mesh.material_map) else 3
+        per_tri[start:end] = mesh.material_ids[k]
+    for t in range(3):
+        assert per_tri[t] == (1 if mesh.indices[t].max() <= 3 else 0)
