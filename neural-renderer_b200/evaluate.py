@@ -8,7 +8,7 @@ neural render through RendererNeural, total_samples accumulated in batches of 8 
 Asset formats: the reference loads meshes through assimp/tinygltf and environments through stb/tinyexr
 (out of scope).  Here: Wavefront OBJ, ASCII / binary-little-endian PLY and glTF 2.0 (.glb / .gltf, a
 restatement of the reference's LoadGltfWithMaterials: node transforms, per-primitive materials, embedded images) meshes,
-Radiance .hdr environments (RLE decoder below), raw fp16 .bin checkpoints, plus `synthetic:` pseudo-paths so the
+Radiance .hdr (RLE decoder below), OpenEXR (through OpenCV) and 8-bit .png / .jpg environments, raw fp16 .bin checkpoints, plus `synthetic:` pseudo-paths so the
 driver runs without any asset on disk:
     "path": "synthetic:ico:5"         displaced icosphere, 5 subdivisions       (original mesh)
     "path": "synthetic:shell:3:1.12"  icosphere(3) scaled by 1.12               (shells)
@@ -399,6 +399,27 @@ def load_gltf(path):
                 material_ids=np.asarray(mids, np.int32), textures=[(px, srgb) for px, srgb in textures])
 
 
+def load_env(path):
+    """EnvironmentMap::loadFromFile (reference src/scene.cu:289-316): .exr -> RGB of the float image (tinyexr LoadEXR
+    there, OpenCV's OpenEXR reader here), .png / .jpg / .jpeg -> 8-bit RGB / 255 (no gamma, :245-280), anything else ->
+    Radiance .hdr.  -> [H, W, 3] fp32."""
+    low = path.lower()
+    if low.endswith(".exr"):
+        os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")  # must be set before cv2 is first imported
+        import cv2
+        img = cv2.imread(path, cv2.IMREAD_UNCHANGED)
+        if img is None:
+            raise ValueError(f"{path}: OpenCV could not read the EXR file (OPENCV_IO_ENABLE_OPENEXR must be 1 before cv2 is imported)")
+        img = np.asarray(img, np.float32)
+        if img.ndim == 2:
+            img = np.repeat(img[..., None], 3, -1)
+        return np.ascontiguousarray(img[..., 2::-1] if img.shape[-1] >= 3 else np.repeat(img[..., :1], 3, -1))  # BGR(A) -> RGB
+    if low.endswith((".png", ".jpg", ".jpeg")):
+        from PIL import Image
+        return np.asarray(Image.open(path).convert("RGB"), np.float32) / np.float32(255.0)
+    return load_hdr(path)
+
+
 def load_mesh(spec, what):
     """-> MeshData or None.  `spec` = {"path", "scale"}; vertices are multiplied by scale (LoadMeshLabeled)."""
     path, scale = spec["path"], np.float32(spec["scale"])
@@ -457,10 +478,11 @@ def build_scene(cfg):
     env = cfg["environment"]
     if env["hdri_path"].startswith("synthetic:"):
         scene.env_pixels = scenes.sky_env(1024, 512)
-    elif env["hdri_path"].lower().endswith(".hdr"):
-        scene.env_pixels = load_hdr(env["hdri_path"])
     elif env["hdri_path"]:
-        print(f"Failed to load HDRI '{env['hdri_path']}': only Radiance .hdr is supported here", file=sys.stderr)
+        try:
+            scene.env_pixels = load_env(env["hdri_path"])
+        except Exception as e:  # noqa: BLE001 - evaluate prints and goes on without an environment (evaluate.cu:213-216)
+            print(f"Failed to load HDRI '{env['hdri_path']}': {e}", file=sys.stderr)
     scene.env_strength = env["strength"]
     return scene
 

@@ -160,3 +160,22 @@ def test_gltf_mesh_goes_through_the_bvh_build_with_its_materials(tmp_path):
         per_tri[start:end] = mesh.material_ids[k]
     for t in range(3):
         assert per_tri[t] == (1 if mesh.indices[t].max() <= 3 else 0)
+
+
+def test_environment_formats(tmp_path):
+    """EnvironmentMap::loadFromFile dispatch (src/scene.cu:289-316): .exr float RGB, 8-bit .png / 255, else Radiance .hdr."""
+    import os
+    os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")
+    cv2 = pytest.importorskip("cv2")
+    from PIL import Image
+    rgb = (np.random.RandomState(1).rand(6, 9, 3) * 5).astype(np.float32)
+    exr = str(tmp_path / "env.exr")
+    if not cv2.imwrite(exr, rgb[..., ::-1]):
+        pytest.skip("this OpenCV build has no OpenEXR writer")
+    got = nrb.evaluate.load_env(exr)
+    assert got.shape == (6, 9, 3) and got.dtype == np.float32 and np.array_equal(got, rgb)
+    px = (np.random.RandomState(2).rand(4, 5, 3) * 255).astype(np.uint8)
+    png = str(tmp_path / "env.png")
+    Image.fromarray(px, "RGB").save(png)
+    got = nrb.evaluate.load_env(png)
+    assert np.array_equal(got, px.astype(np.float32) / np.float32(255.0))
