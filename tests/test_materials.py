@@ -64,6 +64,38 @@ def test_texture_branches_gt(oracle_lib):
         orc.close()
 
 
+def test_multi_primitive_material_map_gt(oracle_lib):
+    """A mesh of three primitives with three materials (what a glTF file loads as, src/mesh_loader.cpp:445-563): the
+    material map is rebuilt behind the BVH reordering (Mesh::buildBvh, src/mesh_bvh.cpp:70-123) into many short runs,
+    and getMaterialIdForTriangle's binary search (src/mesh_intersection.cuh:53-85) must find every triangle's material -
+    hit colours and parameters bit-exact, frame within the usual bars."""
+    K = nrb._capi
+    base = nrb.scenes.make_scene("ico", 4, additional=True, textured=True)
+    m = base.original_mesh
+    # the same geometry with a three-primitive map laid over the triangles in their PRE-build order
+    v0, idx = nrb.scenes.icosphere(4)
+    v = nrb.scenes.displace(v0, 0.1)
+    uv = np.stack([np.arctan2(v0[:, 0], v0[:, 2]) / (2 * np.pi) + 0.5, np.arccos(np.clip(v0[:, 1], -1, 1)) / np.pi], -1).astype(np.float32)
+    mats = []
+    for k, color in enumerate(((0.9, 0.2, 0.2), (0.2, 0.9, 0.2), (0.8, 0.8, 0.8))):
+        mats.append(K.Material.from_config(base_color=color, roughness=0.3 + 0.2 * k, metallic=0.5 * k, specular=0.5))
+    mats[2].base_color.textured, mats[2].base_color.texture_id = 1, 0
+    n_tri = len(idx)
+    mesh = nrb.scenes.mesh_from(v, idx, normals=nrb.scenes.vertex_normals(v, idx), texcoords=uv, materials=mats,
+                                material_map=np.array([0, n_tri // 3, 2 * n_tri // 3], np.uint32),
+                                material_ids=np.array([2, 0, 1], np.int32), textures=list(m.textures),
+                                has_mesh_materials=True, texture_nearest=True)
+    assert len(mesh.material_map) > 3  # the reordering interleaves the primitives
+    base.original_mesh = mesh
+    prod, orc, eye = make_pair(base, oracle_lib, 192, 108, spp=2, bounces=2)
+    _frame_bars(prod, orc, eye)
+    colors = prod.read_buffer("hit_colors")
+    hit = prod.read_buffer("hit_flags") != 0
+    # all three materials are on screen: the two constant colours and texels of the third
+    assert np.any(np.all(np.isclose(colors[hit], [0.9, 0.2, 0.2]), axis=1)) and np.any(np.all(np.isclose(colors[hit], [0.2, 0.9, 0.2]), axis=1))
+    assert len(np.unique(colors[hit].round(4), axis=0)) > 4
+
+
 @pytest.mark.parametrize("name", ["metal_smooth", "clearcoat", "transmission"])
 def test_disney_lobes_neural(oracle_lib, name):
     """The neural path shades with the global material (applySegmentNeuralOutput, :1007-1123): same lobes, neural hits."""
