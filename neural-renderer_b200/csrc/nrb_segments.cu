@@ -569,7 +569,7 @@ __global__ void __launch_bounds__(kQueueThreads, kBounceCtasPerSm) k_bounce_begi
 // (reconverged every few steps).  Same decisions and counters as the voting kernel (tests compare the two):
 // 0.452 -> 0.342 ms at 1080p.  Cost split measured by leaving traces out: (1) 0.205, (3) 0.09, (2) 0.13 unbounded,
 // ~0.045 with the lower bound.
-constexpr int kBounceEntryCtasPerSm = 8;  // 6 / 8 / 10: 0.456 / 0.424 / 0.424 ms (before the lower bound)
+constexpr int kBounceEntryCtasPerSm = 8;  // 6 / 8 / 10: 0.456 / 0.424 / 0.424 ms before the lower bound; 8 / 10 / 12: 0.341 / 0.343 / 0.348 with it
 __global__ void __launch_bounds__(kQueueThreads, kBounceEntryCtasPerSm) k_bounce_begin(const __grid_constant__ Frame f, int bounce,
                                                                                       int qin, int qray) {
     const int n = f.st.counts[qin];
