@@ -524,6 +524,9 @@ def main():
         "warmup": max(3, a.warmup), "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": a.scaling,
         "vs_baseline": None, "dtype": "f32 geometry + f16 network (f32 accumulate)", "data": "synthetic",
         "config": config_of(a, world),
+        "frames": {"pipelined": bool(a.pipeline), "slices": a.slices or "auto",
+                   "note": "NRB_OPT_PIPELINE: frame k+1 starts on a second stream and state buffer under the end of frame k; "
+                           "all K frames complete inside the timed region"},
         "gather": ("none (1 GPU)" if world == 1 else ("finalize stores into rank 0's frame over NVLink peer memory" if peer_gather else "NCCL sum-reduce of zero-padded frames")),
         "clocks": clocks,
         "e2e": {"value": e2e, "unit": "Mrays/s", "h2d_bytes_per_step": 52, "d2h_bytes_per_step": a.width * a.height * 4,
