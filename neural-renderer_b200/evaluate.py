@@ -118,6 +118,69 @@ def load_obj(path):
     return np.asarray(vs, np.float32), np.asarray(faces, np.uint32)
 
 
+def flat_shaded(vertices, faces):
+    """What assimp's GenNormals + JoinIdenticalVertices leave of a mesh WITHOUT normals (LoadMeshFromFile,
+    src/mesh_loader.cpp:604-690): every face corner gets the face's normal normalize(cross(v1 - v0, v2 - v0)), then
+    corners with the same position and normal become one vertex.  -> (vertices, faces, normals)."""
+    v = np.asarray(vertices, np.float32)
+    f = np.asarray(faces, np.int64)
+    p = v[f]                                                     # [T, 3, 3]
+    n = np.cross(p[:, 1] - p[:, 0], p[:, 2] - p[:, 0]).astype(np.float32)
+    ln = np.linalg.norm(n, axis=1, keepdims=True)
+    n = np.where(ln > 0, n / np.where(ln > 0, ln, 1), np.array([0, 1, 0], np.float32)).astype(np.float32)
+    corners = np.concatenate([p.reshape(-1, 3), np.repeat(n, 3, axis=0)], 1)  # [3T, 6]
+    uniq, inverse = np.unique(corners.view([("", np.float32)] * 6).reshape(-1), return_inverse=True)
+    uniq = uniq.view(np.float32).reshape(-1, 6)
+    return uniq[:, :3].copy(), inverse.reshape(-1, 3).astype(np.uint32), uniq[:, 3:].copy()
+
+
+def load_obj_shaded(path):
+    """Wavefront OBJ as the reference's assimp path delivers it: positions and, where the file has `vn` records, the
+    corners' normals (normalised; one vertex per distinct position / normal couple); without normals, flat_shaded.
+    Texture coordinates and materials are not loaded on this path (`No textures, no materials`, :597).
+    -> (vertices, faces, normals)."""
+    vs, vns, corners, faces = [], [], {}, []
+    out_v, out_n = [], []
+    has_n = True
+    for line in open(path, errors="ignore"):
+        t = line.split()
+        if not t:
+            continue
+        if t[0] == "v":
+            vs.append([float(x) for x in t[1:4]])
+        elif t[0] == "vn":
+            vns.append([float(x) for x in t[1:4]])
+        elif t[0] == "f":
+            ids = []
+            for tok in t[1:]:
+                parts = tok.split("/")
+                vi = int(parts[0])
+                vi = vi - 1 if vi > 0 else len(vs) + vi
+                ni = None
+                if len(parts) > 2 and parts[2]:
+                    ni = int(parts[2])
+                    ni = ni - 1 if ni > 0 else len(vns) + ni
+                else:
+                    has_n = False
+                key = (vi, ni)
+                if key not in corners:
+                    corners[key] = len(out_v)
+                    out_v.append(vi)
+                    out_n.append(ni)
+                ids.append(corners[key])
+            for k in range(1, len(ids) - 1):
+                faces.append([ids[0], ids[k], ids[k + 1]])
+    V = np.asarray(vs, np.float32)
+    F = np.asarray(faces, np.uint32)
+    if not has_n or not vns:
+        v_only, f_only = load_obj(path)
+        return flat_shaded(v_only, f_only)
+    N = np.asarray(vns, np.float32)[np.asarray(out_n)]
+    ln = np.linalg.norm(N, axis=1, keepdims=True)
+    N = np.where(ln > 0, N / np.where(ln > 0, ln, 1), np.array([0, 1, 0], np.float32)).astype(np.float32)
+    return V[np.asarray(out_v)], F, N
+
+
 def load_ply(path):
     f = open(path, "rb")
     if f.readline().strip() != b"ply":
@@ -441,9 +504,12 @@ def load_mesh(spec, what):
         raise ValueError(f"unknown synthetic {what}: {path}")
     ext = os.path.splitext(path)[1].lower()
     if ext == ".obj":
-        v, idx = load_obj(path)
+        v, idx, nrm = load_obj_shaded(path)
+        return scenes.mesh_from((v * scale).astype(np.float32), idx, normals=nrm)
     elif ext == ".ply":
         v, idx = load_ply(path)
+        v, idx, nrm = flat_shaded(v, idx)  # load_ply reads positions and faces only: assimp would generate flat normals
+        return scenes.mesh_from((v * scale).astype(np.float32), idx, normals=nrm)
     elif ext in (".glb", ".gltf"):
         g = load_gltf(path)
         v = (g["vertices"] * scale).astype(np.float32)  # scaleMesh: positions only

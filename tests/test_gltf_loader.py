@@ -179,3 +179,26 @@ def test_environment_formats(tmp_path):
     Image.fromarray(px, "RGB").save(png)
     got = nrb.evaluate.load_env(png)
     assert np.array_equal(got, px.astype(np.float32) / np.float32(255.0))
+
+
+def test_obj_normals_follow_the_assimp_path(tmp_path):
+    """LoadMeshFromFile (src/mesh_loader.cpp:604-690): file normals where the OBJ has them, flat face normals (GenNormals +
+    JoinIdenticalVertices) where it has none."""
+    ev = nrb.evaluate
+    smooth = tmp_path / "s.obj"
+    smooth.write_text("v 0 0 0\nv 1 0 0\nv 0 1 0\nv 0 0 1\nvn 0 0 2\nvn 1 0 0\n"
+                      "f 1//1 2//1 3//1\nf 1//2 3//2 4//2\n")
+    v, f, n = ev.load_obj_shaded(str(smooth))
+    assert len(v) == 6 and f.tolist() == [[0, 1, 2], [3, 4, 5]]          # vertex 1 and 3 appear with two normals each
+    assert np.allclose(n[:3], [[0, 0, 1]] * 3) and np.allclose(n[3:], [[1, 0, 0]] * 3)   # normalised
+    flat = tmp_path / "f.obj"
+    flat.write_text("v 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nv 0 0 1\nf 1 2 3 4\nf 1 5 2\n")   # a quad in z = 0 and a triangle in y = 0
+    v, f, n = ev.load_obj_shaded(str(flat))
+    assert f.shape == (3, 3)
+    tri_n = n[f]                                                           # every corner carries its face's normal
+    geo = np.cross(v[f][:, 1] - v[f][:, 0], v[f][:, 2] - v[f][:, 0])
+    geo /= np.linalg.norm(geo, axis=1, keepdims=True)
+    assert np.allclose(tri_n, geo[:, None, :].repeat(3, 1), atol=1e-6)
+    assert len(v) == 4 + 3                                                 # the quad's two triangles share their 4 corners; the other face has its own
+    mesh = ev.load_mesh({"path": str(flat), "scale": 2.0}, "original mesh")
+    assert mesh.num_triangles == 3 and np.isclose(np.abs(mesh.vertices).max(), 2.0) and mesh.normals.shape == mesh.vertices.shape
