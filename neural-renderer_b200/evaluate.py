@@ -181,13 +181,102 @@ def load_obj_shaded(path):
     return V[np.asarray(out_v)], F, N
 
 
-def load_ply(path):
+_PLY_TYPES = {"char": "i1", "uchar": "u1", "short": "i2", "ushort": "u2", "int": "i4", "uint": "u4", "float": "f4", "double": "f8",
+              "int8": "i1", "uint8": "u1", "int16": "i2", "uint16": "u2", "int32": "i4", "uint32": "u4", "float32": "f4",
+              "float64": "f8"}
+
+
+def _ply_fan(polys):
+    """[n, k] polygons -> [(k - 2) n, 3] triangle fans, face by face (assimp's Triangulate on convex input)."""
+    polys = np.asarray(polys)
+    k = polys.shape[1]
+    if k == 3:
+        return polys
+    return np.stack([np.stack([polys[:, 0], polys[:, m], polys[:, m + 1]], 1) for m in range(1, k - 1)], 1).reshape(-1, 3)
+
+
+def _ply_element_binary(f, count, props, endian):
+    """One element of a binary PLY -> {property: array} (list properties: [count, k] when every row has k entries, else a
+    list of arrays).  Whole-element numpy reads where the rows have one size; a row loop otherwise."""
+    if count == 0:
+        return {pr[-1]: np.zeros((0,)) for pr in props}
+    lists = [pr for pr in props if pr[0] == "list"]
+    start = f.tell()
+    if lists:
+        # probe the first row for the list lengths, then try one structured read with those lengths
+        lens = {}
+        for pr in props:
+            if pr[0] == "list":
+                n = int(np.frombuffer(f.read(np.dtype(_PLY_TYPES[pr[1]]).itemsize), endian + _PLY_TYPES[pr[1]])[0])
+                lens[pr[-1]] = n
+                f.seek(n * np.dtype(_PLY_TYPES[pr[2]]).itemsize, 1)
+            else:
+                f.seek(np.dtype(_PLY_TYPES[pr[0]]).itemsize, 1)
+        f.seek(start)
+    fields = []
+    for pr in props:
+        if pr[0] == "list":
+            fields.append(("#" + pr[-1], endian + _PLY_TYPES[pr[1]]))
+            fields.append((pr[-1], endian + _PLY_TYPES[pr[2]], (lens[pr[-1]],)))
+        else:
+            fields.append((pr[-1], endian + _PLY_TYPES[pr[0]]))
+    dt = np.dtype(fields)
+    raw = f.read(dt.itemsize * count)
+    if len(raw) == dt.itemsize * count:
+        rows = np.frombuffer(raw, dt)
+        if all(np.all(rows["#" + pr[-1]] == lens[pr[-1]]) for pr in lists):
+            return {pr[-1]: rows[pr[-1]] for pr in props}
+    # ragged lists: row by row
+    f.seek(start)
+    out = {pr[-1]: [] for pr in props}
+    for _ in range(count):
+        for pr in props:
+            if pr[0] == "list":
+                n = int(np.frombuffer(f.read(np.dtype(_PLY_TYPES[pr[1]]).itemsize), endian + _PLY_TYPES[pr[1]])[0])
+                out[pr[-1]].append(np.frombuffer(f.read(n * np.dtype(_PLY_TYPES[pr[2]]).itemsize), endian + _PLY_TYPES[pr[2]]))
+            else:
+                out[pr[-1]].append(np.frombuffer(f.read(np.dtype(_PLY_TYPES[pr[0]]).itemsize), endian + _PLY_TYPES[pr[0]])[0])
+    return {k: (v if any(pr[0] == "list" and pr[-1] == k for pr in props) else np.asarray(v)) for k, v in out.items()}
+
+
+def _ply_element_ascii(f, count, props):
+    out = {pr[-1]: [] for pr in props}
+    for _ in range(count):
+        tok = f.readline().split()
+        while not tok:
+            tok = f.readline().split()
+        at = 0
+        for pr in props:
+            if pr[0] == "list":
+                n = int(tok[at])
+                out[pr[-1]].append(np.asarray(tok[at + 1:at + 1 + n], np.float64).astype(_PLY_TYPES[pr[2]]))
+                at += 1 + n
+            else:
+                out[pr[-1]].append(float(tok[at]))
+                at += 1
+    res = {}
+    for pr in props:
+        v = out[pr[-1]]
+        if pr[0] == "list":
+            res[pr[-1]] = np.stack(v) if v and all(len(x) == len(v[0]) for x in v) else v
+        else:
+            res[pr[-1]] = np.asarray(v, np.float64).astype(_PLY_TYPES[pr[0]])
+    return res
+
+
+def load_ply_full(path):
+    """Stanford PLY (ascii, binary_little_endian, binary_big_endian) -> (vertices [V,3] f32, faces [T,3] u32 - polygons as
+    fans -, normals [V,3] f32 or None when the vertex element has no nx / ny / nz).  Other elements and properties are
+    skipped by their declared sizes."""
     f = open(path, "rb")
     if f.readline().strip() != b"ply":
         raise ValueError("not a PLY file")
     fmt, elems = None, []
     while True:
-        p = f.readline().split()
+        line = f.readline()
+        if not line:
+            raise ValueError("PLY header without end_header")
+        p = line.split()
         if not p:
             continue
         if p[0] == b"format":
@@ -198,36 +287,38 @@ def load_ply(path):
             elems[-1][2].append([x.decode() for x in p[1:]])
         elif p[0] == b"end_header":
             break
-    sizes = {"char": "b", "uchar": "B", "short": "h", "ushort": "H", "int": "i", "uint": "I", "float": "f", "double": "d",
-             "int8": "b", "uint8": "B", "int16": "h", "uint16": "H", "int32": "i", "uint32": "I", "float32": "f", "float64": "d"}
-    verts, faces = [], []
+    if fmt not in ("ascii", "binary_little_endian", "binary_big_endian"):
+        raise ValueError("unsupported PLY format " + str(fmt))
+    verts = np.zeros((0, 3), np.float32)
+    normals, tris = None, []
     for name, count, props in elems:
-        for _ in range(count):
-            if fmt == "ascii":
-                tok = f.readline().split()
-                if name == "vertex":
-                    verts.append([float(tok[i]) for i in range(3)])
-                elif name == "face":
-                    n = int(tok[0])
-                    idx = [int(x) for x in tok[1:1 + n]]
-                    faces += [[idx[0], idx[k], idx[k + 1]] for k in range(1, n - 1)]
-            elif fmt == "binary_little_endian":
-                row = []
-                for pr in props:
-                    if pr[0] == "list":
-                        n = struct.unpack("<" + sizes[pr[1]], f.read(struct.calcsize(sizes[pr[1]])))[0]
-                        row.append(list(struct.unpack("<" + sizes[pr[2]] * n, f.read(struct.calcsize(sizes[pr[2]]) * n))))
-                    else:
-                        row.append(struct.unpack("<" + sizes[pr[0]], f.read(struct.calcsize(sizes[pr[0]])))[0])
-                if name == "vertex":
-                    names = [pr[-1] for pr in props]
-                    verts.append([row[names.index(c)] for c in "xyz"])
-                elif name == "face":
-                    idx = next(x for x in row if isinstance(x, list))
-                    faces += [[idx[0], idx[k], idx[k + 1]] for k in range(1, len(idx) - 1)]
+        if fmt == "ascii":
+            data = _ply_element_ascii(f, count, props)
+        else:
+            data = _ply_element_binary(f, count, props, "<" if fmt == "binary_little_endian" else ">")
+        if name == "vertex":
+            verts = np.stack([np.asarray(data[c], np.float32) for c in "xyz"], 1) if count else verts
+            if count and all(c in data for c in ("nx", "ny", "nz")):
+                normals = np.stack([np.asarray(data[c], np.float32) for c in ("nx", "ny", "nz")], 1)
+        elif name == "face" and count:
+            key = next((k for k in ("vertex_indices", "vertex_index") if k in data), None)
+            if key is None:
+                key = next(pr[-1] for pr in props if pr[0] == "list")
+            polys = data[key]
+            if isinstance(polys, np.ndarray) and polys.ndim == 2:
+                if polys.shape[1] >= 3:
+                    tris.append(_ply_fan(polys))
             else:
-                raise ValueError("unsupported PLY format " + str(fmt))
-    return np.asarray(verts, np.float32), np.asarray(faces, np.uint32)
+                for poly in polys:
+                    if len(poly) >= 3:
+                        tris.append(_ply_fan(np.asarray(poly)[None, :]))
+    faces = np.concatenate(tris).astype(np.uint32) if tris else np.zeros((0, 3), np.uint32)
+    return verts, faces, normals
+
+
+def load_ply(path):
+    v, f, _ = load_ply_full(path)
+    return v, f
 
 
 def load_hdr(path):
@@ -507,8 +598,12 @@ def load_mesh(spec, what):
         v, idx, nrm = load_obj_shaded(path)
         return scenes.mesh_from((v * scale).astype(np.float32), idx, normals=nrm)
     elif ext == ".ply":
-        v, idx = load_ply(path)
-        v, idx, nrm = flat_shaded(v, idx)  # load_ply reads positions and faces only: assimp would generate flat normals
+        v, idx, nrm = load_ply_full(path)
+        if nrm is None:
+            v, idx, nrm = flat_shaded(v, idx)  # no nx / ny / nz: assimp's GenNormals
+        else:
+            ln = np.linalg.norm(nrm, axis=1, keepdims=True)
+            nrm = np.where(ln > 0, nrm / np.where(ln > 0, ln, 1), np.array([0, 1, 0], np.float32)).astype(np.float32)
         return scenes.mesh_from((v * scale).astype(np.float32), idx, normals=nrm)
     elif ext in (".glb", ".gltf"):
         g = load_gltf(path)

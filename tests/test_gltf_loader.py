@@ -202,3 +202,46 @@ def test_obj_normals_follow_the_assimp_path(tmp_path):
     assert len(v) == 4 + 3                                                 # the quad's two triangles share their 4 corners; the other face has its own
     mesh = ev.load_mesh({"path": str(flat), "scale": 2.0}, "original mesh")
     assert mesh.num_triangles == 3 and np.isclose(np.abs(mesh.vertices).max(), 2.0) and mesh.normals.shape == mesh.vertices.shape
+
+
+def test_ply_reader_variants(tmp_path):
+    """Binary PLY in both byte orders with extra properties and elements, normals, quads and ragged polygon lists; a
+    larger file goes through the whole-element numpy path (no per-row Python)."""
+    import struct, time
+    ev = nrb.evaluate
+    head = ("ply\nformat {fmt} 1.0\ncomment made by a test\nelement vertex 5\nproperty float x\nproperty float y\nproperty float z\n"
+            "property float nx\nproperty float ny\nproperty float nz\nproperty uchar red\n"
+            "element face 2\nproperty uchar flags\nproperty list uchar int vertex_indices\n"
+            "element edge 1\nproperty int a\nproperty int b\nend_header\n")
+    pos = [(0, 0, 0), (1, 0, 0), (1, 1, 0), (0, 1, 0), (0, 0, 1)]
+    for fmt, e in (("binary_little_endian", "<"), ("binary_big_endian", ">")):
+        body = b"".join(struct.pack(e + "6fB", *p, 0, 0, 2, 7) for p in pos)
+        body += struct.pack(e + "BB4i", 1, 4, 0, 1, 2, 3) + struct.pack(e + "BB3i", 0, 3, 0, 4, 1)   # a quad, then a triangle (ragged)
+        body += struct.pack(e + "2i", 0, 1)
+        path = tmp_path / (fmt + ".ply")
+        path.write_bytes(head.format(fmt=fmt).encode() + body)
+        v, f, n = ev.load_ply_full(str(path))
+        assert v.tolist() == [list(map(float, p)) for p in pos]
+        assert f.tolist() == [[0, 1, 2], [0, 2, 3], [0, 4, 1]]
+        assert n.shape == (5, 3) and np.all(n[:, 2] == 2)
+        mesh = ev.load_mesh({"path": str(path), "scale": 1.0}, "original mesh")
+        assert mesh.num_triangles == 3 and np.allclose(np.linalg.norm(mesh.normals, axis=1), 1)     # file normals, normalised
+    asc = tmp_path / "asc.ply"
+    asc.write_text("ply\nformat ascii 1.0\nelement vertex 4\nproperty double x\nproperty double y\nproperty double z\n"
+                   "element face 1\nproperty list uchar uint vertex_index\nend_header\n0 0 0\n1 0 0\n1 1 0\n\n0 1 0\n4 0 1 2 3\n")
+    v, f, n = ev.load_ply_full(str(asc))
+    assert n is None and v.dtype == np.float32 and f.tolist() == [[0, 1, 2], [0, 2, 3]]
+    # 200 K triangles, uniform lists: one structured read
+    rng = np.random.default_rng(0)
+    nv, nf = 100_000, 200_000
+    verts = rng.standard_normal((nv, 3)).astype("<f4")
+    faces = np.zeros(nf, np.dtype([("n", "u1"), ("i", "<i4", (3,))]))
+    faces["n"] = 3
+    faces["i"] = rng.integers(0, nv, (nf, 3))
+    big = tmp_path / "big.ply"
+    big.write_bytes((f"ply\nformat binary_little_endian 1.0\nelement vertex {nv}\nproperty float x\nproperty float y\nproperty float z\n"
+                     f"element face {nf}\nproperty list uchar int vertex_indices\nend_header\n").encode() + verts.tobytes() + faces.tobytes())
+    t0 = time.time()
+    v, f, n = ev.load_ply_full(str(big))
+    assert time.time() - t0 < 2.0
+    assert np.array_equal(v, verts) and np.array_equal(f, faces["i"].astype(np.uint32))
