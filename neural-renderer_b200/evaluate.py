@@ -129,8 +129,15 @@ def flat_shaded(vertices, faces):
     ln = np.linalg.norm(n, axis=1, keepdims=True)
     n = np.where(ln > 0, n / np.where(ln > 0, ln, 1), np.array([0, 1, 0], np.float32)).astype(np.float32)
     corners = np.concatenate([p.reshape(-1, 3), np.repeat(n, 3, axis=0)], 1)  # [3T, 6]
-    uniq, inverse = np.unique(corners.view([("", np.float32)] * 6).reshape(-1), return_inverse=True)
-    uniq = uniq.view(np.float32).reshape(-1, 6)
+    corners = np.ascontiguousarray(corners + np.float32(0.0))    # -0 -> +0: equal values, equal bits
+    keys = corners.view(np.uint64)                               # [3T, 3]: rows compare as three 64-bit words
+    order = np.lexsort((keys[:, 2], keys[:, 1], keys[:, 0]))
+    sorted_keys = keys[order]
+    first = np.ones(len(order), bool)
+    first[1:] = np.any(sorted_keys[1:] != sorted_keys[:-1], axis=1)
+    inverse = np.empty(len(order), np.int64)
+    inverse[order] = np.cumsum(first) - 1
+    uniq = corners[order[first]]
     return uniq[:, :3].copy(), inverse.reshape(-1, 3).astype(np.uint32), uniq[:, 3:].copy()
 
 
